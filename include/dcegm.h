@@ -1,0 +1,237 @@
+/*
+ * dcegm.h — C ABI of libdcegm_cuda.so, the B200-native DC-EGM solver.
+ *
+ * This is the drop-in boundary named by BASELINE.json `north_star`: the host
+ * side (Julia `ccall`, or the Python/ctypes mirror in dcegm.jl_b200/) fills an
+ * array of POD `dcegm_param` (one per model parameterisation) and receives the
+ * value/policy polylines the reference stores in `m.v[id,it]` / `m.c[id,it]`
+ * (`Envelope.env :: MLine`, a `Vector{Point{Float64}}` — bit-compatible with the
+ * interleaved (x,y) doubles used here).
+ *
+ * The reference has no FFI of its own (pure Julia).  Each entry point below cites
+ * the Julia function (file:line under the reference tree) whose work it replaces.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative DCEGM_E_* code; nothing
+ *     throws or aborts across the ABI; dcegm_last_error() gives the text.
+ *   - the caller owns every pointer it passes in and every host destination
+ *     buffer; the library owns all device memory and streams (freed by
+ *     dcegm_destroy).  One handle per GPU; a handle is used from one host thread
+ *     at a time.
+ *   - indices are 0-based: it = 0..nT-1 (reference period it+1), id = 0 worker /
+ *     1 retiree (reference id = 1 / 2), iy = 0..nstate-1.
+ *   - there is NO CPU fallback: without a CUDA device dcegm_create fails.
+ */
+#ifndef DCEGM_H
+#define DCEGM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DCEGM_ABI_VERSION 1
+
+/* ---- error codes (function return values) --------------------------------- */
+#define DCEGM_OK            0
+#define DCEGM_E_INVALID    (-1)  /* bad argument (null pointer, size mismatch, unsupported size) */
+#define DCEGM_E_CUDA       (-2)  /* CUDA runtime error, see dcegm_last_error */
+#define DCEGM_E_NOSOLUTION (-3)  /* fetch before any solve */
+#define DCEGM_E_NODEVICE   (-4)  /* no CUDA device: the library has no CPU path */
+#define DCEGM_E_CAPACITY   (-5)  /* destination buffer too small */
+
+/* ---- per-model status bits (dcegm_status) ---------------------------------
+ * Each bit corresponds to a condition under which the reference would throw a
+ * Julia exception; a failing model never aborts the batch. */
+#define DCEGM_ST_OK              0u
+#define DCEGM_ST_ISECT_OVERFLOW  (1u << 0) /* more intersections than isec_cap */
+#define DCEGM_ST_LINE_OVERFLOW   (1u << 1) /* a line outgrew `cap` points */
+#define DCEGM_ST_NONMONOTONE     (1u << 2) /* a stored line is not strictly increasing in x: the next
+                                              period's interpolate() throws (line.jl:236) */
+#define DCEGM_ST_NO_BRACKET      (1u << 3) /* fzero without sign change (envelope.jl:199,225-228) */
+#define DCEGM_ST_MISALIGNED      (1u << 4) /* insert_left / insert_right lengths differ (dc_algo.jl:486-491) */
+#define DCEGM_ST_ALL_FALLING     (1u << 5) /* splitLine returned no section (envelope.jl:97-104) */
+#define DCEGM_ST_NONFINITE       (1u << 6) /* NaN/Inf in a computed line */
+#define DCEGM_ST_SEG_OVERFLOW    (1u << 7) /* more sections than seg_cap */
+#define DCEGM_ST_INSERT_RANGE    (1u << 8) /* kink insertion index out of range (dc_algo.jl:472,489) */
+#define DCEGM_ST_LOOP_LIMIT      (1u << 9) /* third-line loop did not terminate (envelope.jl:197-240) */
+
+/* ---- model parameters: POD mirror of `mutable struct Param` ----------------
+ * reference: src/param.jl:33-70, defaults src/param.json, SURVEY.md App. C.
+ * Derived fields (neg_gamma, oneminusgamma, ...; param.jl:90-93) are recomputed
+ * by the library. */
+typedef struct dcegm_param {
+    double gamma;        /* CRRA coefficient                    (1.95) */
+    double beta;         /* discount factor                     (0.95) */
+    double sigma;        /* income shock std                    (0.35) */
+    double lambda;       /* taste-shock scale                   (2e-6) */
+    double R;            /* gross interest                      (1.0526315789473684) */
+    double a_high;       /* upper bound of savings grid         (50) */
+    double a_low;        /* lower bound of savings grid         (0) */
+    double a_lowT;       /* lower bound in the last period      (0) */
+    double cfloor;       /* consumption floor                   (1e-3) */
+    double cfloor_plot;  /* unused on this path                 (0.01) */
+    double alpha;        /* disutility of work                  (0.35) */
+    double alphaT;       /* unused on this path                 (0) */
+    double inc0, inc1, inc2; /* income profile                  (0.75, 0.04, 2e-4) */
+    double rho;          /* AR1 persistence (GModel)            (0.95) */
+    double pension;      /*                                      (0) */
+    double delta;        /* prob. of returning to work (FModel) (0) */
+    double maxinterest;  /* unused on this path                 (200) */
+    double bbar;         /* bequest luxury shifter              (7.7) */
+    double nu;           /* bequest strength                    (0) */
+    double initw0, initw1; /* simulator initial wealth interval (5, 20) */
+    int32_t na;          /* savings grid points                 (100) */
+    int32_t ny;          /* income nodes                        (5) */
+    int32_t nT;          /* periods                             (25) */
+    int32_t nD;          /* discrete choices, must be 2         (2) */
+    int32_t k;           /* unused on this path                 (100) */
+    int32_t retage;      /* mandatory retirement period         (26) */
+    int32_t nsims;       /* simulated agents                    (100) */
+    int32_t quad_group;  /* lanes sharing one quadrature sum (power of two, 1 = ascending
+                            serial order; no reference field — the reference's order is
+                            BLAS-internal, dc_algo.jl:58,74).  0 means 1. */
+    int64_t rseed;       /* simulator seed                      (25032020) */
+} dcegm_param;
+
+/* fill *p with the defaults of src/param.json */
+void dcegm_param_defaults(dcegm_param* p);
+
+/* ---- which solver produced the resident solution -------------------------- */
+#define DCEGM_MODEL_F       1   /* dc_EGM!(::FModel)  dc_algo.jl:8-105   */
+#define DCEGM_MODEL_G       2   /* dc_EGM!(::GModel)  dc_algo.jl:112-206 */
+#define DCEGM_MODEL_MINIMAL 3   /* minimal_EGM        minimal_EGM.jl:3-43 */
+
+/* ---- line kinds ------------------------------------------------------------ */
+#define DCEGM_KIND_C       0   /* m.c[id,it].env  (policy)            */
+#define DCEGM_KIND_V       1   /* m.v[id,it].env  (value)             */
+#define DCEGM_KIND_CDIRTY  2   /* m.cdirty[id,it] (dc_algo.jl:79-82)  */
+#define DCEGM_KIND_VDIRTY  3   /* m.vdirty[id,it]                     */
+
+/* ---- solve flags ------------------------------------------------------------ */
+#define DCEGM_KEEP_DIRTY   (1u << 0)  /* runfdemo: also keep the pre-envelope lines */
+#define DCEGM_SUMMARY_ONLY (1u << 1)  /* do not materialise lines in HBM, only summaries */
+
+/* ---- geometry of the resident solution ------------------------------------- *
+ * lines  : double [nmodels][nT][nstate][2 id][2 kind(c,v)][cap][2 (x,y)]
+ * lens   : int32  [nmodels][nT][nstate][2 id][2 kind]
+ * vbound : double [nmodels][nT][nstate][2 id]           Envelope.vbound (envelope.jl:20)
+ * meta   : dcegm_env_meta [nmodels][nT][nstate]         worker (id=0) envelope call
+ * isects : double [nmodels][nT][nstate][isec_cap][2]    Envelope.isects
+ * removed: uint32 [nmodels][nT][nstate][rem_words]      bit k set <=> index k (0-based, in the
+ *          line handed to secondary_envelope, i.e. including bend-back points) is in
+ *          Envelope.removed (envelope.jl:64-71)
+ * dirty  : double [nmodels][nT][nstate][2 id][2 kind][na][2]   (only with DCEGM_KEEP_DIRTY)
+ * For DCEGM_MODEL_MINIMAL nstate = 1 and only (id 0, kind c) is used: x = m[it], y = c[it].
+ */
+typedef struct dcegm_layout {
+    int32_t model;      /* DCEGM_MODEL_* */
+    int32_t nmodels;
+    int32_t na, ny, nT;
+    int32_t nstate;     /* 1 (F, minimal) or ny (G) */
+    int32_t cap;        /* points per line slot */
+    int32_t isec_cap;
+    int32_t rem_words;
+    int32_t seg_cap;
+    int32_t has_dirty;
+    int32_t has_lines;
+} dcegm_layout;
+
+typedef struct dcegm_env_meta {
+    int32_t n_segments;   /* sections returned by splitLine (envelope.jl:80-126); 1 = no envelope needed */
+    int32_t n_isects;     /* length(Envelope.isects) */
+    int32_t n_removed;    /* length(Envelope.removed) */
+    int32_t n_prepended;  /* bend-back points prepended by do_secondary (dc_algo.jl:406-417) */
+} dcegm_env_meta;
+
+/* fixed-size per-model record: the payload of the one allgather of a multi-GPU sweep */
+#define DCEGM_SUMMARY_NPROBE 8
+typedef struct dcegm_summary {
+    int32_t status;            /* DCEGM_ST_* bits */
+    int32_t n_env_periods;     /* (it,iy) worker steps where the envelope removed points */
+    int32_t tot_segments;
+    int32_t tot_isects;
+    int32_t tot_removed;
+    int32_t max_len;           /* longest stored line */
+    int64_t tot_points;        /* sum of all line lengths */
+    double  v1_probe[DCEGM_SUMMARY_NPROBE]; /* worker value, period 1, state 0, at probe cash-on-hand */
+    double  c1_probe[DCEGM_SUMMARY_NPROBE]; /* worker policy, same points */
+    double  checksum_c;        /* sum of all policy ordinates of period 1 */
+    double  checksum_v;        /* sum of all finite value ordinates of period 1 */
+} dcegm_summary;
+
+typedef struct dcegm_ctx* dcegm_handle;
+
+/* ---- lifetime ---------------------------------------------------------------- */
+int  dcegm_abi_version(void);
+int  dcegm_create(int device_ordinal, dcegm_handle* out);
+int  dcegm_destroy(dcegm_handle h);
+const char* dcegm_last_error(dcegm_handle h);   /* valid until the next call on h */
+
+/* pinned host memory for the destination buffers of the fetch calls (optional) */
+int  dcegm_host_alloc(void** ptr, size_t bytes);
+int  dcegm_host_free(void* ptr);
+
+/* ---- solvers (blocking) -------------------------------------------------------
+ * params: host array of nmodels records; all must share na, ny, nT (one launch
+ * geometry per call).  The solution stays resident on the device until the next
+ * solve or dcegm_destroy.
+ *   dcegm_solve_f       replaces runf / runfdemo / dc_EGM!(::FModel)  dc_algo.jl:8-105,335-348
+ *                       incl. FModel(p) setup                          param.jl:189-223
+ *   dcegm_solve_g       replaces rung / dc_EGM!(::GModel)             dc_algo.jl:112-206,356-362
+ *                       incl. GModel(p) setup                          param.jl:261-310
+ *   dcegm_solve_minimal replaces minimal_EGM (data, not the plot)     minimal_EGM.jl:3-43
+ */
+int  dcegm_solve_f(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
+int  dcegm_solve_g(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
+int  dcegm_solve_minimal(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
+
+/* ---- results -------------------------------------------------------------------- */
+int  dcegm_get_layout(dcegm_handle h, dcegm_layout* out);
+/* one polyline; replaces getx/gety(m.c[id,it].env) etc. (line.jl:121-124).  xy receives len
+ * interleaved (x,y) pairs; *len is set even when cap_points is too small (then DCEGM_E_CAPACITY). */
+int  dcegm_fetch_line(dcegm_handle h, int model, int kind, int id, int iy, int it,
+                      double* xy, int cap_points, int* len);
+/* bulk copies of models [first, first+count) in the layout documented above */
+int  dcegm_fetch_lines(dcegm_handle h, int first, int count, double* lines);
+int  dcegm_fetch_lens(dcegm_handle h, int first, int count, int32_t* lens);
+int  dcegm_fetch_vbound(dcegm_handle h, int first, int count, double* vbound);
+int  dcegm_fetch_meta(dcegm_handle h, int first, int count, dcegm_env_meta* meta);
+int  dcegm_fetch_isects(dcegm_handle h, int first, int count, double* isects);
+int  dcegm_fetch_removed(dcegm_handle h, int first, int count, uint32_t* removed);
+int  dcegm_fetch_dirty(dcegm_handle h, int first, int count, double* dirty);
+/* densely packed lines: offsets[(count*nT*nstate*4)+1] prefix offsets in points, xy the
+ * concatenated points of all lines in layout order; *npoints total.  Pass xy == NULL to
+ * query npoints/offsets only. */
+int  dcegm_fetch_packed(dcegm_handle h, int first, int count, double* xy, size_t cap_points,
+                        int64_t* offsets, int64_t* npoints);
+int  dcegm_status(dcegm_handle h, int32_t* per_model_status);   /* nmodels entries */
+int  dcegm_summaries(dcegm_handle h, dcegm_summary* dst);       /* nmodels records, host */
+/* device-to-device copy of the summaries into caller-provided device memory (the send
+ * buffer of the NCCL allgather of a multi-GPU sweep) */
+int  dcegm_summaries_to_device(dcegm_handle h, void* dst_device, size_t bytes);
+
+/* ---- timing of the last solve, measured with CUDA events on the library's stream ---- */
+typedef struct dcegm_timing {
+    float  setup_host_ms;   /* FModel/GModel grids and tables on the host */
+    float  h2d_ms;
+    float  kernel_ms;       /* all solver kernels */
+    int32_t n_launches;     /* kernels launched by the solve */
+    int32_t _pad;
+} dcegm_timing;
+int  dcegm_last_timing(dcegm_handle h, dcegm_timing* out);
+
+/* ---- split solve for benchmarking with inputs already resident in HBM --------------
+ * dcegm_upload_f does the host setup + H2D; dcegm_run launches the solver kernels on the
+ * data already resident (can be called repeatedly). */
+int  dcegm_upload_f(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
+int  dcegm_upload_g(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
+int  dcegm_upload_minimal(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
+int  dcegm_run(dcegm_handle h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DCEGM_H */

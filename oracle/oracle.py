@@ -1,0 +1,186 @@
+"""ctypes front end of oracle/liboracle.so — TEST INFRASTRUCTURE ONLY (see dcegm_oracle.cpp).
+
+May be imported from tests/, __graft_entry__.smoke() and the cpu_baseline / --impl reference
+legs of bench.py; never from dcegm.jl_b200/."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+import dcegm_jl_b200 as pkg
+from dcegm_jl_b200 import _abi
+from dcegm_jl_b200.param import params_array
+from dcegm_jl_b200.solution import Solution
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "liboracle.so")
+    src = os.path.join(_HERE, "dcegm_oracle.cpp")
+    hdr = os.path.join(_HERE, "..", "include", "dcegm.h")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(src), os.path.getmtime(hdr)):
+        subprocess.check_call(["make", "-C", _HERE, "-B" if force else "-s"], stdout=subprocess.DEVNULL)
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = C.CDLL(build())
+        dp = C.POINTER(C.c_double)
+        ip = C.POINTER(C.c_int)
+        _LIB.oracle_norminv.restype = C.c_double
+        _LIB.oracle_norminv.argtypes = [C.c_double]
+        for f in ("oracle_u",):
+            getattr(_LIB, f).restype = C.c_double
+            getattr(_LIB, f).argtypes = [C.c_double, C.c_int, C.POINTER(_abi.dcegm_param)]
+        for f in ("oracle_up", "oracle_iup"):
+            getattr(_LIB, f).restype = C.c_double
+            getattr(_LIB, f).argtypes = [C.c_double, C.POINTER(_abi.dcegm_param)]
+        _LIB.oracle_income.restype = C.c_double
+        _LIB.oracle_income.argtypes = [C.c_int, C.c_double, C.POINTER(_abi.dcegm_param)]
+        _LIB.oracle_solve.restype = C.c_int
+    return _LIB
+
+
+def _p(a, t=C.c_double):
+    return a.ctypes.data_as(C.POINTER(t)) if a is not None else None
+
+
+def layout(model, nmodels, na, ny, nT, keep_dirty=False):
+    lay = _abi.dcegm_layout()
+    lib().oracle_layout(model, nmodels, na, ny, nT, int(keep_dirty), C.byref(lay))
+    return lay
+
+
+def solve(model, params, keep_dirty=False, literal=False, nthreads=1):
+    """Solve a batch of Param on the host.  Returns a Solution in the layout of include/dcegm.h."""
+    arr = params_array(params)
+    n = len(params)
+    lay = layout(model, n, arr[0].na, arr[0].ny, arr[0].nT, keep_dirty)
+    s = Solution.allocate(lay, keep_dirty)
+    rc = lib().oracle_solve(
+        C.c_int(model), arr, C.c_int(n), C.c_int(int(keep_dirty)), C.c_int(int(literal)), C.c_int(nthreads),
+        _p(s.lines), _p(s.lens, C.c_int32), _p(s.vbound), _p(s.meta, C.c_int32), _p(s.isects),
+        _p(s.removed, C.c_uint32), _p(s.dirty), _p(s.status, C.c_int32))
+    if rc != 0:
+        raise ValueError("oracle_solve: all models of a batch must share na, ny, nT")
+    return s
+
+
+def solve_f(params, **kw):
+    return solve(_abi.MODEL_F, params, **kw)
+
+
+def solve_g(params, **kw):
+    return solve(_abi.MODEL_G, params, **kw)
+
+
+def solve_minimal(params, **kw):
+    return solve(_abi.MODEL_MINIMAL, params, **kw)
+
+
+def secondary_envelope(x, y, literal=False):
+    x = np.ascontiguousarray(x, float)
+    y = np.ascontiguousarray(y, float)
+    n = len(x)
+    cap = 2 * n + 64
+    env = np.zeros((cap, 2))
+    isec = np.zeros((cap, 2))
+    rem = np.zeros(cap, np.int32)
+    ne, ni, nr, ns = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+    st = lib().oracle_secondary_envelope(_p(x), _p(y), n, int(literal), _p(env), cap, C.byref(ne), _p(isec), cap,
+                                         C.byref(ni), _p(rem, C.c_int32), cap, C.byref(nr), C.byref(ns))
+    return dict(env=env[: ne.value], isects=isec[: ni.value], removed=rem[: nr.value], n_segments=ns.value, status=st)
+
+
+def upper_env(lines, literal=False):
+    """lines: list of (x, y) arrays, one per section"""
+    xs = np.concatenate([np.asarray(l[0], float) for l in lines])
+    ys = np.concatenate([np.asarray(l[1], float) for l in lines])
+    off = np.zeros(len(lines) + 1, np.int32)
+    off[1:] = np.cumsum([len(l[0]) for l in lines])
+    cap = 2 * len(xs) + 64
+    env = np.zeros((cap, 2))
+    isec = np.zeros((cap, 2))
+    ne, ni = C.c_int(), C.c_int()
+    st = lib().oracle_upper_env(_p(xs), _p(ys), _p(off, C.c_int32), len(lines), int(literal), _p(env), cap,
+                                C.byref(ne), _p(isec), cap, C.byref(ni))
+    return dict(env=env[: ne.value], isects=isec[: ni.value], status=st)
+
+
+def split_line(x, y):
+    x = np.ascontiguousarray(x, float)
+    y = np.ascontiguousarray(y, float)
+    cap = len(x) + 2
+    ln = np.zeros(cap, np.int32)
+    lo = np.zeros(cap)
+    hi = np.zeros(cap)
+    ns = lib().oracle_split_line(_p(x), _p(y), len(x), _p(ln, C.c_int32), _p(lo), _p(hi), cap)
+    return [(int(ln[s]), float(lo[s]), float(hi[s])) for s in range(ns)]
+
+
+def interp(x, y, q):
+    x = np.ascontiguousarray(x, float)
+    y = np.ascontiguousarray(y, float)
+    q = np.ascontiguousarray(q, float)
+    ox = np.zeros(len(q))
+    oy = np.zeros(len(q))
+    lib().oracle_interp(_p(x), _p(y), len(x), _p(q), len(q), _p(ox), _p(oy))
+    return ox, oy
+
+
+def ccp(v1, v2, lam):
+    v1 = np.ascontiguousarray(v1, float)
+    v2 = np.ascontiguousarray(v2, float)
+    out = np.zeros(len(v1))
+    lib().oracle_ccp(_p(v1), _p(v2), len(v1), C.c_double(lam), _p(out))
+    return out
+
+
+def logsum(v1, v2, lam):
+    v1 = np.ascontiguousarray(v1, float)
+    v2 = np.ascontiguousarray(v2, float)
+    out = np.zeros(len(v1))
+    lib().oracle_logsum(_p(v1), _p(v2), len(v1), C.c_double(lam), _p(out))
+    return out
+
+
+def quadpoints(n, lo=0.0, hi=1.0):
+    x = np.zeros(n)
+    w = np.zeros(n)
+    lib().oracle_quadpoints(n, C.c_double(lo), C.c_double(hi), _p(x), _p(w))
+    return x, w
+
+
+def norminv(p):
+    return lib().oracle_norminv(float(p))
+
+
+def gausshermite(n):
+    x = np.zeros(n)
+    w = np.zeros(n)
+    lib().oracle_gausshermite(n, _p(x), _p(w))
+    return x, w
+
+
+def rouwenhorst(rho, mu, sigma, n):
+    z = np.zeros(n)
+    P = np.zeros((n, n))
+    lib().oracle_rouwenhorst(C.c_double(rho), C.c_double(mu), C.c_double(sigma), n, _p(z), _p(P))
+    return z, P
+
+
+def scalegrid(lb, ub, n, logorder=1):
+    out = np.zeros(n)
+    lib().oracle_scalegrid(C.c_double(lb), C.c_double(ub), n, logorder, _p(out))
+    return out
+
+
+def linrange(lo, hi, n):
+    out = np.zeros(n)
+    lib().oracle_linrange(C.c_double(lo), C.c_double(hi), n, _p(out))
+    return out
