@@ -1,0 +1,429 @@
+// dcegm_abi.cu — the C ABI of libdcegm_cuda.so (include/dcegm.h): handle, device memory, streams,
+// uploads, kernel launches and result transfers.  No solver arithmetic lives here and there is no
+// CPU path: every solve runs the sm_100a kernels of solver_*.cu.
+#include <cuda_runtime.h>
+
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/dcegm.h"
+#include "device_common.cuh"
+#include "host_setup.hpp"
+
+namespace dcegm {
+cudaError_t launch_solve_f(const DeviceBatch& B, cudaStream_t stream);
+cudaError_t launch_solve_g(const DeviceBatch& B, cudaStream_t stream);
+cudaError_t launch_solve_minimal(const DeviceBatch& B, cudaStream_t stream);
+cudaError_t launch_pack_lines(const DeviceBatch& B, int first, int count, const long long* d_offsets, double2* d_dst,
+                              cudaStream_t stream);
+size_t solver_f_smem_bytes(int cap, int isec_cap);
+size_t solver_g_smem_bytes(int cap, int isec_cap, int na);
+}  // namespace dcegm
+
+using namespace dcegm;
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+struct dcegm_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    std::string err;
+    DevBuf models, grids, off, wgt, lines, lens, vbound, meta, isects, removed, dirty, status, summaries, pack_off, pack_xy;
+    DeviceBatch batch{};
+    HostTables tab;
+    bool uploaded = false, solved = false;
+    unsigned flags = 0;
+    int max_smem_optin = 0;
+    dcegm_timing timing{};
+};
+
+namespace {
+
+int fail(dcegm_ctx* h, int code, const std::string& msg) {
+    if (h) h->err = msg;
+    return code;
+}
+int cuda_fail(dcegm_ctx* h, cudaError_t e, const char* what) {
+    return fail(h, DCEGM_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CK(call)                                                \
+    do {                                                        \
+        cudaError_t e_ = (call);                                \
+        if (e_ != cudaSuccess) return cuda_fail(h, e_, #call);  \
+    } while (0)
+
+int ensure(dcegm_ctx* h, DevBuf& b, size_t bytes, bool zero_new) {
+    if (bytes <= b.cap) return DCEGM_OK;
+    if (b.p) CK(cudaFree(b.p));
+    b.p = nullptr;
+    b.cap = 0;
+    CK(cudaMalloc(&b.p, bytes));
+    b.cap = bytes;
+    if (zero_new) CK(cudaMemsetAsync(b.p, 0, bytes, h->stream));
+    return DCEGM_OK;
+}
+
+int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsigned flags) {
+    if (!h) return DCEGM_E_INVALID;
+    if (!params || nmodels <= 0) return fail(h, DCEGM_E_INVALID, "params is null or nmodels <= 0");
+    CK(cudaSetDevice(h->device));
+    h->uploaded = h->solved = false;
+    auto t0 = std::chrono::steady_clock::now();
+    const char* why = "";
+    if (!build_tables(model, params, nmodels, h->tab, &why)) return fail(h, DCEGM_E_INVALID, why);
+    auto t1 = std::chrono::steady_clock::now();
+    h->timing.setup_host_ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
+
+    const int na = params[0].na, ny = params[0].ny, nT = params[0].nT;
+    dcegm_layout lay;
+    make_layout(model, nmodels, na, ny, nT, (flags & DCEGM_KEEP_DIRTY) ? 1 : 0, (flags & DCEGM_SUMMARY_ONLY) ? 0 : 1, &lay);
+    if (lay.cap > 65535) return fail(h, DCEGM_E_INVALID, "na too large for the shared-memory resident solver");
+    size_t smem = model == DCEGM_MODEL_F   ? solver_f_smem_bytes(lay.cap, lay.isec_cap)
+                  : model == DCEGM_MODEL_G ? solver_g_smem_bytes(lay.cap, lay.isec_cap, na)
+                                           : (size_t)(4 * (na + 1) * 8 + 1024);
+    if ((long long)smem > (long long)h->max_smem_optin) {
+        char msg[256];
+        snprintf(msg, sizeof msg,
+                 "na=%d needs %zu B of shared memory per CTA (device limit %d B): grid too fine for the "
+                 "shared-memory resident solver",
+                 na, smem, h->max_smem_optin);
+        return fail(h, DCEGM_E_INVALID, msg);
+    }
+
+    const size_t nslots = (size_t)nmodels * nT * lay.nstate * 4;
+    const size_t nstates = (size_t)nmodels * nT * lay.nstate;
+    int rc;
+    if ((rc = ensure(h, h->models, sizeof(DevModel) * nmodels, false))) return rc;
+    if ((rc = ensure(h, h->grids, sizeof(double) * h->tab.grids.size(), false))) return rc;
+    if ((rc = ensure(h, h->off, sizeof(double) * h->tab.off.size(), false))) return rc;
+    if ((rc = ensure(h, h->wgt, sizeof(double) * h->tab.wgt.size(), false))) return rc;
+    if (lay.has_lines)
+        if ((rc = ensure(h, h->lines, sizeof(double2) * nslots * lay.cap, true))) return rc;
+    if ((rc = ensure(h, h->lens, sizeof(int32_t) * nslots, true))) return rc;
+    if ((rc = ensure(h, h->vbound, sizeof(double) * nstates * 2, true))) return rc;
+    if ((rc = ensure(h, h->meta, sizeof(dcegm_env_meta) * nstates, true))) return rc;
+    if ((rc = ensure(h, h->isects, sizeof(double2) * nstates * lay.isec_cap, true))) return rc;
+    if ((rc = ensure(h, h->removed, sizeof(uint32_t) * nstates * lay.rem_words, true))) return rc;
+    if (lay.has_dirty)
+        if ((rc = ensure(h, h->dirty, sizeof(double2) * nslots * na, true))) return rc;
+    if ((rc = ensure(h, h->status, sizeof(int32_t) * nmodels, true))) return rc;
+    if ((rc = ensure(h, h->summaries, sizeof(dcegm_summary) * nmodels, true))) return rc;
+
+    CK(cudaEventRecord(h->ev[0], h->stream));
+    CK(cudaMemcpyAsync(h->models.p, h->tab.models.data(), sizeof(DevModel) * nmodels, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->grids.p, h->tab.grids.data(), sizeof(double) * h->tab.grids.size(), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->off.p, h->tab.off.data(), sizeof(double) * h->tab.off.size(), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->wgt.p, h->tab.wgt.data(), sizeof(double) * h->tab.wgt.size(), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaEventRecord(h->ev[1], h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaEventElapsedTime(&h->timing.h2d_ms, h->ev[0], h->ev[1]));
+
+    DeviceBatch& B = h->batch;
+    B.lay = lay;
+    B.models = (const DevModel*)h->models.p;
+    B.grids = (const double*)h->grids.p;
+    B.off = (const double*)h->off.p;
+    B.wgt = (const double*)h->wgt.p;
+    B.lines = lay.has_lines ? (double2*)h->lines.p : nullptr;
+    B.lens = (int32_t*)h->lens.p;
+    B.vbound = (double*)h->vbound.p;
+    B.meta = (dcegm_env_meta*)h->meta.p;
+    B.isects = (double2*)h->isects.p;
+    B.removed = (uint32_t*)h->removed.p;
+    B.dirty = lay.has_dirty ? (double2*)h->dirty.p : nullptr;
+    B.status = (int32_t*)h->status.p;
+    B.summaries = (dcegm_summary*)h->summaries.p;
+    h->flags = flags;
+    h->uploaded = true;
+    return DCEGM_OK;
+}
+
+int run(dcegm_ctx* h) {
+    if (!h) return DCEGM_E_INVALID;
+    if (!h->uploaded) return fail(h, DCEGM_E_NOSOLUTION, "dcegm_run before dcegm_upload_*");
+    CK(cudaSetDevice(h->device));
+    const DeviceBatch& B = h->batch;
+    const size_t nstates = (size_t)B.lay.nmodels * B.lay.nT * B.lay.nstate;
+    CK(cudaEventRecord(h->ev[2], h->stream));
+    // terminal-period slots of the per-state side tables are not written by the solver
+    CK(cudaMemsetAsync(B.isects, 0, sizeof(double2) * nstates * B.lay.isec_cap, h->stream));
+    CK(cudaMemsetAsync(B.removed, 0, sizeof(uint32_t) * nstates * B.lay.rem_words, h->stream));
+    cudaError_t e;
+    if (B.lay.model == DCEGM_MODEL_F)
+        e = launch_solve_f(B, h->stream);
+    else if (B.lay.model == DCEGM_MODEL_G)
+        e = launch_solve_g(B, h->stream);
+    else
+        e = launch_solve_minimal(B, h->stream);
+    if (e != cudaSuccess) return cuda_fail(h, e, "kernel launch");
+    CK(cudaEventRecord(h->ev[3], h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaEventElapsedTime(&h->timing.kernel_ms, h->ev[2], h->ev[3]));
+    h->timing.n_launches = 1;
+    h->solved = true;
+    return DCEGM_OK;
+}
+
+int need_solution(dcegm_ctx* h) {
+    if (!h) return DCEGM_E_INVALID;
+    if (!h->solved) return fail(h, DCEGM_E_NOSOLUTION, "no resident solution: call dcegm_solve_* first");
+    cudaError_t e = cudaSetDevice(h->device);
+    if (e != cudaSuccess) return cuda_fail(h, e, "cudaSetDevice");
+    return DCEGM_OK;
+}
+
+int check_range(dcegm_ctx* h, int first, int count) {
+    if (first < 0 || count < 0 || first + count > h->batch.lay.nmodels) return fail(h, DCEGM_E_INVALID, "model range out of bounds");
+    return DCEGM_OK;
+}
+
+template <typename T>
+int fetch_per_model(dcegm_ctx* h, const void* base, size_t per_model, int first, int count, T* dst) {
+    int rc = need_solution(h);
+    if (rc) return rc;
+    if ((rc = check_range(h, first, count))) return rc;
+    if (!dst) return fail(h, DCEGM_E_INVALID, "destination is null");
+    if (!base) return fail(h, DCEGM_E_NOSOLUTION, "this buffer was not produced by the last solve");
+    CK(cudaMemcpyAsync(dst, (const char*)base + per_model * sizeof(T) * first, per_model * sizeof(T) * count,
+                       cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return DCEGM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int dcegm_abi_version(void) { return DCEGM_ABI_VERSION; }
+
+void dcegm_param_defaults(dcegm_param* p) {  // src/param.json
+    if (!p) return;
+    memset(p, 0, sizeof *p);
+    p->gamma = 1.95;
+    p->beta = 0.95;
+    p->sigma = 0.35;
+    p->lambda = 2e-6;
+    p->R = 1.0526315789473684;
+    p->a_high = 50.0;
+    p->a_low = 0.0;
+    p->a_lowT = 0.0;
+    p->cfloor = 0.001;
+    p->cfloor_plot = 0.01;
+    p->alpha = 0.35;
+    p->alphaT = 0.0;
+    p->inc0 = 0.75;
+    p->inc1 = 0.04;
+    p->inc2 = 0.0002;
+    p->rho = 0.95;
+    p->pension = 0.0;
+    p->delta = 0.0;
+    p->maxinterest = 200.0;
+    p->bbar = 7.7;
+    p->nu = 0.0;
+    p->initw0 = 5.0;
+    p->initw1 = 20.0;
+    p->na = 100;
+    p->ny = 5;
+    p->nT = 25;
+    p->nD = 2;
+    p->k = 100;
+    p->retage = 26;
+    p->nsims = 100;
+    p->quad_group = 1;
+    p->rseed = 25032020;
+}
+
+int dcegm_create(int device_ordinal, dcegm_handle* out) {
+    if (!out) return DCEGM_E_INVALID;
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return DCEGM_E_NODEVICE;  // no CPU fallback
+    if (device_ordinal < 0 || device_ordinal >= ndev) return DCEGM_E_INVALID;
+    dcegm_ctx* h = new dcegm_ctx();
+    h->device = device_ordinal;
+    if (cudaSetDevice(device_ordinal) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete h;
+        return DCEGM_E_CUDA;
+    }
+    for (auto& ev : h->ev) cudaEventCreate(&ev);
+    cudaDeviceGetAttribute(&h->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device_ordinal);
+    *out = h;
+    return DCEGM_OK;
+}
+
+int dcegm_destroy(dcegm_handle h) {
+    if (!h) return DCEGM_E_INVALID;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    DevBuf* bufs[] = {&h->models, &h->grids, &h->off, &h->wgt, &h->lines, &h->lens, &h->vbound, &h->meta, &h->isects,
+                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy};
+    for (DevBuf* b : bufs)
+        if (b->p) cudaFree(b->p);
+    for (auto& ev : h->ev)
+        if (ev) cudaEventDestroy(ev);
+    cudaStreamDestroy(h->stream);
+    delete h;
+    return DCEGM_OK;
+}
+
+const char* dcegm_last_error(dcegm_handle h) { return h ? h->err.c_str() : "null handle"; }
+
+int dcegm_host_alloc(void** ptr, size_t bytes) {
+    if (!ptr) return DCEGM_E_INVALID;
+    return cudaHostAlloc(ptr, bytes, cudaHostAllocDefault) == cudaSuccess ? DCEGM_OK : DCEGM_E_CUDA;
+}
+int dcegm_host_free(void* ptr) { return cudaFreeHost(ptr) == cudaSuccess ? DCEGM_OK : DCEGM_E_CUDA; }
+
+int dcegm_upload_f(dcegm_handle h, const dcegm_param* p, int n, unsigned flags) { return upload(h, DCEGM_MODEL_F, p, n, flags); }
+int dcegm_upload_g(dcegm_handle h, const dcegm_param* p, int n, unsigned flags) { return upload(h, DCEGM_MODEL_G, p, n, flags); }
+int dcegm_upload_minimal(dcegm_handle h, const dcegm_param* p, int n, unsigned flags) {
+    return upload(h, DCEGM_MODEL_MINIMAL, p, n, flags);
+}
+int dcegm_run(dcegm_handle h) { return run(h); }
+
+int dcegm_solve_f(dcegm_handle h, const dcegm_param* p, int n, unsigned flags) {
+    int rc = upload(h, DCEGM_MODEL_F, p, n, flags);
+    return rc ? rc : run(h);
+}
+int dcegm_solve_g(dcegm_handle h, const dcegm_param* p, int n, unsigned flags) {
+    int rc = upload(h, DCEGM_MODEL_G, p, n, flags);
+    return rc ? rc : run(h);
+}
+int dcegm_solve_minimal(dcegm_handle h, const dcegm_param* p, int n, unsigned flags) {
+    int rc = upload(h, DCEGM_MODEL_MINIMAL, p, n, flags);
+    return rc ? rc : run(h);
+}
+
+int dcegm_get_layout(dcegm_handle h, dcegm_layout* out) {
+    if (!h || !out) return DCEGM_E_INVALID;
+    if (!h->uploaded) return fail(h, DCEGM_E_NOSOLUTION, "no batch uploaded");
+    *out = h->batch.lay;
+    return DCEGM_OK;
+}
+
+int dcegm_fetch_line(dcegm_handle h, int model, int kind, int id, int iy, int it, double* xy, int cap_points, int* len) {
+    int rc = need_solution(h);
+    if (rc) return rc;
+    const dcegm_layout& l = h->batch.lay;
+    if (model < 0 || model >= l.nmodels || id < 0 || id > 1 || iy < 0 || iy >= l.nstate || it < 0 || it >= l.nT || kind < 0 ||
+        kind > 3 || !len)
+        return fail(h, DCEGM_E_INVALID, "dcegm_fetch_line: index out of range");
+    const bool dirty = kind >= 2;
+    const size_t slot = ((((size_t)model * l.nT + it) * l.nstate + iy) * 2 + id) * 2 + (kind & 1);
+    int n;
+    const double2* src;
+    if (dirty) {
+        if (!h->batch.dirty) return fail(h, DCEGM_E_NOSOLUTION, "solve without DCEGM_KEEP_DIRTY");
+        n = it == l.nT - 1 ? 0 : l.na;
+        src = h->batch.dirty + slot * (size_t)l.na;
+    } else {
+        if (!h->batch.lines) return fail(h, DCEGM_E_NOSOLUTION, "solve with DCEGM_SUMMARY_ONLY keeps no lines");
+        CK(cudaMemcpyAsync(&n, h->batch.lens + slot, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        src = h->batch.lines + slot * (size_t)l.cap;
+    }
+    *len = n;
+    if (n > cap_points || !xy) return fail(h, DCEGM_E_CAPACITY, "dcegm_fetch_line: destination too small");
+    if (n > 0) {
+        CK(cudaMemcpyAsync(xy, src, sizeof(double2) * n, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    return DCEGM_OK;
+}
+
+int dcegm_fetch_lines(dcegm_handle h, int first, int count, double* lines) {
+    if (!h) return DCEGM_E_INVALID;
+    const dcegm_layout& l = h->batch.lay;
+    return fetch_per_model<double>(h, h->batch.lines, (size_t)l.nT * l.nstate * 4 * l.cap * 2, first, count, lines);
+}
+int dcegm_fetch_lens(dcegm_handle h, int first, int count, int32_t* lens) {
+    if (!h) return DCEGM_E_INVALID;
+    const dcegm_layout& l = h->batch.lay;
+    return fetch_per_model<int32_t>(h, h->batch.lens, (size_t)l.nT * l.nstate * 4, first, count, lens);
+}
+int dcegm_fetch_vbound(dcegm_handle h, int first, int count, double* vbound) {
+    if (!h) return DCEGM_E_INVALID;
+    const dcegm_layout& l = h->batch.lay;
+    return fetch_per_model<double>(h, h->batch.vbound, (size_t)l.nT * l.nstate * 2, first, count, vbound);
+}
+int dcegm_fetch_meta(dcegm_handle h, int first, int count, dcegm_env_meta* meta) {
+    if (!h) return DCEGM_E_INVALID;
+    const dcegm_layout& l = h->batch.lay;
+    return fetch_per_model<dcegm_env_meta>(h, h->batch.meta, (size_t)l.nT * l.nstate, first, count, meta);
+}
+int dcegm_fetch_isects(dcegm_handle h, int first, int count, double* isects) {
+    if (!h) return DCEGM_E_INVALID;
+    const dcegm_layout& l = h->batch.lay;
+    return fetch_per_model<double>(h, h->batch.isects, (size_t)l.nT * l.nstate * l.isec_cap * 2, first, count, isects);
+}
+int dcegm_fetch_removed(dcegm_handle h, int first, int count, uint32_t* removed) {
+    if (!h) return DCEGM_E_INVALID;
+    const dcegm_layout& l = h->batch.lay;
+    return fetch_per_model<uint32_t>(h, h->batch.removed, (size_t)l.nT * l.nstate * l.rem_words, first, count, removed);
+}
+int dcegm_fetch_dirty(dcegm_handle h, int first, int count, double* dirty) {
+    if (!h) return DCEGM_E_INVALID;
+    const dcegm_layout& l = h->batch.lay;
+    return fetch_per_model<double>(h, h->batch.dirty, (size_t)l.nT * l.nstate * 4 * l.na * 2, first, count, dirty);
+}
+
+int dcegm_fetch_packed(dcegm_handle h, int first, int count, double* xy, size_t cap_points, int64_t* offsets, int64_t* npoints) {
+    int rc = need_solution(h);
+    if (rc) return rc;
+    if ((rc = check_range(h, first, count))) return rc;
+    if (!offsets || !npoints) return fail(h, DCEGM_E_INVALID, "offsets/npoints is null");
+    if (!h->batch.lines) return fail(h, DCEGM_E_NOSOLUTION, "solve with DCEGM_SUMMARY_ONLY keeps no lines");
+    const dcegm_layout& l = h->batch.lay;
+    const size_t per = (size_t)l.nT * l.nstate * 4, nsl = per * count;
+    std::vector<int32_t> lens(nsl);
+    CK(cudaMemcpyAsync(lens.data(), h->batch.lens + per * first, sizeof(int32_t) * nsl, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    offsets[0] = 0;
+    for (size_t s = 0; s < nsl; s++) offsets[s + 1] = offsets[s] + (lens[s] < l.cap ? lens[s] : l.cap);
+    *npoints = offsets[nsl];
+    if (!xy) return DCEGM_OK;
+    if ((size_t)*npoints > cap_points) return fail(h, DCEGM_E_CAPACITY, "dcegm_fetch_packed: destination too small");
+    if ((rc = ensure(h, h->pack_off, sizeof(long long) * (nsl + 1), false))) return rc;
+    if ((rc = ensure(h, h->pack_xy, sizeof(double2) * (size_t)*npoints, false))) return rc;
+    static_assert(sizeof(long long) == sizeof(int64_t), "offset width");
+    CK(cudaMemcpyAsync(h->pack_off.p, offsets, sizeof(int64_t) * (nsl + 1), cudaMemcpyHostToDevice, h->stream));
+    cudaError_t e = launch_pack_lines(h->batch, first, count, (const long long*)h->pack_off.p, (double2*)h->pack_xy.p, h->stream);
+    if (e != cudaSuccess) return cuda_fail(h, e, "pack kernel");
+    CK(cudaMemcpyAsync(xy, h->pack_xy.p, sizeof(double2) * (size_t)*npoints, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return DCEGM_OK;
+}
+
+int dcegm_status(dcegm_handle h, int32_t* st) {
+    if (!h) return DCEGM_E_INVALID;
+    return fetch_per_model<int32_t>(h, h->batch.status, 1, 0, h->batch.lay.nmodels, st);
+}
+int dcegm_summaries(dcegm_handle h, dcegm_summary* dst) {
+    if (!h) return DCEGM_E_INVALID;
+    return fetch_per_model<dcegm_summary>(h, h->batch.summaries, 1, 0, h->batch.lay.nmodels, dst);
+}
+int dcegm_summaries_to_device(dcegm_handle h, void* dst_device, size_t bytes) {
+    int rc = need_solution(h);
+    if (rc) return rc;
+    const size_t need = sizeof(dcegm_summary) * (size_t)h->batch.lay.nmodels;
+    if (!dst_device || bytes < need) return fail(h, DCEGM_E_CAPACITY, "dcegm_summaries_to_device: destination too small");
+    CK(cudaMemcpyAsync(dst_device, h->batch.summaries, need, cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return DCEGM_OK;
+}
+
+int dcegm_last_timing(dcegm_handle h, dcegm_timing* out) {
+    if (!h || !out) return DCEGM_E_INVALID;
+    *out = h->timing;
+    return DCEGM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,249 @@
+// device_common.cuh — shared-memory layout, polyline primitives and block-level helpers used by
+// the solver kernels.  FP64 throughout; compiled with -fmad=false so that every +,-,*,/ below is
+// a separately rounded IEEE operation in the order written (the CPU oracle is compiled with
+// -ffp-contract=off and uses the same order — decisions such as `x[k+1] > x[k]` or the arg-max
+// over segments then see the same bits given the same inputs).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/dcegm.h"
+#include "host_setup.hpp"
+
+namespace dcegm {
+
+constexpr int kThreads = 256;   // threads per CTA of the persistent solver kernels
+constexpr int kWarps = kThreads / 32;
+constexpr int kSegCap = 192;    // max sections of one splitLine
+constexpr int kSwitchMaxIsect = 8;  // max intersections produced by one change of winner
+
+// geometry of the resident solution; must match oracle_layout() (tests compare slot by slot)
+__host__ __device__ inline void make_layout(int model, int nmodels, int na, int ny, int nT, int keep_dirty,
+                                            int has_lines, dcegm_layout* l) {
+    l->model = model;
+    l->nmodels = nmodels;
+    l->na = na;
+    l->ny = ny;
+    l->nT = nT;
+    l->nstate = model == DCEGM_MODEL_G ? ny : 1;
+    l->isec_cap = na / 16 > 32 ? na / 16 : 32;
+    int cap = na + na / 10 + 2 * l->isec_cap + 2;
+    l->cap = (cap + 7) / 8 * 8;
+    l->rem_words = (l->cap + 31) / 32;
+    l->seg_cap = kSegCap;
+    l->has_dirty = keep_dirty;
+    l->has_lines = has_lines;
+}
+
+// device pointers of one batch solution + inputs
+struct DeviceBatch {
+    dcegm_layout lay;
+    const DevModel* models;
+    const double* grids;
+    const double* off;
+    const double* wgt;
+    double2* lines;          // [nmodels][nT][nstate][2][2][cap]
+    int32_t* lens;           // [nmodels][nT][nstate][2][2]
+    double* vbound;          // [nmodels][nT][nstate][2]
+    dcegm_env_meta* meta;    // [nmodels][nT][nstate]
+    double2* isects;         // [nmodels][nT][nstate][isec_cap]
+    uint32_t* removed;       // [nmodels][nT][nstate][rem_words]
+    double2* dirty;          // [nmodels][nT][nstate][2][2][na] or null
+    int32_t* status;         // [nmodels]
+    dcegm_summary* summaries;  // [nmodels]
+};
+
+__device__ __forceinline__ size_t line_slot(const dcegm_layout& l, int m, int it, int iy, int id, int kind) {
+    return ((((size_t)m * l.nT + it) * l.nstate + iy) * 2 + id) * 2 + kind;
+}
+__device__ __forceinline__ size_t state_slot(const dcegm_layout& l, int m, int it, int iy) {
+    return ((size_t)m * l.nT + it) * l.nstate + iy;
+}
+
+// ---------------------------------------------------------------------------------------------
+// polyline primitives (line.jl:220-254).  Lines live in shared memory as SoA (x[], y[]).
+// ---------------------------------------------------------------------------------------------
+// number of knots <= q  (searchsortedlast), branch-free binary search
+__device__ __forceinline__ int count_le(const double* __restrict__ x, int n, double q) {
+    int lo = 0, len = n;
+    while (len > 0) {
+        int half = len >> 1;
+        bool le = x[lo + half] <= q;
+        lo = le ? lo + half + 1 : lo;
+        len = le ? len - half - 1 : half;
+    }
+    return lo;
+}
+__device__ __forceinline__ int left_knot(const double* __restrict__ x, int n, double q) {
+    int i = count_le(x, n, q) - 1;
+    i = i < 0 ? 0 : i;
+    i = i > n - 2 ? n - 2 : i;
+    return i;
+}
+// Gridded(Linear()) inside, extrapolate(.., Line()) outside; y only
+__device__ __forceinline__ double interp_at(const double* __restrict__ x, const double* __restrict__ y, int n, int i,
+                                            double q) {
+    if (q < x[0]) {
+        double d = x[1] - x[0];
+        return y[0] + ((y[1] - y[0]) / d) * (q - x[0]);
+    }
+    if (q > x[n - 1]) {
+        double d = x[n - 1] - x[n - 2];
+        return y[n - 1] + ((y[n - 1] - y[n - 2]) / d) * (q - x[n - 1]);
+    }
+    double f = (q - x[i]) / (x[i + 1] - x[i]);
+    return (1.0 - f) * y[i] + f * y[i + 1];
+}
+__device__ __forceinline__ double interp_y(const double* __restrict__ x, const double* __restrict__ y, int n, double q) {
+    return interp_at(x, y, n, left_knot(x, n, q), q);
+}
+// whole-Point interpolation on a 2-point line (dc_algo.jl:446-478)
+__device__ __forceinline__ double2 interp2pt(double2 a, double2 b, double q) {
+    if (b.x < a.x) {  // sortx!(newleft)
+        double2 t = a;
+        a = b;
+        b = t;
+    }
+    double2 r;
+    double d = b.x - a.x;
+    if (q < a.x) {
+        r.x = a.x + ((b.x - a.x) / d) * (q - a.x);
+        r.y = a.y + ((b.y - a.y) / d) * (q - a.x);
+    } else if (q > b.x) {
+        r.x = b.x + ((b.x - a.x) / d) * (q - b.x);
+        r.y = b.y + ((b.y - a.y) / d) * (q - b.x);
+    } else {
+        // searchsortedlast clamps to the single interval
+        double f = (q - a.x) / d;
+        r.x = (1.0 - f) * a.x + f * b.x;
+        r.y = (1.0 - f) * a.y + f * b.y;
+    }
+    return r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// scalar economics (utils.jl)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double u_work(double x, bool working, const DevModel& p) {  // utils.jl:40-46
+    double dis = working ? p.alpha : 0.0;
+    if (p.gamma_is_one) return log(x) - dis;
+    return p.oneover_oneminusgamma * (pow(x, p.oneminusgamma) - 1.0) - dis;
+}
+__device__ __forceinline__ double u_plain(double x, const DevModel& p) {  // utils.jl:23-29
+    if (p.gamma_is_one) return log(x);
+    return p.oneover_oneminusgamma * pow(x, p.oneminusgamma);
+}
+__device__ __forceinline__ double up(double c, const DevModel& p) {  // utils.jl:72-78
+    if (p.gamma_is_one) return 1.0 / c;
+    return pow(c, p.neg_gamma);
+}
+__device__ __forceinline__ double iup(double u, const DevModel& p) {  // utils.jl:102-108
+    if (p.gamma_is_one) return 1.0 / u;
+    return pow(u, p.neg_oneover_gamma);
+}
+
+// ---------------------------------------------------------------------------------------------
+// block helpers (kThreads threads)
+// ---------------------------------------------------------------------------------------------
+// exclusive prefix sum of data[0..n) in place; returns the total.  red: kWarps+1 ints of scratch.
+__device__ inline int block_scan_excl(int* data, int n, int* red) {
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int per = (n + kThreads - 1) / kThreads;
+    const int b = tid * per;
+    int local = 0;
+    for (int i = 0; i < per; i++) {
+        int k = b + i;
+        if (k < n) local += data[k];
+    }
+    int inc = local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) red[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        int v = lane < kWarps ? red[lane] : 0;
+        int vi = v;
+#pragma unroll
+        for (int o = 1; o < kWarps; o <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, vi, o);
+            if (lane >= o) vi += t;
+        }
+        if (lane < kWarps) red[lane] = vi - v;
+        if (lane == kWarps - 1) red[kWarps] = vi;
+    }
+    __syncthreads();
+    int run = red[wid] + inc - local;
+    const int total = red[kWarps];
+    for (int i = 0; i < per; i++) {
+        int k = b + i;
+        if (k < n) {
+            int v = data[k];
+            data[k] = run;
+            run += v;
+        }
+    }
+    __syncthreads();
+    return total;
+}
+
+__device__ inline double block_min(double v, double* red) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+    if (lane == 0) red[wid] = v;
+    __syncthreads();
+    double r = red[0];
+#pragma unroll
+    for (int w = 1; w < kWarps; w++) r = fmin(r, red[w]);
+    __syncthreads();
+    return r;
+}
+__device__ inline int block_sum(int v, int* red) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) red[wid] = v;
+    __syncthreads();
+    int r = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; w++) r += red[w];
+    __syncthreads();
+    return r;
+}
+__device__ inline int block_min_int(int v, int* red) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
+    if (lane == 0) red[wid] = v;
+    __syncthreads();
+    int r = red[0];
+#pragma unroll
+    for (int w = 1; w < kWarps; w++) r = min(r, red[w]);
+    __syncthreads();
+    return r;
+}
+
+// Julia range(lo, stop=hi, length=n)[i] in double-double arithmetic: (lo*(n-1-i) + hi*i)/(n-1)
+__device__ inline double linrange_at(double lo, double hi, int n, int i) {
+    if (i == 0) return lo;
+    if (i == n - 1) return hi;
+    const double wa = (double)(n - 1 - i), wb = (double)i, d = (double)(n - 1);
+    // exact products
+    double p1 = __dmul_rn(lo, wa), e1 = __fma_rn(lo, wa, -p1);
+    double p2 = __dmul_rn(hi, wb), e2 = __fma_rn(hi, wb, -p2);
+    // two-sum
+    double s = __dadd_rn(p1, p2);
+    double bb = __dsub_rn(s, p1);
+    double es = __dadd_rn(__dsub_rn(p1, __dsub_rn(s, bb)), __dsub_rn(p2, bb));
+    double lo_part = __dadd_rn(__dadd_rn(e1, e2), es);
+    // (s + lo_part)/d
+    double q1 = __ddiv_rn(s, d);
+    double r = __dadd_rn(__fma_rn(-q1, d, s), lo_part);
+    double q2 = __ddiv_rn(r, d);
+    return __dadd_rn(q1, q2);
+}
+
+}  // namespace dcegm

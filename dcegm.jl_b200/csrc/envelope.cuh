@@ -1,0 +1,585 @@
+// envelope.cuh — block-level secondary upper envelope + policy repair, all in shared memory.
+//
+// Replaces, for one (model, period[, income state]) worker step:
+//   do_secondary        src/dc_algo.jl:393-495   (bend-back guard, kink insertion into the policy)
+//   secondary_envelope  src/envelope.jl:268-285
+//   splitLine           src/envelope.jl:80-126   (+ splitat, src/line.jl:323-345)
+//   upper_env           src/envelope.jl:143-258  (+ interp extrap=false / linemax, line.jl:220-288)
+//   removed!            src/envelope.jl:64-71
+//   tail of the step    src/dc_algo.jl:94-101    (vbound, prepend, sortx!)
+//
+// The reference walks the union grid sequentially.  Here every grid point finds its sorted
+// position, the winning section (first arg-max, strict >) and the interpolated top point with
+// one binary search per section; changes of winner are handled independently (each one is a
+// local root-finding problem on one cell of the union grid, with the reference's third-line
+// loop), and the emission order of the reference is rebuilt with prefix sums.  The result is
+// the same point sequence, intersection list and removed-index set as the sequential walk.
+#pragma once
+#include "device_common.cuh"
+
+namespace dcegm {
+
+struct EnvScratch {
+    // extended dirty worker line (EGM order): x, value, policy.  The EGM step writes the na
+    // points at offset `koff` = max(na/10-1,0); bend-back points are prepended in front.
+    double *Dx, *Dv, *Dc;
+    double *Tx, *Ty;  // per point: interpolated top Point of the winning section at this x
+    unsigned short *pos, *order, *ord2, *win, *swj;
+    unsigned char *fknot, *fuq, *frem, *cntI;
+    int* scan;
+    int* segb;               // kSegCap+1 boundaries (point indices)
+    unsigned char* segrise;  // kSegCap
+    double *islx, *isly, *isl2x, *isl2y;  // intersections (unsorted / sorted by emission order)
+    int *islkey, *isl2key;
+    double *insLx, *insLy, *insRx, *insRy;  // policy points to insert (dc_algo.jl:434-479)
+    unsigned char *insLok, *insRok;
+    int* red;     // kWarps+1 (+ a few counters)
+    double* redd; // kWarps
+    int* cnt;     // [0] nsw, [1] nis, [2] status bits, [3] tmp
+    int cap, isec_cap;
+};
+
+struct SegView {
+    const double* X;
+    const double* Y;
+    int base, st, len;
+};
+__device__ __forceinline__ SegView seg_view(const EnvScratch& S, const double* X, const double* Y, int s) {
+    SegView v;
+    int b0 = S.segb[s], b1 = S.segb[s + 1];
+    bool rise = S.segrise[s];
+    v.X = X;
+    v.Y = Y;
+    v.base = rise ? b0 : b1;
+    v.st = rise ? 1 : -1;
+    v.len = b1 - b0 + 1;
+    return v;
+}
+__device__ __forceinline__ double seg_x(const SegView& v, int i) { return v.X[v.base + v.st * i]; }
+__device__ __forceinline__ double seg_y(const SegView& v, int i) { return v.Y[v.base + v.st * i]; }
+__device__ __forceinline__ bool seg_in_domain(const SegView& v, double q) {
+    return !(q < seg_x(v, 0) || q > seg_x(v, v.len - 1));
+}
+// #knots <= q on the ascending view
+__device__ __forceinline__ int seg_count_le(const SegView& v, double q) {
+    int lo = 0, len = v.len;
+    while (len > 0) {
+        int half = len >> 1;
+        bool le = seg_x(v, lo + half) <= q;
+        lo = le ? lo + half + 1 : lo;
+        len = le ? len - half - 1 : half;
+    }
+    return lo;
+}
+// interp(L[s],[q]) with extrap=true (line.jl:220-254), y only
+__device__ __forceinline__ double seg_interp_y(const SegView& v, double q) {
+    const int n = v.len;
+    if (q < seg_x(v, 0)) {
+        double d = seg_x(v, 1) - seg_x(v, 0);
+        return seg_y(v, 0) + ((seg_y(v, 1) - seg_y(v, 0)) / d) * (q - seg_x(v, 0));
+    }
+    if (q > seg_x(v, n - 1)) {
+        double d = seg_x(v, n - 1) - seg_x(v, n - 2);
+        return seg_y(v, n - 1) + ((seg_y(v, n - 1) - seg_y(v, n - 2)) / d) * (q - seg_x(v, n - 1));
+    }
+    int i = seg_count_le(v, q) - 1;
+    i = i < 0 ? 0 : i;
+    i = i > n - 2 ? n - 2 : i;
+    double f = (q - seg_x(v, i)) / (seg_x(v, i + 1) - seg_x(v, i));
+    return (1.0 - f) * seg_y(v, i) + f * seg_y(v, i + 1);
+}
+
+// One change of winner between union-grid cells j-1 and j (envelope.jl:174-243).  Returns the
+// number of intersections found; points go to px/py (at most kSwitchMaxIsect are stored).
+__device__ inline int resolve_switch(const EnvScratch& S, const double* X, const double* V, int nseg, int k0, int k1,
+                                     double xl, double xr, double* px, double* py, unsigned* status) {
+    int ln1 = k0, ln2 = k1;
+    double pt1 = xl, pt2 = xr;
+    SegView A = seg_view(S, X, V, ln1), B = seg_view(S, X, V, ln2);
+    bool neither = seg_in_domain(A, pt1) && seg_in_domain(A, pt2) && seg_in_domain(B, pt1) && seg_in_domain(B, pt2);
+    double fa = seg_interp_y(A, pt1) - seg_interp_y(B, pt1);
+    double fb = seg_interp_y(A, pt2) - seg_interp_y(B, pt2);
+    bool diffsign = fa * fb < 0;
+    int cnt = 0;
+    if (!(neither && diffsign)) return 0;
+    int guard = 0;
+    while (true) {
+        if (++guard > 4 * nseg + 16) {
+            *status |= DCEGM_ST_LOOP_LIMIT;
+            break;
+        }
+        A = seg_view(S, X, V, ln1);
+        B = seg_view(S, X, V, ln2);
+        // root of A-B in [pt1,pt2]: both are linear inside one cell of the union grid (envelope.jl:199)
+        double f1 = seg_interp_y(A, pt1) - seg_interp_y(B, pt1);
+        double f2 = seg_interp_y(A, pt2) - seg_interp_y(B, pt2);
+        double pt3;
+        if (f1 == 0.0)
+            pt3 = pt1;
+        else if (f2 == 0.0)
+            pt3 = pt2;
+        else if (!(f1 * f2 < 0.0)) {
+            *status |= DCEGM_ST_NO_BRACKET;
+            break;
+        } else {
+            pt3 = pt1 - f1 * (pt2 - pt1) / (f2 - f1);
+            if (pt3 < pt1) pt3 = pt1;
+            if (pt3 > pt2) pt3 = pt2;
+        }
+        // all sections at pt3, extrap=false, first arg-max (envelope.jl:205-206)
+        int ln3 = -1;
+        double y3 = 0.0;
+        for (int s = 0; s < nseg; s++) {
+            SegView C = seg_view(S, X, V, s);
+            double y = seg_in_domain(C, pt3) ? seg_interp_y(C, pt3) : -CUDART_INF;
+            if (ln3 < 0 || y > y3) {
+                y3 = y;
+                ln3 = s;
+            }
+        }
+        if (ln3 == ln2 || ln3 == ln1) {
+            if (cnt < kSwitchMaxIsect) {
+                px[cnt] = pt3;
+                py[cnt] = y3;
+            } else
+                *status |= DCEGM_ST_ISECT_OVERFLOW;
+            cnt++;
+            if (ln2 == k1) break;
+            ln1 = ln2;
+            pt1 = pt3;
+            ln2 = k1;
+            pt2 = xr;
+        } else {
+            ln2 = ln3;
+            pt2 = pt3;
+        }
+    }
+    return cnt < kSwitchMaxIsect ? cnt : kSwitchMaxIsect;
+}
+
+// Full worker step after the EGM inversion.  On entry the na dirty points sit in
+// S.Dx/S.Dv/S.Dc[koff .. koff+na).  On exit (Vx,Vy,*nV) holds m.v[1,it].env and (Cx,Cy,*nC)
+// m.c[1,it].env, both with the prepended credit-constraint point; meta / isects / removed are
+// written to global memory.  All threads of the block must call this.
+__device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, double a0, double ev0, const DevModel& p,
+                                       double* Vx, double* Vy, int* nV, double* Cx, double* Cy, int* nC,
+                                       dcegm_env_meta* meta_out, double2* isects_out, uint32_t* removed_out,
+                                       int rem_words) {
+    const int tid = threadIdx.x;
+    unsigned status = 0;
+
+    // ---- bend-back guard (dc_algo.jl:394-418) ------------------------------------------------
+    double mn = CUDART_INF;
+    for (int k = tid; k < na; k += kThreads) mn = fmin(mn, S.Dx[koff + k]);
+    const double minx = block_min(mn, S.redd);
+    const double first = S.Dx[koff];
+    int npre = 0;
+    if (!(first <= minx)) {
+        npre = koff;  // floor(na/10) - 1 points
+        const int klen = na / 10;
+        for (int i = tid; i < npre; i += kThreads) {
+            double x0 = linrange_at(minx, first, klen, i);
+            double c0 = x0;
+            if (minx < 0) c0 = c0 + fabs(minx) + p.cfloor;
+            S.Dx[i] = x0;
+            S.Dc[i] = c0;
+            S.Dv[i] = u_work(c0, true, p) + p.beta * ev0;
+        }
+    }
+    const int s0 = koff - npre;
+    const double* X = S.Dx + s0;
+    const double* V = S.Dv + s0;
+    const double* Cc = S.Dc + s0;
+    const int n = na + npre;
+    if (tid == 0) {
+        S.cnt[0] = 0;
+        S.cnt[1] = 0;
+        S.cnt[2] = 0;
+    }
+    __syncthreads();
+
+    // ---- splitLine: direction changes (envelope.jl:84-110) -----------------------------------
+    for (int k = tid; k < n; k += kThreads) {
+        int isb = 0;
+        if (k >= 1 && k <= n - 2) isb = (X[k] > X[k - 1]) != (X[k + 1] > X[k]);
+        S.scan[k] = isb;
+        S.fknot[k] = (unsigned char)isb;
+    }
+    __syncthreads();
+    const int nb = block_scan_excl(S.scan, n, S.red);
+    int nseg = nb + 1;
+    const bool first_rising = X[1] > X[0];
+    bool plain = false;
+    if (nseg == 1) {
+        plain = true;
+        if (!first_rising) {
+            status |= DCEGM_ST_ALL_FALLING;
+            nseg = 0;
+        }
+    } else if (nseg > kSegCap) {
+        status |= DCEGM_ST_SEG_OVERFLOW;
+        plain = true;
+    }
+
+    int ne = 0, nis = 0, nrem = 0;
+    if (plain) {
+        for (int k = tid; k < n; k += kThreads) {
+            Vx[1 + k] = X[k];
+            Vy[1 + k] = V[k];
+            S.frem[k] = 0;
+        }
+        ne = n;
+    } else {
+        for (int k = tid; k < n; k += kThreads)
+            if (S.fknot[k]) S.segb[S.scan[k] + 1] = k;
+        if (tid == 0) {
+            S.segb[0] = 0;
+            S.segb[nseg] = n - 1;
+        }
+        __syncthreads();
+        for (int s = tid; s < nseg; s += kThreads) S.segrise[s] = X[S.segb[s] + 1] > X[S.segb[s]];
+        for (int k = tid; k < n; k += kThreads) S.order[k] = 0;
+        __syncthreads();
+
+        // ---- every point: sorted position, winning section, top Point (envelope.jl:154-164) ----
+        for (int k = tid; k < n; k += kThreads) {
+            const double xk = X[k];
+            int rank = 0, ties = 0, w = -1;
+            double best = -CUDART_INF, bestx = xk;
+            bool knot = false;
+            for (int s = 0; s < nseg; s++) {
+                SegView v = seg_view(S, X, V, s);
+                // #knots < xk
+                int lo = 0, len = v.len;
+                while (len > 0) {
+                    int half = len >> 1;
+                    bool lt = seg_x(v, lo + half) < xk;
+                    lo = lt ? lo + half + 1 : lo;
+                    len = lt ? len - half - 1 : half;
+                }
+                const int cnt = lo;
+                const bool eq = cnt < v.len && seg_x(v, cnt) == xk;
+                // each point is owned by one section: the shared boundary belongs to the earlier one
+                const int b0 = S.segb[s];
+                int own = cnt;
+                if (s > 0 && X[b0] < xk) own -= 1;
+                rank += own;
+                if (eq) {
+                    int i = v.base + v.st * cnt;
+                    if ((s == 0 || i != b0) && i < k) ties++;
+                }
+                if (!(xk < seg_x(v, 0) || xk > seg_x(v, v.len - 1))) {
+                    int i = cnt + (eq ? 1 : 0) - 1;
+                    i = i < 0 ? 0 : i;
+                    i = i > v.len - 2 ? v.len - 2 : i;
+                    const double xa = seg_x(v, i), xb = seg_x(v, i + 1);
+                    const double f = (xk - xa) / (xb - xa);
+                    const double yv = (1.0 - f) * seg_y(v, i) + f * seg_y(v, i + 1);
+                    if (yv > best) {  // linemax: first strictly larger wins (line.jl:280)
+                        best = yv;
+                        bestx = (1.0 - f) * xa + f * xb;
+                        w = s;
+                        knot = (xa == xk) || (xb == xk);
+                    }
+                }
+            }
+            if (w < 0) {
+                status |= DCEGM_ST_NONFINITE;
+                w = 0;
+            }
+            int ps = rank + ties;
+            ps = ps < n ? ps : n - 1;
+            S.pos[k] = (unsigned short)ps;
+            S.win[k] = (unsigned short)w;
+            S.Tx[k] = bestx;
+            S.Ty[k] = best;
+            S.fknot[k] = knot;
+        }
+        __syncthreads();
+        for (int k = tid; k < n; k += kThreads) S.order[S.pos[k]] = (unsigned short)k;
+        __syncthreads();
+        // unique(xx)
+        for (int q = tid; q < n; q += kThreads) {
+            int uq = (q == 0) || (X[S.order[q]] != X[S.order[q - 1]]);
+            S.fuq[q] = (unsigned char)uq;
+            S.scan[q] = uq;
+        }
+        __syncthreads();
+        const int nu = block_scan_excl(S.scan, n, S.red);
+        for (int q = tid; q < n; q += kThreads)
+            if (S.fuq[q]) S.ord2[S.scan[q]] = S.order[q];
+        for (int k = tid; k < n; k += kThreads) {
+            int q = S.pos[k];
+            S.pos[k] = (unsigned short)(S.fuq[q] ? S.scan[q] : S.scan[q] - 1);  // index into the unique grid
+        }
+        __syncthreads();
+
+        // ---- changes of winner (envelope.jl:173-243) ---------------------------------------------
+        for (int j = tid; j < nu; j += kThreads) {
+            S.cntI[j] = 0;
+            if (j >= 1 && S.win[S.ord2[j]] != S.win[S.ord2[j - 1]]) {
+                int slot = atomicAdd(&S.cnt[0], 1);
+                S.swj[slot] = (unsigned short)j;
+            }
+        }
+        __syncthreads();
+        const int nsw = S.cnt[0];
+        for (int t = tid; t < nsw; t += kThreads) {
+            const int j = S.swj[t];
+            double px[kSwitchMaxIsect], py[kSwitchMaxIsect];
+            int c = resolve_switch(S, X, V, nseg, S.win[S.ord2[j - 1]], S.win[S.ord2[j]], X[S.ord2[j - 1]], X[S.ord2[j]],
+                                   px, py, &status);
+            if (c > 0) {
+                int base = atomicAdd(&S.cnt[1], c);
+                for (int q = 0; q < c; q++) {
+                    if (base + q < S.isec_cap) {
+                        S.islx[base + q] = px[q];
+                        S.isly[base + q] = py[q];
+                        S.islkey[base + q] = j * kSwitchMaxIsect + q;
+                    }
+                }
+                S.cntI[j] = (unsigned char)c;
+            }
+        }
+        __syncthreads();
+        nis = S.cnt[1];
+        if (nis > S.isec_cap) {
+            status |= DCEGM_ST_ISECT_OVERFLOW;
+            nis = S.isec_cap;
+        }
+        // intersections in emission order (ascending cell, then order of discovery)
+        for (int t = tid; t < nis; t += kThreads) {
+            int key = S.islkey[t], r = 0;
+            for (int u = 0; u < nis; u++) r += S.islkey[u] < key;
+            S.isl2x[r] = S.islx[t];
+            S.isl2y[r] = S.isly[t];
+            S.isl2key[r] = key;
+        }
+        // ---- emission (envelope.jl:170, 212, 248-252) ----------------------------------------------
+        for (int j = tid; j < nu; j += kThreads) {
+            int k = S.ord2[j];
+            int reg = (j == 0) || S.fknot[k] || (j == nu - 1);
+            S.scan[j] = (j == 0 ? 0 : (int)S.cntI[j]) + reg;
+        }
+        __syncthreads();
+        ne = block_scan_excl(S.scan, nu, S.red);
+        const int room = S.cap - 1;
+        if (ne > room) status |= DCEGM_ST_LINE_OVERFLOW;
+        for (int j = tid; j < nu; j += kThreads) {
+            int k = S.ord2[j];
+            int reg = (j == 0) || S.fknot[k] || (j == nu - 1);
+            int at = S.scan[j] + (j == 0 ? 0 : (int)S.cntI[j]);
+            if (reg && at < room) {
+                Vx[1 + at] = S.Tx[k];
+                Vy[1 + at] = S.Ty[k];
+            }
+        }
+        for (int t = tid; t < nis; t += kThreads) {
+            int key = S.isl2key[t];
+            int at = S.scan[key / kSwitchMaxIsect] + key % kSwitchMaxIsect;
+            if (at < room) {
+                Vx[1 + at] = S.isl2x[t];
+                Vy[1 + at] = S.isl2y[t];
+            }
+        }
+        if (ne > room) ne = room;
+        // ---- removed! (envelope.jl:64-71): points with no exactly equal Point in the envelope ------
+        for (int k = tid; k < n; k += kThreads) {
+            int j = S.pos[k];
+            bool reg = (j == 0) || S.fknot[k] || (j == nu - 1);
+            bool kept = reg && S.Tx[k] == X[k] && S.Ty[k] == V[k];
+            for (int t = 0; t < nis && !kept; t++) kept = (S.isl2x[t] == X[k]) && (S.isl2y[t] == V[k]);
+            S.frem[k] = kept ? 0 : 1;
+        }
+        __syncthreads();
+    }
+    {
+        int local = 0;
+        for (int k = tid; k < n; k += kThreads) local += S.frem[k];
+        nrem = block_sum(local, S.red);
+    }
+    // removed bitmask -> global
+    for (int base = 0; base < rem_words * 32; base += kThreads) {
+        int k = base + tid;
+        unsigned bit = (k < n) ? S.frem[k] : 0;
+        unsigned word = __ballot_sync(0xffffffffu, bit);
+        if ((tid & 31) == 0 && k / 32 < rem_words) removed_out[k / 32] = word;
+    }
+    for (int t = tid; t < S.isec_cap; t += kThreads)
+        isects_out[t] = t < nis ? make_double2(S.isl2x[t], S.isl2y[t]) : make_double2(0.0, 0.0);
+
+    // ---- policy repair (dc_algo.jl:423-493) -----------------------------------------------------
+    int ncur;
+    if (nrem > 0) {
+        const int lane = tid & 31, wid = tid >> 5;
+        for (int t = wid; t < nis; t += kWarps) {
+            const double ix = S.isl2x[t];
+            int jl = -1, jr = 0x7fffffff;
+            for (int k = lane; k < n; k += 32) {
+                if (!S.frem[k]) {
+                    if (X[k] < ix) jl = max(jl, k);
+                    if (X[k] > ix) jr = min(jr, k);
+                }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                jl = max(jl, __shfl_xor_sync(0xffffffffu, jl, o));
+                jr = min(jr, __shfl_xor_sync(0xffffffffu, jr, o));
+            }
+            if (lane == 0) {
+                S.insLok[t] = 0;
+                S.insRok[t] = 0;
+                if (jl >= 0 && jl < n - 1) {  // dc_algo.jl:446-460
+                    double2 r = interp2pt(make_double2(X[jl], Cc[jl]), make_double2(X[jl + 1], Cc[jl + 1]), ix);
+                    S.insLx[t] = r.x - 1e3 * 2.220446049250313e-16;
+                    S.insLy[t] = r.y;
+                    S.insLok[t] = 1;
+                }
+                if (jr != 0x7fffffff) {  // dc_algo.jl:468-476
+                    if (jr == 0) {
+                        atomicOr(&S.cnt[2], (int)DCEGM_ST_INSERT_RANGE);
+                    } else {
+                        double2 r = interp2pt(make_double2(X[jr - 1], Cc[jr - 1]), make_double2(X[jr], Cc[jr]), ix);
+                        S.insRx[t] = r.x;
+                        S.insRy[t] = r.y;
+                        S.insRok[t] = 1;
+                    }
+                }
+            }
+        }
+        // deleteat!(cout, rmidx)  (dc_algo.jl:482)
+        for (int k = tid; k < n; k += kThreads) S.scan[k] = S.frem[k] ? 0 : 1;
+        __syncthreads();
+        // compact the two insertion lists (push! order)
+        if (tid == 0) {
+            int nl = 0, nr = 0;
+            for (int t = 0; t < nis; t++) {
+                if (S.insLok[t]) {
+                    S.insLx[nl] = S.insLx[t];
+                    S.insLy[nl] = S.insLy[t];
+                    nl++;
+                }
+                if (S.insRok[t]) {
+                    S.insRx[nr] = S.insRx[t];
+                    S.insRy[nr] = S.insRy[t];
+                    nr++;
+                }
+            }
+            S.cnt[0] = nl;
+            S.cnt[1] = nr;
+        }
+        ncur = block_scan_excl(S.scan, n, S.red);
+        for (int k = tid; k < n; k += kThreads)
+            if (!S.frem[k]) {
+                Cx[1 + S.scan[k]] = X[k];
+                Cy[1 + S.scan[k]] = Cc[k];
+            }
+        __syncthreads();
+        const int nl = S.cnt[0], nr = S.cnt[1];
+        if (nl != nr) status |= DCEGM_ST_MISALIGNED;
+        // insert!(…) pairs (dc_algo.jl:486-492)
+        for (int i = 0; i < nl; i++) {
+            const double lx = S.insLx[i];
+            int cand = 0x7fffffff;
+            for (int k = tid; k < ncur; k += kThreads)
+                if (Cx[1 + k] > lx) {
+                    cand = k;
+                    break;
+                }
+            const int j = block_min_int(cand, S.red);
+            if (j == 0x7fffffff || i >= nr) {
+                status |= DCEGM_ST_INSERT_RANGE;
+                break;
+            }
+            if (ncur + 2 > S.cap - 1) {
+                status |= DCEGM_ST_LINE_OVERFLOW;
+                break;
+            }
+            // shift [j, ncur) right by two, highest chunk first
+            for (int top = ncur - 1; top >= j; top -= kThreads) {
+                int k = top - tid;
+                double vx = 0, vy = 0;
+                if (k >= j) {
+                    vx = Cx[1 + k];
+                    vy = Cy[1 + k];
+                }
+                __syncthreads();
+                if (k >= j) {
+                    Cx[1 + k + 2] = vx;
+                    Cy[1 + k + 2] = vy;
+                }
+                __syncthreads();
+            }
+            if (tid == 0) {
+                Cx[1 + j] = lx;
+                Cy[1 + j] = S.insLy[i];
+                Cx[1 + j + 1] = S.insRx[i];
+                Cy[1 + j + 1] = S.insRy[i];
+            }
+            ncur += 2;
+            __syncthreads();
+        }
+    } else {
+        for (int k = tid; k < n; k += kThreads) {
+            Cx[1 + k] = X[k];
+            Cy[1 + k] = Cc[k];
+        }
+        ncur = n;
+    }
+
+    // ---- tail of the step (dc_algo.jl:94-101) ----------------------------------------------------
+    if (tid == 0) {
+        Vx[0] = a0;
+        Vy[0] = ev0;
+        Cx[0] = a0;
+        Cy[0] = 0.0;
+    }
+    __syncthreads();
+    const int lenV = ne + 1, lenC = ncur + 1;
+    // sortx!(c): stable sort on x.  The repaired policy is already ascending except in degenerate
+    // cases; detect, and only then rank-sort through the (now free) D arrays.
+    int bad = 0;
+    for (int k = tid; k + 1 < lenC; k += kThreads) bad |= Cx[k + 1] < Cx[k];
+    bad = block_sum(bad, S.red);
+    if (bad) {
+        for (int k = tid; k < lenC; k += kThreads) {
+            const double xk = Cx[k];
+            int r = 0;
+            for (int i = 0; i < lenC; i++) {
+                double xi = Cx[i];
+                r += (xi < xk) || (xi == xk && i < k);
+            }
+            S.Dx[r] = xk;
+            S.Dv[r] = Cy[k];
+        }
+        __syncthreads();
+        for (int k = tid; k < lenC; k += kThreads) {
+            Cx[k] = S.Dx[k];
+            Cy[k] = S.Dv[k];
+        }
+        __syncthreads();
+    }
+    // status: knot vectors the next period's interpolate() would reject, non-finite entries
+    int flag = 0;
+    for (int k = tid; k < lenC; k += kThreads) {
+        if (k + 1 < lenC && !(Cx[k + 1] > Cx[k])) flag |= DCEGM_ST_NONMONOTONE;
+        if (!isfinite(Cx[k]) || !isfinite(Cy[k])) flag |= DCEGM_ST_NONFINITE;
+    }
+    for (int k = tid; k < lenV; k += kThreads) {
+        if (k + 1 < lenV && !(Vx[k + 1] > Vx[k])) flag |= DCEGM_ST_NONMONOTONE;
+        if (!isfinite(Vx[k]) || !isfinite(Vy[k])) flag |= DCEGM_ST_NONFINITE;
+    }
+    if (flag || status) atomicOr(&S.cnt[2], flag | (int)status);
+    __syncthreads();
+    if (tid == 0) {
+        *nV = lenV;
+        *nC = lenC;
+        meta_out->n_segments = nseg;
+        meta_out->n_isects = nis;
+        meta_out->n_removed = nrem;
+        meta_out->n_prepended = npre;
+    }
+    __syncthreads();
+}
+
+}  // namespace dcegm

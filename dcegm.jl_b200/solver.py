@@ -1,0 +1,138 @@
+"""Solver — thin owner of one library handle (one per GPU), returning Solution views."""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi, _lib
+from .param import params_array
+from .solution import Solution
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+class Solver:
+    def __init__(self, device=0):
+        self.lib = _lib.load()
+        self.h = C.c_void_p()
+        rc = self.lib.dcegm_create(int(device), C.byref(self.h))
+        if rc == _abi.E_NODEVICE:
+            raise _lib.DcegmError(rc, "no CUDA device; libdcegm_cuda has no CPU path")
+        if rc != 0:
+            raise _lib.DcegmError(rc, "dcegm_create failed")
+        self.device = device
+
+    def close(self):
+        if self.h:
+            self.lib.dcegm_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise _lib.DcegmError(rc, self.lib.dcegm_last_error(self.h).decode())
+
+    # ---- solving -------------------------------------------------------------------------
+    def solve(self, model, params, keep_dirty=False, summary_only=False, fetch=True):
+        arr = params if isinstance(params, C.Array) else params_array(params)
+        flags = (_abi.KEEP_DIRTY if keep_dirty else 0) | (_abi.SUMMARY_ONLY if summary_only else 0)
+        fn = {_abi.MODEL_F: self.lib.dcegm_solve_f, _abi.MODEL_G: self.lib.dcegm_solve_g,
+              _abi.MODEL_MINIMAL: self.lib.dcegm_solve_minimal}[model]
+        self._ck(fn(self.h, arr, len(arr), flags))
+        return self.fetch() if fetch and not summary_only else None
+
+    def upload(self, model, params, keep_dirty=False, summary_only=False):
+        arr = params if isinstance(params, C.Array) else params_array(params)
+        flags = (_abi.KEEP_DIRTY if keep_dirty else 0) | (_abi.SUMMARY_ONLY if summary_only else 0)
+        fn = {_abi.MODEL_F: self.lib.dcegm_upload_f, _abi.MODEL_G: self.lib.dcegm_upload_g,
+              _abi.MODEL_MINIMAL: self.lib.dcegm_upload_minimal}[model]
+        self._ck(fn(self.h, arr, len(arr), flags))
+
+    def run(self):
+        self._ck(self.lib.dcegm_run(self.h))
+
+    def layout(self):
+        lay = _abi.dcegm_layout()
+        self._ck(self.lib.dcegm_get_layout(self.h, C.byref(lay)))
+        return lay
+
+    def timing(self):
+        t = _abi.dcegm_timing()
+        self._ck(self.lib.dcegm_last_timing(self.h, C.byref(t)))
+        return t
+
+    # ---- results ----------------------------------------------------------------------------
+    def fetch(self, first=0, count=None, into=None):
+        lay = self.layout()
+        count = lay.nmodels - first if count is None else count
+        sub = _abi.dcegm_layout()
+        C.memmove(C.byref(sub), C.byref(lay), C.sizeof(lay))
+        sub.nmodels = count
+        s = into if into is not None else Solution.allocate(sub, bool(lay.has_dirty))
+        if lay.has_lines:
+            self._ck(self.lib.dcegm_fetch_lines(self.h, first, count, _dp(s.lines)))
+        self._ck(self.lib.dcegm_fetch_lens(self.h, first, count, s.lens.ctypes.data_as(C.POINTER(C.c_int32))))
+        self._ck(self.lib.dcegm_fetch_vbound(self.h, first, count, _dp(s.vbound)))
+        self._ck(self.lib.dcegm_fetch_meta(self.h, first, count, s.meta.ctypes.data_as(C.c_void_p)))
+        self._ck(self.lib.dcegm_fetch_isects(self.h, first, count, _dp(s.isects)))
+        self._ck(self.lib.dcegm_fetch_removed(self.h, first, count, s.removed.ctypes.data_as(C.POINTER(C.c_uint32))))
+        if lay.has_dirty:
+            self._ck(self.lib.dcegm_fetch_dirty(self.h, first, count, _dp(s.dirty)))
+        st = np.zeros(lay.nmodels, np.int32)
+        self._ck(self.lib.dcegm_status(self.h, st.ctypes.data_as(C.POINTER(C.c_int32))))
+        s.status[:] = st[first:first + count]
+        return s
+
+    def fetch_line(self, model, kind, id, it, iy=0):
+        lay = self.layout()
+        buf = np.zeros((max(lay.cap, lay.na), 2))
+        n = C.c_int()
+        self._ck(self.lib.dcegm_fetch_line(self.h, model, kind, id, iy, it, _dp(buf), buf.shape[0], C.byref(n)))
+        return buf[: n.value, 0].copy(), buf[: n.value, 1].copy()
+
+    def fetch_packed(self, first=0, count=None):
+        lay = self.layout()
+        count = lay.nmodels - first if count is None else count
+        nsl = count * lay.nT * lay.nstate * 4
+        offsets = np.zeros(nsl + 1, np.int64)
+        npts = C.c_int64()
+        op = offsets.ctypes.data_as(C.POINTER(C.c_int64))
+        self._ck(self.lib.dcegm_fetch_packed(self.h, first, count, None, 0, op, C.byref(npts)))
+        xy = np.zeros((npts.value, 2))
+        self._ck(self.lib.dcegm_fetch_packed(self.h, first, count, _dp(xy), npts.value, op, C.byref(npts)))
+        return xy, offsets
+
+    def status(self):
+        lay = self.layout()
+        st = np.zeros(lay.nmodels, np.int32)
+        self._ck(self.lib.dcegm_status(self.h, st.ctypes.data_as(C.POINTER(C.c_int32))))
+        return st
+
+    def summaries(self):
+        lay = self.layout()
+        arr = (_abi.dcegm_summary * lay.nmodels)()
+        self._ck(self.lib.dcegm_summaries(self.h, arr))
+        return np.frombuffer(arr, dtype=SUMMARY_DTYPE).copy()
+
+    def summaries_to_device(self, ptr, nbytes):
+        self._ck(self.lib.dcegm_summaries_to_device(self.h, C.c_void_p(ptr), nbytes))
+
+
+SUMMARY_DTYPE = np.dtype([
+    ("status", np.int32), ("n_env_periods", np.int32), ("tot_segments", np.int32), ("tot_isects", np.int32),
+    ("tot_removed", np.int32), ("max_len", np.int32), ("tot_points", np.int64),
+    ("v1_probe", np.float64, (_abi.SUMMARY_NPROBE,)), ("c1_probe", np.float64, (_abi.SUMMARY_NPROBE,)),
+    ("checksum_c", np.float64), ("checksum_v", np.float64)])
+assert SUMMARY_DTYPE.itemsize == C.sizeof(_abi.dcegm_summary)
