@@ -1,14 +1,16 @@
 // device_common.cuh — shared-memory layout, polyline primitives and block-level helpers used by
 // the solver kernels.  FP64 throughout; compiled with -fmad=false so that every +,-,*,/ below is
-// a separately rounded IEEE operation in the order written (the CPU oracle is compiled with
-// -ffp-contract=off and uses the same order — decisions such as `x[k+1] > x[k]` or the arg-max
-// over segments then see the same bits given the same inputs).
+// a separately rounded IEEE operation in the order written, and pow/exp/log come from dc_math.h
+// (IEEE ops + fma only) instead of the CUDA math library.  The CPU oracle, compiled with
+// -ffp-contract=off, reproduces every kernel result bit for bit in its `portable` mode: decisions
+// such as `x[k+1] > x[k]` or the arg-max over segments see the same bits.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 #include "../../include/dcegm.h"
 #include "host_setup.hpp"
+#include "dc_math.h"
 
 namespace dcegm {
 
@@ -126,20 +128,20 @@ __device__ __forceinline__ double2 interp2pt(double2 a, double2 b, double q) {
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ double u_work(double x, bool working, const DevModel& p) {  // utils.jl:40-46
     double dis = working ? p.alpha : 0.0;
-    if (p.gamma_is_one) return log(x) - dis;
-    return p.oneover_oneminusgamma * (pow(x, p.oneminusgamma) - 1.0) - dis;
+    if (p.gamma_is_one) return dc_log(x) - dis;
+    return p.oneover_oneminusgamma * (dc_pow(x, p.oneminusgamma) - 1.0) - dis;
 }
 __device__ __forceinline__ double u_plain(double x, const DevModel& p) {  // utils.jl:23-29
-    if (p.gamma_is_one) return log(x);
-    return p.oneover_oneminusgamma * pow(x, p.oneminusgamma);
+    if (p.gamma_is_one) return dc_log(x);
+    return p.oneover_oneminusgamma * dc_pow(x, p.oneminusgamma);
 }
 __device__ __forceinline__ double up(double c, const DevModel& p) {  // utils.jl:72-78
     if (p.gamma_is_one) return 1.0 / c;
-    return pow(c, p.neg_gamma);
+    return dc_pow(c, p.neg_gamma);
 }
 __device__ __forceinline__ double iup(double u, const DevModel& p) {  // utils.jl:102-108
     if (p.gamma_is_one) return 1.0 / u;
-    return pow(u, p.neg_oneover_gamma);
+    return dc_pow(u, p.neg_oneover_gamma);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -224,26 +226,6 @@ __device__ inline int block_min_int(int v, int* red) {
     for (int w = 1; w < kWarps; w++) r = min(r, red[w]);
     __syncthreads();
     return r;
-}
-
-// Julia range(lo, stop=hi, length=n)[i] in double-double arithmetic: (lo*(n-1-i) + hi*i)/(n-1)
-__device__ inline double linrange_at(double lo, double hi, int n, int i) {
-    if (i == 0) return lo;
-    if (i == n - 1) return hi;
-    const double wa = (double)(n - 1 - i), wb = (double)i, d = (double)(n - 1);
-    // exact products
-    double p1 = __dmul_rn(lo, wa), e1 = __fma_rn(lo, wa, -p1);
-    double p2 = __dmul_rn(hi, wb), e2 = __fma_rn(hi, wb, -p2);
-    // two-sum
-    double s = __dadd_rn(p1, p2);
-    double bb = __dsub_rn(s, p1);
-    double es = __dadd_rn(__dsub_rn(p1, __dsub_rn(s, bb)), __dsub_rn(p2, bb));
-    double lo_part = __dadd_rn(__dadd_rn(e1, e2), es);
-    // (s + lo_part)/d
-    double q1 = __ddiv_rn(s, d);
-    double r = __dadd_rn(__fma_rn(-q1, d, s), lo_part);
-    double q2 = __ddiv_rn(r, d);
-    return __dadd_rn(q1, q2);
 }
 
 }  // namespace dcegm

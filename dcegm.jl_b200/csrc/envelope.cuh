@@ -178,7 +178,7 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
         npre = koff;  // floor(na/10) - 1 points
         const int klen = na / 10;
         for (int i = tid; i < npre; i += kThreads) {
-            double x0 = linrange_at(minx, first, klen, i);
+            double x0 = dc_linrange_at(minx, first, klen, i);
             double c0 = x0;
             if (minx < 0) c0 = c0 + fabs(minx) + p.cfloor;
             S.Dx[i] = x0;

@@ -252,11 +252,11 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
                     const bool w_hi = v1 > v2;
                     const double mx = w_hi ? v1 : v2;
                     const double d = ((w_hi ? v2 : v1) - mx) / p.lambda;
-                    const double e = d < -746.0 ? 0.0 : exp(d);  // exp underflows to +0 below -745.14
+                    const double e = dc_exp(d);  // exactly 0 below -745.2
                     const double e1 = w_hi ? 1.0 : e, e2 = w_hi ? e : 1.0;
                     const double s = e1 + e2;
                     pw = e1 / s;
-                    ls = mx + p.lambda * log(s);
+                    ls = mx + p.lambda * dc_log(s);
                     if (id == 1) pw = p.delta;  // dc_algo.jl:44
                 } else {
                     pw = p.delta;  // == 0
@@ -273,9 +273,10 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
                 else
                     mu = pw * up(c1, p) + (1.0 - pw) * up(c2, p);
                 const double w = wgt[iy];
-                acc_mu = acc_mu + w * mu;
-                acc_ls = acc_ls + w * ls;
-                acc_v2 = acc_v2 + w * v2;
+                // quadrature sums, ascending node order (dc_algo.jl:58,74)
+                acc_mu = iy == 0 ? w * mu : acc_mu + w * mu;
+                acc_ls = iy == 0 ? w * ls : acc_ls + w * ls;
+                acc_v2 = iy == 0 ? w * v2 : acc_v2 + w * v2;
             }
             const double rhs = scale * acc_mu;  // dc_algo.jl:50,58
             const double c0 = iup(rhs, p);      // dc_algo.jl:62

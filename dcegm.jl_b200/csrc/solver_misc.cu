@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(kThreads) solve_minimal_kernel(DeviceBatch B) 
                 const double w1 = ey[iy] + Ra;                 // minimal_EGM.jl:21
                 double c1 = interp_y(nx, nyv, nnext, w1);      // minimal_EGM.jl:25
                 if (c1 < 0) c1 = p.cfloor;                     // minimal_EGM.jl:26
-                acc = acc + wgt[iy] * (1.0 / c1);              // minimal_EGM.jl:27
+                acc = iy == 0 ? wgt[iy] * (1.0 / c1) : acc + wgt[iy] * (1.0 / c1);  // minimal_EGM.jl:27
             }
             const double rhs = p.betaR * acc;                  // minimal_EGM.jl:28
             const double c0 = 1.0 / rhs;                       // minimal_EGM.jl:29

@@ -24,6 +24,7 @@
 //
 // Build: see oracle/Makefile (g++ -O2 -ffp-contract=off -pthread).
 #include "../include/dcegm.h"
+#include "../dcegm.jl_b200/csrc/dc_math.h"  // shared reproducible math (portable mode only)
 
 #include <algorithm>
 #include <atomic>
@@ -43,11 +44,20 @@ typedef std::vector<Pt> Line;
 
 struct Par : dcegm_param {
     double neg_gamma, oneminusgamma, oneover_oneminusgamma, neg_oneover_gamma;
+    // 0: glibc libm (default; the mode pinned against the golden files)
+    // 1: the reproducible pow/exp/log of dcegm.jl_b200/csrc/dc_math.h, which the CUDA kernels use too.
+    //    In this mode GPU and oracle must agree bit for bit; the difference between the two modes
+    //    is the reference algorithm's own sensitivity to 1-ulp libm differences.
+    int portable;
 };
+inline double m_pow(double x, double y, int portable) { return portable ? dc_pow(x, y) : std::pow(x, y); }
+inline double m_exp(double x, int portable) { return portable ? dc_exp(x) : std::exp(x); }
+inline double m_log(double x, int portable) { return portable ? dc_log(x) : std::log(x); }
 
 // param.jl:90-93
-Par derive(const dcegm_param& p) {
+Par derive(const dcegm_param& p, int portable = 0) {
     Par q;
+    q.portable = portable;
     static_cast<dcegm_param&>(q) = p;
     q.neg_gamma = (-1.0) * p.gamma;
     q.oneminusgamma = 1.0 - p.gamma;
@@ -63,14 +73,14 @@ const double NEG_INF = -std::numeric_limits<double>::infinity();
 // ---------------------------------------------------------------------------------------
 // utils.jl:23-29
 double u_plain(double x, const Par& p) {
-    if (p.gamma == 1.0) return std::log(x);
-    return p.oneover_oneminusgamma * std::pow(x, p.oneminusgamma);
+    if (p.gamma == 1.0) return m_log(x, p.portable);
+    return p.oneover_oneminusgamma * m_pow(x, p.oneminusgamma, p.portable);
 }
 // utils.jl:40-46
 double u_work(double x, bool working, const Par& p) {
     double dis = working ? p.alpha : 0.0;
-    if (p.gamma == 1.0) return std::log(x) - dis;
-    return p.oneover_oneminusgamma * (std::pow(x, p.oneminusgamma) - 1.0) - dis;
+    if (p.gamma == 1.0) return m_log(x, p.portable) - dis;
+    return p.oneover_oneminusgamma * (m_pow(x, p.oneminusgamma, p.portable) - 1.0) - dis;
 }
 // utils.jl:6-9, 57-59
 double bequest(double b, const Par& p) { return p.nu * u_plain(b + p.bbar, p); }
@@ -80,12 +90,12 @@ double bequest_work(double b, bool working, const Par& p) {
 // utils.jl:72-78
 double up(double c, const Par& p) {
     if (p.gamma == 1.0) return 1.0 / c;
-    return std::pow(c, p.neg_gamma);
+    return m_pow(c, p.neg_gamma, p.portable);
 }
 // utils.jl:102-108
 double iup(double u, const Par& p) {
     if (p.gamma == 1.0) return 1.0 / u;
-    return std::pow(u, p.neg_oneover_gamma);
+    return m_pow(u, p.neg_oneover_gamma, p.portable);
 }
 // utils.jl:243-250
 double income(int it /*1-based*/, const Par& p, double shock) {
@@ -609,7 +619,11 @@ void do_secondary(Line& vline, Line& cline, bool working, double ev0, const Par&
         // dc_algo.jl:401-418
         int k = p.na / 10;
         std::vector<double> x0;
-        linrange(minx, vline[0].x, k, x0);
+        if (p.portable) {
+            for (int i = 0; i < k; i++) x0.push_back(dc_linrange_at(minx, vline[0].x, k, i));
+        } else {
+            linrange(minx, vline[0].x, k, x0);
+        }
         if (k > 0) x0.pop_back();
         std::vector<Pt> pv, pc;
         for (double x : x0) {
@@ -685,15 +699,15 @@ void do_secondary(Line& vline, Line& cline, bool working, double ev0, const Par&
 // ---------------------------------------------------------------------------------------
 // choice probabilities — dc_algo.jl:316-332 (two rows)
 // ---------------------------------------------------------------------------------------
-inline double ccp2(double v1, double v2, double lambda) {
+inline double ccp2(double v1, double v2, double lambda, int portable = 0) {
     double mx = v1 > v2 ? v1 : v2;  // maximum(x,dims=1)
-    double e1 = std::exp((v1 - mx) / lambda), e2 = std::exp((v2 - mx) / lambda);
+    double e1 = m_exp((v1 - mx) / lambda, portable), e2 = m_exp((v2 - mx) / lambda, portable);
     return e1 / (e1 + e2);
 }
-inline double logsum2(double v1, double v2, double lambda) {
+inline double logsum2(double v1, double v2, double lambda, int portable = 0) {
     double mx = v1 > v2 ? v1 : v2;
-    double e1 = std::exp((v1 - mx) / lambda), e2 = std::exp((v2 - mx) / lambda);
-    return mx + lambda * std::log(e1 + e2);
+    double e1 = m_exp((v1 - mx) / lambda, portable), e2 = m_exp((v2 - mx) / lambda, portable);
+    return mx + lambda * m_log(e1 + e2, portable);
 }
 
 // dc_algo.jl:220-251.  itn is the 1-based period of the value line v (it+1 of the caller).
@@ -818,8 +832,8 @@ void finish_step(Envelope& v, Envelope& c, double a0, double ev0, unsigned* stat
 // ---------------------------------------------------------------------------------------
 // FModel — param.jl:189-223 and dc_EGM!(::FModel) dc_algo.jl:8-105
 // ---------------------------------------------------------------------------------------
-void solve_f_one(const dcegm_param& pin, int m, const OutView& o, int literal) {
-    Par p = derive(pin);
+void solve_f_one(const dcegm_param& pin, int m, const OutView& o, int literal, int portable) {
+    Par p = derive(pin, portable);
     unsigned status = 0;
     const int na = p.na, ny = p.ny, nT = p.nT;
     const int G = p.quad_group > 0 ? p.quad_group : 1;
@@ -871,13 +885,13 @@ void solve_f_one(const dcegm_param& pin, int m, const OutView& o, int literal) {
                             c1[iid - 1] = cc;
                             v1[iid - 1] = vfun(iid, it + 1, cc, m1, *vn[iid - 1], p);
                         }
-                        double pwork = working ? ccp2(v1[0], v1[1], p.lambda) : p.delta;  // dc_algo.jl:44
+                        double pwork = working ? ccp2(v1[0], v1[1], p.lambda, p.portable) : p.delta;  // dc_algo.jl:44
                         if (beq) {                                                          // dc_algo.jl:46-48
                             c1[0] = c1[0] + p.bbar;
                             c1[1] = c1[1] + p.bbar;
                         }
                         mu[iy] = pwork * up(c1[0], p) + (1.0 - pwork) * up(c1[1], p);  // dc_algo.jl:49,53
-                        ls[iy] = logsum2(v1[0], v1[1], p.lambda);
+                        ls[iy] = logsum2(v1[0], v1[1], p.lambda, p.portable);
                         v2[iy] = v1[1];
                     }
                     double emu = quad_sum(ywgt.data(), mu.data(), ny, G);
@@ -922,8 +936,8 @@ void solve_f_one(const dcegm_param& pin, int m, const OutView& o, int literal) {
 // ---------------------------------------------------------------------------------------
 // GModel — param.jl:261-310 and dc_EGM!(::GModel) dc_algo.jl:112-206
 // ---------------------------------------------------------------------------------------
-void solve_g_one(const dcegm_param& pin, int m, const OutView& o, int literal) {
-    Par p = derive(pin);
+void solve_g_one(const dcegm_param& pin, int m, const OutView& o, int literal, int portable) {
+    Par p = derive(pin, portable);
     unsigned status = 0;
     const int na = p.na, ny = p.ny, nT = p.nT;
     std::vector<double> yvec, ywgt /* row-major [iy][jy] */, avec;
@@ -996,11 +1010,11 @@ void solve_g_one(const dcegm_param& pin, int m, const OutView& o, int literal) {
                     Line cline(na), vline(na);
                     double ev0 = 0;
                     for (int ia = 0; ia < na; ia++) {
-                        double pwork = working ? ccp2(vmat[0][ia], vmat[1][ia], p.lambda) : 0.0;
+                        double pwork = working ? ccp2(vmat[0][ia], vmat[1][ia], p.lambda, p.portable) : 0.0;
                         double mu1 = pwork * cmat[0][ia] + (1.0 - pwork) * cmat[1][ia];
                         double rhs = is_bequest ? (p.beta * p.R * p.nu) * mu1 : (p.beta * p.R) * mu1;
                         double c0 = iup(rhs, p);
-                        double ev = working ? logsum2(vmat[0][ia], vmat[1][ia], p.lambda) : vmat[1][ia];
+                        double ev = working ? logsum2(vmat[0][ia], vmat[1][ia], p.lambda, p.portable) : vmat[1][ia];
                         if (ia == 0) ev0 = ev;
                         cline[ia] = Pt{avec[ia] + c0, c0};
                         vline[ia] = Pt{avec[ia] + c0, u_work(c0, id == 1, p) + p.beta * ev};
@@ -1101,7 +1115,8 @@ void oracle_layout(int model, int nmodels, int na, int ny, int nT, int keep_dirt
 }
 
 // Solve a batch on `nthreads` host threads (std::thread).  Buffers follow include/dcegm.h.
-int oracle_solve(int model, const dcegm_param* params, int nmodels, int keep_dirty, int literal, int nthreads,
+int oracle_solve(int model, const dcegm_param* params, int nmodels, int keep_dirty, int literal, int portable,
+                 int nthreads,
                  double* lines, int32_t* lens, double* vbound, dcegm_env_meta* meta, double* isects,
                  uint32_t* removed, double* dirty, int32_t* status) {
     if (nmodels <= 0) return 0;
@@ -1124,9 +1139,9 @@ int oracle_solve(int model, const dcegm_param* params, int nmodels, int keep_dir
             int m = next.fetch_add(1);
             if (m >= nmodels) break;
             if (model == DCEGM_MODEL_F)
-                solve_f_one(params[m], m, o, literal);
+                solve_f_one(params[m], m, o, literal, portable);
             else if (model == DCEGM_MODEL_G)
-                solve_g_one(params[m], m, o, literal);
+                solve_g_one(params[m], m, o, literal, portable);
             else
                 solve_minimal_one(params[m], m, o);
         }
@@ -1251,9 +1266,26 @@ void oracle_linrange(double lo, double hi, int n, double* out) {
     linrange(lo, hi, n, g);
     std::copy(g.begin(), g.end(), out);
 }
+// the shared reproducible math, exported for accuracy tests against mpmath
+void oracle_dc_pow(const double* x, const double* y, int n, double* out) {
+    for (int i = 0; i < n; i++) out[i] = dc_pow(x[i], y[i]);
+}
+void oracle_dc_exp(const double* x, int n, double* out) {
+    for (int i = 0; i < n; i++) out[i] = dc_exp(x[i]);
+}
+void oracle_dc_log(const double* x, int n, double* out) {
+    for (int i = 0; i < n; i++) out[i] = dc_log(x[i]);
+}
+double oracle_dc_linrange_at(double lo, double hi, int n, int i) { return dc_linrange_at(lo, hi, n, i); }
 double oracle_u(double x, int working, const dcegm_param* p) { return u_work(x, working != 0, derive(*p)); }
 double oracle_up(double x, const dcegm_param* p) { return up(x, derive(*p)); }
 double oracle_iup(double x, const dcegm_param* p) { return iup(x, derive(*p)); }
 double oracle_income(int it, double shock, const dcegm_param* p) { return income(it, derive(*p), shock); }
 
 }  // extern "C"
+extern "C" void oracle_dc_log_parts(const double* x, int n, double* hi, double* lo) {
+    for (int i = 0; i < n; i++) dc_log_parts(x[i], &hi[i], &lo[i]);
+}
+extern "C" void oracle_dc_exp_parts(const double* h, const double* l, int n, double* out) {
+    for (int i = 0; i < n; i++) out[i] = dc_exp_parts(h[i], l[i]);
+}

@@ -21,7 +21,9 @@ def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
     src = os.path.join(_HERE, "dcegm_oracle.cpp")
     hdr = os.path.join(_HERE, "..", "include", "dcegm.h")
-    if force or not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(src), os.path.getmtime(hdr)):
+    mth = os.path.join(_HERE, "..", "dcegm.jl_b200", "csrc", "dc_math.h")
+    srcs = [f for f in (src, hdr, mth) if os.path.exists(f)]
+    if force or not os.path.exists(so) or (srcs and os.path.getmtime(so) < max(os.path.getmtime(f) for f in srcs)):
         subprocess.check_call(["make", "-C", _HERE, "-B" if force else "-s"], stdout=subprocess.DEVNULL)
     return so
 
@@ -56,14 +58,14 @@ def layout(model, nmodels, na, ny, nT, keep_dirty=False):
     return lay
 
 
-def solve(model, params, keep_dirty=False, literal=False, nthreads=1):
+def solve(model, params, keep_dirty=False, literal=False, nthreads=1, portable=False):
     """Solve a batch of Param on the host.  Returns a Solution in the layout of include/dcegm.h."""
     arr = params_array(params)
     n = len(params)
     lay = layout(model, n, arr[0].na, arr[0].ny, arr[0].nT, keep_dirty)
     s = Solution.allocate(lay, keep_dirty)
     rc = lib().oracle_solve(
-        C.c_int(model), arr, C.c_int(n), C.c_int(int(keep_dirty)), C.c_int(int(literal)), C.c_int(nthreads),
+        C.c_int(model), arr, C.c_int(n), C.c_int(int(keep_dirty)), C.c_int(int(literal)), C.c_int(int(portable)), C.c_int(nthreads),
         _p(s.lines), _p(s.lens, C.c_int32), _p(s.vbound), _p(s.meta, C.c_int32), _p(s.isects),
         _p(s.removed, C.c_uint32), _p(s.dirty), _p(s.status, C.c_int32))
     if rc != 0:
@@ -95,6 +97,28 @@ def secondary_envelope(x, y, literal=False):
     st = lib().oracle_secondary_envelope(_p(x), _p(y), n, int(literal), _p(env), cap, C.byref(ne), _p(isec), cap,
                                          C.byref(ni), _p(rem, C.c_int32), cap, C.byref(nr), C.byref(ns))
     return dict(env=env[: ne.value], isects=isec[: ni.value], removed=rem[: nr.value], n_segments=ns.value, status=st)
+
+
+def dc_pow(x, y):
+    x = np.ascontiguousarray(x, float)
+    y = np.ascontiguousarray(np.broadcast_to(y, x.shape), float)
+    out = np.zeros_like(x)
+    lib().oracle_dc_pow(_p(x), _p(y), x.size, _p(out))
+    return out
+
+
+def dc_exp(x):
+    x = np.ascontiguousarray(x, float)
+    out = np.zeros_like(x)
+    lib().oracle_dc_exp(_p(x), x.size, _p(out))
+    return out
+
+
+def dc_log(x):
+    x = np.ascontiguousarray(x, float)
+    out = np.zeros_like(x)
+    lib().oracle_dc_log(_p(x), x.size, _p(out))
+    return out
 
 
 def upper_env(lines, literal=False):

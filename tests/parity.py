@@ -40,3 +40,44 @@ def assert_parity(gpu, ref, rtol=RTOL):
     vb = np.abs(gpu.vbound - ref.vbound) / (ATOL / RTOL + np.abs(ref.vbound))
     assert vb.max() <= rtol
     return err
+
+
+def _stored_mask(sol):
+    k = np.arange(sol.lay.cap)
+    m = k[None, None, None, None, None, :] < sol.lens[..., None]
+    return np.broadcast_to(m[..., None], sol.lines.shape)
+
+
+def assert_bitwise(gpu, ref):
+    """GPU vs the oracle in portable-math mode: every stored number identical (NaN == NaN)."""
+    assert_same_structure(gpu, ref)
+    m = _stored_mask(ref)
+    a, b = gpu.lines[m], ref.lines[m]
+    same = (a == b) | (np.isnan(a) & np.isnan(b))
+    assert same.all(), f"{(~same).sum()} of {same.size} stored ordinates differ; max abs diff {np.nanmax(np.abs(a - b)):.3e}"
+    assert np.array_equal(gpu.isects, ref.isects)
+    assert np.array_equal(gpu.vbound, ref.vbound)
+    if ref.dirty is not None and gpu.dirty is not None:
+        assert np.array_equal(gpu.dirty, ref.dirty)
+
+
+def libm_sensitivity(a, b):
+    """Relative deviations between two solutions that differ only in the libm used (1-ulp level
+    differences in pow/exp/log).  Returns (share of ordinates within RTOL, max rel. deviation of policy
+    kink insertions, max rel. deviation elsewhere).  Requires equal structure."""
+    m = _stored_mask(a)
+    rel = np.abs(a.lines - b.lines) / (ATOL / RTOL + np.abs(b.lines))
+    rel = np.where(m, np.nan_to_num(rel, nan=0.0), 0.0)
+    # kink insertions: policy points (kind 0, worker id 0) whose x lies within 1e-9 of an intersection
+    kink = np.zeros(a.lines.shape[:-1], bool)
+    ni = a.meta[..., 1]
+    for (mm, it, iy) in np.argwhere(ni > 0):
+        xs = a.isects[mm, it, iy, : ni[mm, it, iy], 0]
+        cx = a.lines[mm, it, iy, 0, 0, :, 0]
+        near = np.abs(cx[:, None] - xs[None, :]) <= 1e-9 * np.maximum(1.0, np.abs(xs[None, :]))
+        kink[mm, it, iy, 0, 0] = near.any(axis=1)
+    kink = np.broadcast_to(kink[..., None], rel.shape)
+    share = float((rel[m] <= RTOL).mean())
+    worst_kink = float(rel[kink & m].max()) if (kink & m).any() else 0.0
+    worst_rest = float(rel[~kink & m].max())
+    return share, worst_kink, worst_rest
