@@ -20,7 +20,7 @@ cudaError_t launch_solve_minimal(const DeviceBatch& B, cudaStream_t stream);
 cudaError_t launch_pack_lines(const DeviceBatch& B, int first, int count, const long long* d_offsets, double2* d_dst,
                               cudaStream_t stream);
 size_t solver_f_smem_bytes(int cap, int isec_cap);
-size_t solver_g_smem_bytes(int cap, int isec_cap, int na);
+size_t solver_g_smem_bytes(int cap, int isec_cap, int na, int ny);
 }  // namespace dcegm
 
 using namespace dcegm;
@@ -86,7 +86,7 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
     make_layout(model, nmodels, na, ny, nT, (flags & DCEGM_KEEP_DIRTY) ? 1 : 0, (flags & DCEGM_SUMMARY_ONLY) ? 0 : 1, &lay);
     if (lay.cap > 65535) return fail(h, DCEGM_E_INVALID, "na too large for the shared-memory resident solver");
     size_t smem = model == DCEGM_MODEL_F   ? solver_f_smem_bytes(lay.cap, lay.isec_cap)
-                  : model == DCEGM_MODEL_G ? solver_g_smem_bytes(lay.cap, lay.isec_cap, na)
+                  : model == DCEGM_MODEL_G ? solver_g_smem_bytes(lay.cap, lay.isec_cap, na, ny)
                                            : (size_t)(4 * (na + 1) * 8 + 1024);
     if ((long long)smem > (long long)h->max_smem_optin) {
         char msg[256];

@@ -19,24 +19,49 @@
 
 namespace dcegm {
 
+// All scratch of the envelope lives in the kernel's dynamic shared memory and is addressed as
+// integer offsets from the one `extern __shared__` symbol, so every access compiles to LDS/STS
+// (pointer tables in registers or local memory made the compiler fall back to generic LD/ST).
+extern __shared__ __align__(16) unsigned char dc_smem[];
+
 struct EnvScratch {
-    // extended dirty worker line (EGM order): x, value, policy.  The EGM step writes the na
-    // points at offset `koff` = max(na/10-1,0); bend-back points are prepended in front.
-    double *Dx, *Dv, *Dc;
-    double *Tx, *Ty;  // per point: interpolated top Point of the winning section at this x
-    unsigned short *pos, *order, *ord2, *win, *swj;
-    unsigned char *fknot, *fuq, *frem, *cntI;
-    int* scan;
-    int* segb;               // kSegCap+1 boundaries (point indices)
-    unsigned char* segrise;  // kSegCap
-    double *islx, *isly, *isl2x, *isl2y;  // intersections (unsorted / sorted by emission order)
-    int *islkey, *isl2key;
-    double *insLx, *insLy, *insRx, *insRy;  // policy points to insert (dc_algo.jl:434-479)
-    unsigned char *insLok, *insRok;
-    int* red;     // kWarps+1 (+ a few counters)
-    double* redd; // kWarps
-    int* cnt;     // [0] nsw, [1] nis, [2] status bits, [3] tmp
+    int off;  // byte offset of the region inside dc_smem
     int cap, isec_cap;
+    // region layout: 5 double[cap] | 12 double[isec_cap] | redd[kWarps] | scan int[cap] | segb int[kSegCap+1]
+    //                | 2 int[isec_cap] | red int[kWarps+1] | cnt int[8] | 5 u16[cap] | 4 u8[cap] | segrise u8[kSegCap]
+    //                | 2 u8[isec_cap]
+    __host__ __device__ static int align16(int b) { return (b + 15) / 16 * 16; }
+    __host__ __device__ int o_d(int j) const { return off + j * align16(cap * 8); }
+    __host__ __device__ int o_i(int j) const { return o_d(5) + j * align16(isec_cap * 8); }
+    __host__ __device__ int o_redd() const { return o_i(12); }
+    __host__ __device__ int o_scan() const { return o_redd() + align16(kWarps * 8); }
+    __host__ __device__ int o_segb() const { return o_scan() + align16(cap * 4); }
+    __host__ __device__ int o_key(int j) const { return o_segb() + align16((kSegCap + 1) * 4) + j * align16(isec_cap * 4); }
+    __host__ __device__ int o_red() const { return o_key(2); }
+    __host__ __device__ int o_cnt() const { return o_red() + align16((kWarps + 1) * 4); }
+    __host__ __device__ int o_u16(int j) const { return o_cnt() + 32 + j * align16(cap * 2); }
+    __host__ __device__ int o_u8(int j) const { return o_u16(5) + j * align16(cap); }
+    __host__ __device__ int o_segrise() const { return o_u8(4); }
+    __host__ __device__ int o_ok(int j) const { return o_segrise() + align16(kSegCap) + j * align16(isec_cap); }
+    __host__ __device__ int bytes() const { return o_ok(2) - off; }
+#define DC_ARR(T, name, expr) \
+    __device__ __forceinline__ T* name() const { return reinterpret_cast<T*>(dc_smem + (expr)); }
+    // extended dirty worker line (EGM order): x, value, policy.  The EGM step writes the na points at
+    // offset `koff` = max(na/10-1,0); bend-back points are prepended in front.
+    DC_ARR(double, Dx, o_d(0)) DC_ARR(double, Dv, o_d(1)) DC_ARR(double, Dc, o_d(2))
+    // per point: interpolated top Point of the winning section at this x
+    DC_ARR(double, Tx, o_d(3)) DC_ARR(double, Ty, o_d(4))
+    // intersections (unsorted / sorted by emission order), policy points to insert (dc_algo.jl:434-479)
+    DC_ARR(double, islx, o_i(0)) DC_ARR(double, isly, o_i(1)) DC_ARR(double, isl2x, o_i(2)) DC_ARR(double, isl2y, o_i(3))
+    DC_ARR(double, insLx, o_i(4)) DC_ARR(double, insLy, o_i(5)) DC_ARR(double, insRx, o_i(6)) DC_ARR(double, insRy, o_i(7))
+    DC_ARR(double, redd, o_redd())
+    DC_ARR(int, scan, o_scan()) DC_ARR(int, segb, o_segb()) DC_ARR(int, islkey, o_key(0)) DC_ARR(int, isl2key, o_key(1))
+    DC_ARR(int, red, o_red()) DC_ARR(int, cnt, o_cnt())  // cnt: [0] nsw/nl, [1] nis/nr, [2] status bits
+    DC_ARR(unsigned short, pos, o_u16(0)) DC_ARR(unsigned short, order, o_u16(1)) DC_ARR(unsigned short, ord2, o_u16(2))
+    DC_ARR(unsigned short, win, o_u16(3)) DC_ARR(unsigned short, swj, o_u16(4))
+    DC_ARR(unsigned char, fknot, o_u8(0)) DC_ARR(unsigned char, fuq, o_u8(1)) DC_ARR(unsigned char, frem, o_u8(2))
+    DC_ARR(unsigned char, cntI, o_u8(3)) DC_ARR(unsigned char, segrise, o_segrise())
+    DC_ARR(unsigned char, insLok, o_ok(0)) DC_ARR(unsigned char, insRok, o_ok(1))
 };
 
 struct SegView {
@@ -46,8 +71,8 @@ struct SegView {
 };
 __device__ __forceinline__ SegView seg_view(const EnvScratch& S, const double* X, const double* Y, int s) {
     SegView v;
-    int b0 = S.segb[s], b1 = S.segb[s + 1];
-    bool rise = S.segrise[s];
+    int b0 = S.segb()[s], b1 = S.segb()[s + 1];
+    bool rise = S.segrise()[s];
     v.X = X;
     v.Y = Y;
     v.base = rise ? b0 : b1;
@@ -158,7 +183,7 @@ __device__ inline int resolve_switch(const EnvScratch& S, const double* X, const
 }
 
 // Full worker step after the EGM inversion.  On entry the na dirty points sit in
-// S.Dx/S.Dv/S.Dc[koff .. koff+na).  On exit (Vx,Vy,*nV) holds m.v[1,it].env and (Cx,Cy,*nC)
+// S.Dx()/S.Dv()/S.Dc()[koff .. koff+na).  On exit (Vx,Vy,*nV) holds m.v[1,it].env and (Cx,Cy,*nC)
 // m.c[1,it].env, both with the prepended credit-constraint point; meta / isects / removed are
 // written to global memory.  All threads of the block must call this.
 __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, double a0, double ev0, const DevModel& p,
@@ -170,9 +195,9 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
 
     // ---- bend-back guard (dc_algo.jl:394-418) ------------------------------------------------
     double mn = CUDART_INF;
-    for (int k = tid; k < na; k += kThreads) mn = fmin(mn, S.Dx[koff + k]);
-    const double minx = block_min(mn, S.redd);
-    const double first = S.Dx[koff];
+    for (int k = tid; k < na; k += kThreads) mn = fmin(mn, S.Dx()[koff + k]);
+    const double minx = block_min(mn, S.redd());
+    const double first = S.Dx()[koff];
     int npre = 0;
     if (!(first <= minx)) {
         npre = koff;  // floor(na/10) - 1 points
@@ -181,20 +206,20 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
             double x0 = dc_linrange_at(minx, first, klen, i);
             double c0 = x0;
             if (minx < 0) c0 = c0 + fabs(minx) + p.cfloor;
-            S.Dx[i] = x0;
-            S.Dc[i] = c0;
-            S.Dv[i] = u_work(c0, true, p) + p.beta * ev0;
+            S.Dx()[i] = x0;
+            S.Dc()[i] = c0;
+            S.Dv()[i] = u_work(c0, true, p) + p.beta * ev0;
         }
     }
     const int s0 = koff - npre;
-    const double* X = S.Dx + s0;
-    const double* V = S.Dv + s0;
-    const double* Cc = S.Dc + s0;
+    const double* X = S.Dx() + s0;
+    const double* V = S.Dv() + s0;
+    const double* Cc = S.Dc() + s0;
     const int n = na + npre;
     if (tid == 0) {
-        S.cnt[0] = 0;
-        S.cnt[1] = 0;
-        S.cnt[2] = 0;
+        S.cnt()[0] = 0;
+        S.cnt()[1] = 0;
+        S.cnt()[2] = 0;
     }
     __syncthreads();
 
@@ -202,11 +227,11 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
     for (int k = tid; k < n; k += kThreads) {
         int isb = 0;
         if (k >= 1 && k <= n - 2) isb = (X[k] > X[k - 1]) != (X[k + 1] > X[k]);
-        S.scan[k] = isb;
-        S.fknot[k] = (unsigned char)isb;
+        S.scan()[k] = isb;
+        S.fknot()[k] = (unsigned char)isb;
     }
     __syncthreads();
-    const int nb = block_scan_excl(S.scan, n, S.red);
+    const int nb = block_scan_excl(S.scan(), n, S.red());
     int nseg = nb + 1;
     const bool first_rising = X[1] > X[0];
     bool plain = false;
@@ -226,19 +251,19 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
         for (int k = tid; k < n; k += kThreads) {
             Vx[1 + k] = X[k];
             Vy[1 + k] = V[k];
-            S.frem[k] = 0;
+            S.frem()[k] = 0;
         }
         ne = n;
     } else {
         for (int k = tid; k < n; k += kThreads)
-            if (S.fknot[k]) S.segb[S.scan[k] + 1] = k;
+            if (S.fknot()[k]) S.segb()[S.scan()[k] + 1] = k;
         if (tid == 0) {
-            S.segb[0] = 0;
-            S.segb[nseg] = n - 1;
+            S.segb()[0] = 0;
+            S.segb()[nseg] = n - 1;
         }
         __syncthreads();
-        for (int s = tid; s < nseg; s += kThreads) S.segrise[s] = X[S.segb[s] + 1] > X[S.segb[s]];
-        for (int k = tid; k < n; k += kThreads) S.order[k] = 0;
+        for (int s = tid; s < nseg; s += kThreads) S.segrise()[s] = X[S.segb()[s] + 1] > X[S.segb()[s]];
+        for (int k = tid; k < n; k += kThreads) S.order()[k] = 0;
         __syncthreads();
 
         // ---- every point: sorted position, winning section, top Point (envelope.jl:154-164) ----
@@ -260,7 +285,7 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
                 const int cnt = lo;
                 const bool eq = cnt < v.len && seg_x(v, cnt) == xk;
                 // each point is owned by one section: the shared boundary belongs to the earlier one
-                const int b0 = S.segb[s];
+                const int b0 = S.segb()[s];
                 int own = cnt;
                 if (s > 0 && X[b0] < xk) own -= 1;
                 rank += own;
@@ -289,134 +314,134 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
             }
             int ps = rank + ties;
             ps = ps < n ? ps : n - 1;
-            S.pos[k] = (unsigned short)ps;
-            S.win[k] = (unsigned short)w;
-            S.Tx[k] = bestx;
-            S.Ty[k] = best;
-            S.fknot[k] = knot;
+            S.pos()[k] = (unsigned short)ps;
+            S.win()[k] = (unsigned short)w;
+            S.Tx()[k] = bestx;
+            S.Ty()[k] = best;
+            S.fknot()[k] = knot;
         }
         __syncthreads();
-        for (int k = tid; k < n; k += kThreads) S.order[S.pos[k]] = (unsigned short)k;
+        for (int k = tid; k < n; k += kThreads) S.order()[S.pos()[k]] = (unsigned short)k;
         __syncthreads();
         // unique(xx)
         for (int q = tid; q < n; q += kThreads) {
-            int uq = (q == 0) || (X[S.order[q]] != X[S.order[q - 1]]);
-            S.fuq[q] = (unsigned char)uq;
-            S.scan[q] = uq;
+            int uq = (q == 0) || (X[S.order()[q]] != X[S.order()[q - 1]]);
+            S.fuq()[q] = (unsigned char)uq;
+            S.scan()[q] = uq;
         }
         __syncthreads();
-        const int nu = block_scan_excl(S.scan, n, S.red);
+        const int nu = block_scan_excl(S.scan(), n, S.red());
         for (int q = tid; q < n; q += kThreads)
-            if (S.fuq[q]) S.ord2[S.scan[q]] = S.order[q];
+            if (S.fuq()[q]) S.ord2()[S.scan()[q]] = S.order()[q];
         for (int k = tid; k < n; k += kThreads) {
-            int q = S.pos[k];
-            S.pos[k] = (unsigned short)(S.fuq[q] ? S.scan[q] : S.scan[q] - 1);  // index into the unique grid
+            int q = S.pos()[k];
+            S.pos()[k] = (unsigned short)(S.fuq()[q] ? S.scan()[q] : S.scan()[q] - 1);  // index into the unique grid
         }
         __syncthreads();
 
         // ---- changes of winner (envelope.jl:173-243) ---------------------------------------------
         for (int j = tid; j < nu; j += kThreads) {
-            S.cntI[j] = 0;
-            if (j >= 1 && S.win[S.ord2[j]] != S.win[S.ord2[j - 1]]) {
-                int slot = atomicAdd(&S.cnt[0], 1);
-                S.swj[slot] = (unsigned short)j;
+            S.cntI()[j] = 0;
+            if (j >= 1 && S.win()[S.ord2()[j]] != S.win()[S.ord2()[j - 1]]) {
+                int slot = atomicAdd(&S.cnt()[0], 1);
+                S.swj()[slot] = (unsigned short)j;
             }
         }
         __syncthreads();
-        const int nsw = S.cnt[0];
+        const int nsw = S.cnt()[0];
         for (int t = tid; t < nsw; t += kThreads) {
-            const int j = S.swj[t];
+            const int j = S.swj()[t];
             double px[kSwitchMaxIsect], py[kSwitchMaxIsect];
-            int c = resolve_switch(S, X, V, nseg, S.win[S.ord2[j - 1]], S.win[S.ord2[j]], X[S.ord2[j - 1]], X[S.ord2[j]],
+            int c = resolve_switch(S, X, V, nseg, S.win()[S.ord2()[j - 1]], S.win()[S.ord2()[j]], X[S.ord2()[j - 1]], X[S.ord2()[j]],
                                    px, py, &status);
             if (c > 0) {
-                int base = atomicAdd(&S.cnt[1], c);
+                int base = atomicAdd(&S.cnt()[1], c);
                 for (int q = 0; q < c; q++) {
                     if (base + q < S.isec_cap) {
-                        S.islx[base + q] = px[q];
-                        S.isly[base + q] = py[q];
-                        S.islkey[base + q] = j * kSwitchMaxIsect + q;
+                        S.islx()[base + q] = px[q];
+                        S.isly()[base + q] = py[q];
+                        S.islkey()[base + q] = j * kSwitchMaxIsect + q;
                     }
                 }
-                S.cntI[j] = (unsigned char)c;
+                S.cntI()[j] = (unsigned char)c;
             }
         }
         __syncthreads();
-        nis = S.cnt[1];
+        nis = S.cnt()[1];
         if (nis > S.isec_cap) {
             status |= DCEGM_ST_ISECT_OVERFLOW;
             nis = S.isec_cap;
         }
         // intersections in emission order (ascending cell, then order of discovery)
         for (int t = tid; t < nis; t += kThreads) {
-            int key = S.islkey[t], r = 0;
-            for (int u = 0; u < nis; u++) r += S.islkey[u] < key;
-            S.isl2x[r] = S.islx[t];
-            S.isl2y[r] = S.isly[t];
-            S.isl2key[r] = key;
+            int key = S.islkey()[t], r = 0;
+            for (int u = 0; u < nis; u++) r += S.islkey()[u] < key;
+            S.isl2x()[r] = S.islx()[t];
+            S.isl2y()[r] = S.isly()[t];
+            S.isl2key()[r] = key;
         }
         // ---- emission (envelope.jl:170, 212, 248-252) ----------------------------------------------
         for (int j = tid; j < nu; j += kThreads) {
-            int k = S.ord2[j];
-            int reg = (j == 0) || S.fknot[k] || (j == nu - 1);
-            S.scan[j] = (j == 0 ? 0 : (int)S.cntI[j]) + reg;
+            int k = S.ord2()[j];
+            int reg = (j == 0) || S.fknot()[k] || (j == nu - 1);
+            S.scan()[j] = (j == 0 ? 0 : (int)S.cntI()[j]) + reg;
         }
         __syncthreads();
-        ne = block_scan_excl(S.scan, nu, S.red);
+        ne = block_scan_excl(S.scan(), nu, S.red());
         const int room = S.cap - 1;
         if (ne > room) status |= DCEGM_ST_LINE_OVERFLOW;
         for (int j = tid; j < nu; j += kThreads) {
-            int k = S.ord2[j];
-            int reg = (j == 0) || S.fknot[k] || (j == nu - 1);
-            int at = S.scan[j] + (j == 0 ? 0 : (int)S.cntI[j]);
+            int k = S.ord2()[j];
+            int reg = (j == 0) || S.fknot()[k] || (j == nu - 1);
+            int at = S.scan()[j] + (j == 0 ? 0 : (int)S.cntI()[j]);
             if (reg && at < room) {
-                Vx[1 + at] = S.Tx[k];
-                Vy[1 + at] = S.Ty[k];
+                Vx[1 + at] = S.Tx()[k];
+                Vy[1 + at] = S.Ty()[k];
             }
         }
         for (int t = tid; t < nis; t += kThreads) {
-            int key = S.isl2key[t];
-            int at = S.scan[key / kSwitchMaxIsect] + key % kSwitchMaxIsect;
+            int key = S.isl2key()[t];
+            int at = S.scan()[key / kSwitchMaxIsect] + key % kSwitchMaxIsect;
             if (at < room) {
-                Vx[1 + at] = S.isl2x[t];
-                Vy[1 + at] = S.isl2y[t];
+                Vx[1 + at] = S.isl2x()[t];
+                Vy[1 + at] = S.isl2y()[t];
             }
         }
         if (ne > room) ne = room;
         // ---- removed! (envelope.jl:64-71): points with no exactly equal Point in the envelope ------
         for (int k = tid; k < n; k += kThreads) {
-            int j = S.pos[k];
-            bool reg = (j == 0) || S.fknot[k] || (j == nu - 1);
-            bool kept = reg && S.Tx[k] == X[k] && S.Ty[k] == V[k];
-            for (int t = 0; t < nis && !kept; t++) kept = (S.isl2x[t] == X[k]) && (S.isl2y[t] == V[k]);
-            S.frem[k] = kept ? 0 : 1;
+            int j = S.pos()[k];
+            bool reg = (j == 0) || S.fknot()[k] || (j == nu - 1);
+            bool kept = reg && S.Tx()[k] == X[k] && S.Ty()[k] == V[k];
+            for (int t = 0; t < nis && !kept; t++) kept = (S.isl2x()[t] == X[k]) && (S.isl2y()[t] == V[k]);
+            S.frem()[k] = kept ? 0 : 1;
         }
         __syncthreads();
     }
     {
         int local = 0;
-        for (int k = tid; k < n; k += kThreads) local += S.frem[k];
-        nrem = block_sum(local, S.red);
+        for (int k = tid; k < n; k += kThreads) local += S.frem()[k];
+        nrem = block_sum(local, S.red());
     }
     // removed bitmask -> global
     for (int base = 0; base < rem_words * 32; base += kThreads) {
         int k = base + tid;
-        unsigned bit = (k < n) ? S.frem[k] : 0;
+        unsigned bit = (k < n) ? S.frem()[k] : 0;
         unsigned word = __ballot_sync(0xffffffffu, bit);
         if ((tid & 31) == 0 && k / 32 < rem_words) removed_out[k / 32] = word;
     }
     for (int t = tid; t < S.isec_cap; t += kThreads)
-        isects_out[t] = t < nis ? make_double2(S.isl2x[t], S.isl2y[t]) : make_double2(0.0, 0.0);
+        isects_out[t] = t < nis ? make_double2(S.isl2x()[t], S.isl2y()[t]) : make_double2(0.0, 0.0);
 
     // ---- policy repair (dc_algo.jl:423-493) -----------------------------------------------------
     int ncur;
     if (nrem > 0) {
         const int lane = tid & 31, wid = tid >> 5;
         for (int t = wid; t < nis; t += kWarps) {
-            const double ix = S.isl2x[t];
+            const double ix = S.isl2x()[t];
             int jl = -1, jr = 0x7fffffff;
             for (int k = lane; k < n; k += 32) {
-                if (!S.frem[k]) {
+                if (!S.frem()[k]) {
                     if (X[k] < ix) jl = max(jl, k);
                     if (X[k] > ix) jr = min(jr, k);
                 }
@@ -427,66 +452,66 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
                 jr = min(jr, __shfl_xor_sync(0xffffffffu, jr, o));
             }
             if (lane == 0) {
-                S.insLok[t] = 0;
-                S.insRok[t] = 0;
+                S.insLok()[t] = 0;
+                S.insRok()[t] = 0;
                 if (jl >= 0 && jl < n - 1) {  // dc_algo.jl:446-460
                     double2 r = interp2pt(make_double2(X[jl], Cc[jl]), make_double2(X[jl + 1], Cc[jl + 1]), ix);
-                    S.insLx[t] = r.x - 1e3 * 2.220446049250313e-16;
-                    S.insLy[t] = r.y;
-                    S.insLok[t] = 1;
+                    S.insLx()[t] = r.x - 1e3 * 2.220446049250313e-16;
+                    S.insLy()[t] = r.y;
+                    S.insLok()[t] = 1;
                 }
                 if (jr != 0x7fffffff) {  // dc_algo.jl:468-476
                     if (jr == 0) {
-                        atomicOr(&S.cnt[2], (int)DCEGM_ST_INSERT_RANGE);
+                        atomicOr(&S.cnt()[2], (int)DCEGM_ST_INSERT_RANGE);
                     } else {
                         double2 r = interp2pt(make_double2(X[jr - 1], Cc[jr - 1]), make_double2(X[jr], Cc[jr]), ix);
-                        S.insRx[t] = r.x;
-                        S.insRy[t] = r.y;
-                        S.insRok[t] = 1;
+                        S.insRx()[t] = r.x;
+                        S.insRy()[t] = r.y;
+                        S.insRok()[t] = 1;
                     }
                 }
             }
         }
         // deleteat!(cout, rmidx)  (dc_algo.jl:482)
-        for (int k = tid; k < n; k += kThreads) S.scan[k] = S.frem[k] ? 0 : 1;
+        for (int k = tid; k < n; k += kThreads) S.scan()[k] = S.frem()[k] ? 0 : 1;
         __syncthreads();
         // compact the two insertion lists (push! order)
         if (tid == 0) {
             int nl = 0, nr = 0;
             for (int t = 0; t < nis; t++) {
-                if (S.insLok[t]) {
-                    S.insLx[nl] = S.insLx[t];
-                    S.insLy[nl] = S.insLy[t];
+                if (S.insLok()[t]) {
+                    S.insLx()[nl] = S.insLx()[t];
+                    S.insLy()[nl] = S.insLy()[t];
                     nl++;
                 }
-                if (S.insRok[t]) {
-                    S.insRx[nr] = S.insRx[t];
-                    S.insRy[nr] = S.insRy[t];
+                if (S.insRok()[t]) {
+                    S.insRx()[nr] = S.insRx()[t];
+                    S.insRy()[nr] = S.insRy()[t];
                     nr++;
                 }
             }
-            S.cnt[0] = nl;
-            S.cnt[1] = nr;
+            S.cnt()[0] = nl;
+            S.cnt()[1] = nr;
         }
-        ncur = block_scan_excl(S.scan, n, S.red);
+        ncur = block_scan_excl(S.scan(), n, S.red());
         for (int k = tid; k < n; k += kThreads)
-            if (!S.frem[k]) {
-                Cx[1 + S.scan[k]] = X[k];
-                Cy[1 + S.scan[k]] = Cc[k];
+            if (!S.frem()[k]) {
+                Cx[1 + S.scan()[k]] = X[k];
+                Cy[1 + S.scan()[k]] = Cc[k];
             }
         __syncthreads();
-        const int nl = S.cnt[0], nr = S.cnt[1];
+        const int nl = S.cnt()[0], nr = S.cnt()[1];
         if (nl != nr) status |= DCEGM_ST_MISALIGNED;
         // insert!(…) pairs (dc_algo.jl:486-492)
         for (int i = 0; i < nl; i++) {
-            const double lx = S.insLx[i];
+            const double lx = S.insLx()[i];
             int cand = 0x7fffffff;
             for (int k = tid; k < ncur; k += kThreads)
                 if (Cx[1 + k] > lx) {
                     cand = k;
                     break;
                 }
-            const int j = block_min_int(cand, S.red);
+            const int j = block_min_int(cand, S.red());
             if (j == 0x7fffffff || i >= nr) {
                 status |= DCEGM_ST_INSERT_RANGE;
                 break;
@@ -512,9 +537,9 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
             }
             if (tid == 0) {
                 Cx[1 + j] = lx;
-                Cy[1 + j] = S.insLy[i];
-                Cx[1 + j + 1] = S.insRx[i];
-                Cy[1 + j + 1] = S.insRy[i];
+                Cy[1 + j] = S.insLy()[i];
+                Cx[1 + j + 1] = S.insRx()[i];
+                Cy[1 + j + 1] = S.insRy()[i];
             }
             ncur += 2;
             __syncthreads();
@@ -540,7 +565,7 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
     // cases; detect, and only then rank-sort through the (now free) D arrays.
     int bad = 0;
     for (int k = tid; k + 1 < lenC; k += kThreads) bad |= Cx[k + 1] < Cx[k];
-    bad = block_sum(bad, S.red);
+    bad = block_sum(bad, S.red());
     if (bad) {
         for (int k = tid; k < lenC; k += kThreads) {
             const double xk = Cx[k];
@@ -549,13 +574,13 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
                 double xi = Cx[i];
                 r += (xi < xk) || (xi == xk && i < k);
             }
-            S.Dx[r] = xk;
-            S.Dv[r] = Cy[k];
+            S.Dx()[r] = xk;
+            S.Dv()[r] = Cy[k];
         }
         __syncthreads();
         for (int k = tid; k < lenC; k += kThreads) {
-            Cx[k] = S.Dx[k];
-            Cy[k] = S.Dv[k];
+            Cx[k] = S.Dx()[k];
+            Cy[k] = S.Dv()[k];
         }
         __syncthreads();
     }
@@ -569,7 +594,7 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
         if (k + 1 < lenV && !(Vx[k + 1] > Vx[k])) flag |= DCEGM_ST_NONMONOTONE;
         if (!isfinite(Vx[k]) || !isfinite(Vy[k])) flag |= DCEGM_ST_NONFINITE;
     }
-    if (flag || status) atomicOr(&S.cnt[2], flag | (int)status);
+    if (flag || status) atomicOr(&S.cnt()[2], flag | (int)status);
     __syncthreads();
     if (tid == 0) {
         *nV = lenV;

@@ -17,97 +17,36 @@
 
 namespace dcegm {
 
-struct SmemPlan {
-    size_t bytes;
-    size_t off_line[2][7];  // [set][wc_x, wc_y, wv_x, wv_y, r_x, rc_y, rv_y]
-    size_t off_D[3], off_T[2];
-    size_t off_isl[4], off_ins[4];
-    size_t off_scan, off_segb, off_islkey[2], off_red, off_redd, off_cnt;
-    size_t off_u16[5], off_u8[4], off_segrise, off_insok[2];
+// shared-memory map of solve_f_kernel: 2 sets x 7 double[cap] polyline arrays, then the envelope scratch
+struct FPlan {
+    int cap8;  // bytes of one double[cap] array (16-byte aligned)
+    EnvScratch env;
+    __host__ __device__ FPlan(int cap, int isec_cap) {
+        cap8 = EnvScratch::align16(cap * 8);
+        env.off = 14 * cap8;
+        env.cap = cap;
+        env.isec_cap = isec_cap;
+    }
+    __host__ __device__ size_t bytes() const { return (size_t)env.off + env.bytes(); }
 };
 
-__host__ __device__ inline SmemPlan plan_smem(int cap, int isec_cap) {
-    SmemPlan p;
-    size_t o = 0;
-    auto take = [&](size_t bytes) {
-        size_t r = o;
-        o += (bytes + 15) / 16 * 16;
-        return r;
-    };
-    for (int s = 0; s < 2; s++)
-        for (int a = 0; a < 7; a++) p.off_line[s][a] = take((size_t)cap * 8);
-    for (int a = 0; a < 3; a++) p.off_D[a] = take((size_t)cap * 8);
-    for (int a = 0; a < 2; a++) p.off_T[a] = take((size_t)cap * 8);
-    for (int a = 0; a < 4; a++) p.off_isl[a] = take((size_t)isec_cap * 8);
-    for (int a = 0; a < 4; a++) p.off_ins[a] = take((size_t)isec_cap * 8);
-    p.off_redd = take(kWarps * 8);
-    p.off_scan = take((size_t)cap * 4);
-    p.off_segb = take((kSegCap + 1) * 4);
-    for (int a = 0; a < 2; a++) p.off_islkey[a] = take((size_t)isec_cap * 4);
-    p.off_red = take((kWarps + 1) * 4);
-    p.off_cnt = take(8 * 4);
-    for (int a = 0; a < 5; a++) p.off_u16[a] = take((size_t)cap * 2);
-    for (int a = 0; a < 4; a++) p.off_u8[a] = take((size_t)cap);
-    p.off_segrise = take(kSegCap);
-    for (int a = 0; a < 2; a++) p.off_insok[a] = take((size_t)isec_cap);
-    p.bytes = o;
-    return p;
-}
+size_t solver_f_smem_bytes(int cap, int isec_cap) { return FPlan(cap, isec_cap).bytes(); }
 
-size_t solver_f_smem_bytes(int cap, int isec_cap) { return plan_smem(cap, isec_cap).bytes; }
-
+// One set of the four polylines of a period: worker policy / value (own knots each), retiree policy and
+// value (shared knots: both are (a + c0) with the same prepended point).  Offsets into dc_smem only.
 struct LineSet {
-    double *wc_x, *wc_y, *wv_x, *wv_y, *r_x, *rc_y, *rv_y;
+    int base, cap8;
     int n_wc, n_wv, n_r;
     double vb_w, vb_r;  // Envelope.vbound of the two value lines
+    __device__ __forceinline__ double* arr(int a) const { return reinterpret_cast<double*>(dc_smem + base + a * cap8); }
+    __device__ __forceinline__ double* wc_x() const { return arr(0); }
+    __device__ __forceinline__ double* wc_y() const { return arr(1); }
+    __device__ __forceinline__ double* wv_x() const { return arr(2); }
+    __device__ __forceinline__ double* wv_y() const { return arr(3); }
+    __device__ __forceinline__ double* r_x() const { return arr(4); }
+    __device__ __forceinline__ double* rc_y() const { return arr(5); }
+    __device__ __forceinline__ double* rv_y() const { return arr(6); }
 };
-
-__device__ inline void bind_scratch(unsigned char* smem, const SmemPlan& P, int cap, int isec_cap, EnvScratch& S,
-                                    LineSet set[2]) {
-    for (int s = 0; s < 2; s++) {
-        set[s].wc_x = (double*)(smem + P.off_line[s][0]);
-        set[s].wc_y = (double*)(smem + P.off_line[s][1]);
-        set[s].wv_x = (double*)(smem + P.off_line[s][2]);
-        set[s].wv_y = (double*)(smem + P.off_line[s][3]);
-        set[s].r_x = (double*)(smem + P.off_line[s][4]);
-        set[s].rc_y = (double*)(smem + P.off_line[s][5]);
-        set[s].rv_y = (double*)(smem + P.off_line[s][6]);
-    }
-    S.Dx = (double*)(smem + P.off_D[0]);
-    S.Dv = (double*)(smem + P.off_D[1]);
-    S.Dc = (double*)(smem + P.off_D[2]);
-    S.Tx = (double*)(smem + P.off_T[0]);
-    S.Ty = (double*)(smem + P.off_T[1]);
-    S.islx = (double*)(smem + P.off_isl[0]);
-    S.isly = (double*)(smem + P.off_isl[1]);
-    S.isl2x = (double*)(smem + P.off_isl[2]);
-    S.isl2y = (double*)(smem + P.off_isl[3]);
-    S.insLx = (double*)(smem + P.off_ins[0]);
-    S.insLy = (double*)(smem + P.off_ins[1]);
-    S.insRx = (double*)(smem + P.off_ins[2]);
-    S.insRy = (double*)(smem + P.off_ins[3]);
-    S.redd = (double*)(smem + P.off_redd);
-    S.scan = (int*)(smem + P.off_scan);
-    S.segb = (int*)(smem + P.off_segb);
-    S.islkey = (int*)(smem + P.off_islkey[0]);
-    S.isl2key = (int*)(smem + P.off_islkey[1]);
-    S.red = (int*)(smem + P.off_red);
-    S.cnt = (int*)(smem + P.off_cnt);
-    S.pos = (unsigned short*)(smem + P.off_u16[0]);
-    S.order = (unsigned short*)(smem + P.off_u16[1]);
-    S.ord2 = (unsigned short*)(smem + P.off_u16[2]);
-    S.win = (unsigned short*)(smem + P.off_u16[3]);
-    S.swj = (unsigned short*)(smem + P.off_u16[4]);
-    S.fknot = smem + P.off_u8[0];
-    S.fuq = smem + P.off_u8[1];
-    S.frem = smem + P.off_u8[2];
-    S.cntI = smem + P.off_u8[3];
-    S.segrise = smem + P.off_segrise;
-    S.insLok = smem + P.off_insok[0];
-    S.insRok = smem + P.off_insok[1];
-    S.cap = cap;
-    S.isec_cap = isec_cap;
-}
 
 // one line -> HBM (interleaved x,y), each point written once
 __device__ inline void store_line(const DeviceBatch& B, int m, int it, int iy, int id, int kind, const double* x,
@@ -130,7 +69,6 @@ __device__ __forceinline__ double vfun_dev(bool worker_line, bool next_terminal,
 }
 
 __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
-    extern __shared__ __align__(16) unsigned char smem[];
     const int m = blockIdx.x;
     const int tid = threadIdx.x;
     __shared__ DevModel s_p;
@@ -138,11 +76,12 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
     __syncthreads();
     const DevModel& p = s_p;
     const int na = p.na, ny = p.ny, nT = p.nT;
-    const int cap = B.lay.cap;
-    const SmemPlan P = plan_smem(cap, B.lay.isec_cap);
-    EnvScratch S;
-    LineSet set[2];
-    bind_scratch(smem, P, cap, B.lay.isec_cap, S, set);
+    const FPlan P(B.lay.cap, B.lay.isec_cap);
+    const EnvScratch S = P.env;
+    LineSet C, N;  // C is being built (period t), N holds period t+1
+    C.cap8 = N.cap8 = P.cap8;
+    C.base = 0;
+    N.base = 7 * P.cap8;
     __shared__ double s_ev0[2];
     __shared__ int s_n[2];
     __shared__ int s_status;
@@ -156,50 +95,47 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
     const bool can_skip = p.cfloor > 0.0;  // 0*up(c) == 0 exactly when c >= cfloor > 0
 
     if (tid == 0) s_status = 0;
-    int cur = 0;  // set[cur] is being built, set[cur^1] holds period t+1
 
     // summary accumulators (thread 0)
     int sum_envp = 0, sum_seg = 0, sum_is = 0, sum_rm = 0, sum_maxlen = 0;
     long long sum_pts = 0;
 
     for (int t = nT - 1; t >= 0; t--) {
-        LineSet& C = set[cur];
-        const LineSet& N = set[cur ^ 1];
         if (t == nT - 1) {
             // terminal period (dc_algo.jl:14-20)
             if (tid == 0) {
-                C.wc_x[0] = p.a_lowT; C.wc_y[0] = 0.0; C.wc_x[1] = p.a_high; C.wc_y[1] = p.a_high;
-                C.r_x[0] = p.a_lowT;  C.rc_y[0] = 0.0; C.r_x[1] = p.a_high;  C.rc_y[1] = p.a_high;
+                C.wc_x()[0] = p.a_lowT; C.wc_y()[0] = 0.0; C.wc_x()[1] = p.a_high; C.wc_y()[1] = p.a_high;
+                C.r_x()[0] = p.a_lowT;  C.rc_y()[0] = 0.0; C.r_x()[1] = p.a_high;  C.rc_y()[1] = p.a_high;
             }
             int nv = 2;
             if (p.nu > 0) {
                 nv = na;
                 for (int k = tid; k < na; k += kThreads) {
                     double b = p.nu * u_plain(avec[k] + p.bbar, p);
-                    C.wv_x[k] = avec[k];
-                    C.wv_y[k] = b - p.alpha;  // bequest(a, true, p)
+                    C.wv_x()[k] = avec[k];
+                    C.wv_y()[k] = b - p.alpha;  // bequest(a, true, p)
                 }
             } else if (tid == 0) {
-                C.wv_x[0] = p.a_lowT; C.wv_y[0] = 0.0; C.wv_x[1] = p.a_high; C.wv_y[1] = kNaN;
-                C.rv_y[0] = 0.0; C.rv_y[1] = kNaN;
+                C.wv_x()[0] = p.a_lowT; C.wv_y()[0] = 0.0; C.wv_x()[1] = p.a_high; C.wv_y()[1] = kNaN;
+                C.rv_y()[0] = 0.0; C.rv_y()[1] = kNaN;
             }
             C.n_wc = 2; C.n_wv = nv; C.n_r = 2;
             C.vb_w = 0.0; C.vb_r = 0.0;
             __syncthreads();
-            store_line(B, m, t, 0, 0, DCEGM_KIND_C, C.wc_x, C.wc_y, 2);
-            store_line(B, m, t, 0, 1, DCEGM_KIND_C, C.r_x, C.rc_y, 2);
+            store_line(B, m, t, 0, 0, DCEGM_KIND_C, C.wc_x(), C.wc_y(), 2);
+            store_line(B, m, t, 0, 1, DCEGM_KIND_C, C.r_x(), C.rc_y(), 2);
             if (p.nu > 0) {
                 // retiree terminal value line lives on the savings grid, not on r_x: stage through D
                 for (int k = tid; k < na; k += kThreads) {
-                    S.Dx[k] = avec[k];
-                    S.Dv[k] = p.nu * u_plain(avec[k] + p.bbar, p) - 0.0;
+                    S.Dx()[k] = avec[k];
+                    S.Dv()[k] = p.nu * u_plain(avec[k] + p.bbar, p) - 0.0;
                 }
                 __syncthreads();
-                store_line(B, m, t, 0, 0, DCEGM_KIND_V, C.wv_x, C.wv_y, na);
-                store_line(B, m, t, 0, 1, DCEGM_KIND_V, S.Dx, S.Dv, na);
+                store_line(B, m, t, 0, 0, DCEGM_KIND_V, C.wv_x(), C.wv_y(), na);
+                store_line(B, m, t, 0, 1, DCEGM_KIND_V, S.Dx(), S.Dv(), na);
             } else {
-                store_line(B, m, t, 0, 0, DCEGM_KIND_V, C.wv_x, C.wv_y, 2);
-                store_line(B, m, t, 0, 1, DCEGM_KIND_V, C.r_x, C.rv_y, 2);
+                store_line(B, m, t, 0, 0, DCEGM_KIND_V, C.wv_x(), C.wv_y(), 2);
+                store_line(B, m, t, 0, 1, DCEGM_KIND_V, C.r_x(), C.rv_y(), 2);
             }
             if (tid == 0) {
                 B.vbound[state_slot(B.lay, m, t, 0) * 2 + 0] = 0.0;
@@ -209,7 +145,11 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
                 sum_pts += 4 + 2 * nv;
             }
             __syncthreads();
-            cur ^= 1;
+            {
+                const LineSet tmp = N;
+                N = C;
+                C = tmp;
+            }
             continue;
         }
 
@@ -230,21 +170,21 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
             for (int iy = 0; iy < ny; iy++) {
                 const double m1 = aR + off[iy];
                 // future retiree (iid = 2): policy and value share their knots
-                const int ir = left_knot(N.r_x, N.n_r, m1);
-                double c2 = interp_at(N.r_x, N.rc_y, N.n_r, ir, m1);
+                const int ir = left_knot(N.r_x(), N.n_r, m1);
+                double c2 = interp_at(N.r_x(), N.rc_y(), N.n_r, ir, m1);
                 c2 = c2 < p.cfloor ? p.cfloor : c2;  // floory! (line.jl:131-139)
                 double v2;
                 if (next_terminal && p.nu > 0)
                     v2 = p.nu * u_plain(c2 + p.bbar, p) - 0.0;
-                else if (next_terminal || m1 < N.r_x[1])
+                else if (next_terminal || m1 < N.r_x()[1])
                     v2 = u_work(c2, false, p) + p.beta * N.vb_r;
                 else
-                    v2 = interp_at(N.r_x, N.rv_y, N.n_r, ir, m1);
+                    v2 = interp_at(N.r_x(), N.rv_y(), N.n_r, ir, m1);
                 double c1 = 0.0, v1 = 0.0;
                 if (need_w) {
-                    c1 = interp_y(N.wc_x, N.wc_y, N.n_wc, m1);
+                    c1 = interp_y(N.wc_x(), N.wc_y(), N.n_wc, m1);
                     c1 = c1 < p.cfloor ? p.cfloor : c1;
-                    v1 = vfun_dev(true, next_terminal, c1, m1, N.wv_x, N.wv_y, N.n_wv, N.vb_w, p);
+                    v1 = vfun_dev(true, next_terminal, c1, m1, N.wv_x(), N.wv_y(), N.n_wv, N.vb_w, p);
                 }
                 double pw, ls = 0.0;
                 if (id == 0 || p.delta != 0.0) {
@@ -290,13 +230,13 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
             const double x = a + c0;
             const double vy = u_work(c0, id == 0, p) + p.beta * ev;  // dc_algo.jl:78
             if (id == 0) {
-                S.Dx[koff + ia] = x;
-                S.Dv[koff + ia] = vy;
-                S.Dc[koff + ia] = c0;
+                S.Dx()[koff + ia] = x;
+                S.Dv()[koff + ia] = vy;
+                S.Dc()[koff + ia] = c0;
             } else {
-                C.r_x[1 + ia] = x;
-                C.rc_y[1 + ia] = c0;
-                C.rv_y[1 + ia] = vy;
+                C.r_x()[1 + ia] = x;
+                C.rc_y()[1 + ia] = c0;
+                C.rv_y()[1 + ia] = vy;
             }
             if (ia == 0) s_ev0[id] = ev;
         }
@@ -306,16 +246,16 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
         if (B.dirty) {  // runfdemo: vdirty / cdirty (dc_algo.jl:79-82)
             double2* d = B.dirty + line_slot(B.lay, m, t, 0, 0, 0) * (size_t)na;
             for (int k = tid; k < na; k += kThreads) {
-                d[k] = make_double2(S.Dx[koff + k], S.Dc[koff + k]);                 // worker c
-                d[(size_t)na + k] = make_double2(S.Dx[koff + k], S.Dv[koff + k]);    // worker v
-                d[(size_t)2 * na + k] = make_double2(C.r_x[1 + k], C.rc_y[1 + k]);   // retiree c
-                d[(size_t)3 * na + k] = make_double2(C.r_x[1 + k], C.rv_y[1 + k]);   // retiree v
+                d[k] = make_double2(S.Dx()[koff + k], S.Dc()[koff + k]);                 // worker c
+                d[(size_t)na + k] = make_double2(S.Dx()[koff + k], S.Dv()[koff + k]);    // worker v
+                d[(size_t)2 * na + k] = make_double2(C.r_x()[1 + k], C.rc_y()[1 + k]);   // retiree c
+                d[(size_t)3 * na + k] = make_double2(C.r_x()[1 + k], C.rv_y()[1 + k]);   // retiree v
             }
         }
 
         // ---------------- 2. worker: secondary envelope + policy repair -----------------------------
         const size_t ss = state_slot(B.lay, m, t, 0);
-        worker_envelope(S, koff, na, a0, ev0w, p, C.wv_x, C.wv_y, &s_n[0], C.wc_x, C.wc_y, &s_n[1], B.meta + ss,
+        worker_envelope(S, koff, na, a0, ev0w, p, C.wv_x(), C.wv_y(), &s_n[0], C.wc_x(), C.wc_y(), &s_n[1], B.meta + ss,
                         B.isects + ss * (size_t)B.lay.isec_cap, B.removed + ss * (size_t)B.lay.rem_words,
                         B.lay.rem_words);
         C.n_wv = s_n[0];
@@ -324,25 +264,25 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
 
         // ---------------- 3. retiree: credit-constraint point and checks (dc_algo.jl:90-101) --------
         if (tid == 0) {
-            C.r_x[0] = a0;
-            C.rc_y[0] = 0.0;
-            C.rv_y[0] = ev0r;
+            C.r_x()[0] = a0;
+            C.rc_y()[0] = 0.0;
+            C.rv_y()[0] = ev0r;
         }
         C.n_r = na + 1;
         C.vb_r = ev0r;
         __syncthreads();
         int flag = 0;
         for (int k = tid; k < na + 1; k += kThreads) {
-            if (k + 1 < na + 1 && !(C.r_x[k + 1] > C.r_x[k])) flag |= DCEGM_ST_NONMONOTONE;
-            if (!isfinite(C.r_x[k]) || !isfinite(C.rc_y[k]) || !isfinite(C.rv_y[k])) flag |= DCEGM_ST_NONFINITE;
+            if (k + 1 < na + 1 && !(C.r_x()[k + 1] > C.r_x()[k])) flag |= DCEGM_ST_NONMONOTONE;
+            if (!isfinite(C.r_x()[k]) || !isfinite(C.rc_y()[k]) || !isfinite(C.rv_y()[k])) flag |= DCEGM_ST_NONFINITE;
         }
         if (flag) atomicOr(&s_status, flag);
-        if (tid == 0 && S.cnt[2]) atomicOr(&s_status, S.cnt[2]);
+        if (tid == 0 && S.cnt()[2]) atomicOr(&s_status, S.cnt()[2]);
 
-        store_line(B, m, t, 0, 0, DCEGM_KIND_C, C.wc_x, C.wc_y, C.n_wc);
-        store_line(B, m, t, 0, 0, DCEGM_KIND_V, C.wv_x, C.wv_y, C.n_wv);
-        store_line(B, m, t, 0, 1, DCEGM_KIND_C, C.r_x, C.rc_y, C.n_r);
-        store_line(B, m, t, 0, 1, DCEGM_KIND_V, C.r_x, C.rv_y, C.n_r);
+        store_line(B, m, t, 0, 0, DCEGM_KIND_C, C.wc_x(), C.wc_y(), C.n_wc);
+        store_line(B, m, t, 0, 0, DCEGM_KIND_V, C.wv_x(), C.wv_y(), C.n_wv);
+        store_line(B, m, t, 0, 1, DCEGM_KIND_C, C.r_x(), C.rc_y(), C.n_r);
+        store_line(B, m, t, 0, 1, DCEGM_KIND_V, C.r_x(), C.rv_y(), C.n_r);
         if (tid == 0) {
             B.vbound[ss * 2 + 0] = ev0w;
             B.vbound[ss * 2 + 1] = ev0r;
@@ -357,16 +297,20 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
             sum_pts += C.n_wc + C.n_wv + 2 * C.n_r;
         }
         __syncthreads();
-        cur ^= 1;
+        {
+            const LineSet tmp = N;
+            N = C;
+            C = tmp;
+        }
     }
 
     // ---------------- per-model summary (payload of the multi-GPU allgather) -------------------------
-    const LineSet& L0 = set[cur ^ 1];  // period 1
+    const LineSet& L0 = N;  // period 1
     double cs_c = 0.0, cs_v = 0.0;
-    for (int k = tid; k < L0.n_wc; k += kThreads) cs_c += L0.wc_y[k];
-    for (int k = tid; k < L0.n_r; k += kThreads) cs_c += L0.rc_y[k];
-    for (int k = tid; k < L0.n_wv; k += kThreads) cs_v += isfinite(L0.wv_y[k]) ? L0.wv_y[k] : 0.0;
-    for (int k = tid; k < L0.n_r; k += kThreads) cs_v += isfinite(L0.rv_y[k]) ? L0.rv_y[k] : 0.0;
+    for (int k = tid; k < L0.n_wc; k += kThreads) cs_c += L0.wc_y()[k];
+    for (int k = tid; k < L0.n_r; k += kThreads) cs_c += L0.rc_y()[k];
+    for (int k = tid; k < L0.n_wv; k += kThreads) cs_v += isfinite(L0.wv_y()[k]) ? L0.wv_y()[k] : 0.0;
+    for (int k = tid; k < L0.n_r; k += kThreads) cs_v += isfinite(L0.rv_y()[k]) ? L0.rv_y()[k] : 0.0;
     // fixed-order block sums: warp butterfly then ascending warps
     __shared__ double s_cs[2][kWarps];
 #pragma unroll
@@ -391,10 +335,10 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
         const double fr[DCEGM_SUMMARY_NPROBE] = {0.02, 0.05, 0.1, 0.2, 0.3, 0.5, 0.7, 0.9};
         for (int q = 0; q < DCEGM_SUMMARY_NPROBE; q++) {
             const double mq = p.a_low + fr[q] * (p.a_high - p.a_low);
-            double c = interp_y(L0.wc_x, L0.wc_y, L0.n_wc, mq);
+            double c = interp_y(L0.wc_x(), L0.wc_y(), L0.n_wc, mq);
             c = c < p.cfloor ? p.cfloor : c;
             sm.c1_probe[q] = c;
-            sm.v1_probe[q] = nT >= 2 ? vfun_dev(true, false, c, mq, L0.wv_x, L0.wv_y, L0.n_wv, L0.vb_w, p) : 0.0;
+            sm.v1_probe[q] = nT >= 2 ? vfun_dev(true, false, c, mq, L0.wv_x(), L0.wv_y(), L0.n_wv, L0.vb_w, p) : 0.0;
         }
         double a = 0.0, b = 0.0;
         for (int w = 0; w < kWarps; w++) {
@@ -409,7 +353,7 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
 }
 
 cudaError_t launch_solve_f(const DeviceBatch& B, cudaStream_t stream) {
-    const size_t smem = plan_smem(B.lay.cap, B.lay.isec_cap).bytes;
+    const size_t smem = FPlan(B.lay.cap, B.lay.isec_cap).bytes();
     static size_t configured = 0;
     if (smem > configured) {
         cudaError_t e = cudaFuncSetAttribute(solve_f_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
