@@ -84,7 +84,7 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
     const int na = params[0].na, ny = params[0].ny, nT = params[0].nT;
     dcegm_layout lay;
     make_layout(model, nmodels, na, ny, nT, (flags & DCEGM_KEEP_DIRTY) ? 1 : 0, (flags & DCEGM_SUMMARY_ONLY) ? 0 : 1, &lay);
-    if (lay.cap > 65535) return fail(h, DCEGM_E_INVALID, "na too large for the shared-memory resident solver");
+    if (lay.cap >= 2 * kSearchTop) return fail(h, DCEGM_E_INVALID, "na too large for the shared-memory resident solver");
     size_t smem = model == DCEGM_MODEL_F   ? solver_f_smem_bytes(lay.cap, lay.isec_cap)
                   : model == DCEGM_MODEL_G ? solver_g_smem_bytes(lay.cap, lay.isec_cap, na, ny)
                                            : (size_t)(4 * (na + 1) * 8 + 1024);
@@ -155,6 +155,9 @@ int run(dcegm_ctx* h) {
     // terminal-period slots of the per-state side tables are not written by the solver
     CK(cudaMemsetAsync(B.isects, 0, sizeof(double2) * nstates * B.lay.isec_cap, h->stream));
     CK(cudaMemsetAsync(B.removed, 0, sizeof(uint32_t) * nstates * B.lay.rem_words, h->stream));
+    CK(cudaMemsetAsync(B.lens, 0, sizeof(int32_t) * nstates * 4, h->stream));
+    CK(cudaMemsetAsync(B.meta, 0, sizeof(dcegm_env_meta) * nstates, h->stream));
+    CK(cudaMemsetAsync(B.vbound, 0, sizeof(double) * nstates * 2, h->stream));
     cudaError_t e;
     if (B.lay.model == DCEGM_MODEL_F)
         e = launch_solve_f(B, h->stream);

@@ -65,14 +65,16 @@ __device__ __forceinline__ size_t state_slot(const dcegm_layout& l, int m, int i
 // ---------------------------------------------------------------------------------------------
 // polyline primitives (line.jl:220-254).  Lines live in shared memory as SoA (x[], y[]).
 // ---------------------------------------------------------------------------------------------
-// number of knots <= q  (searchsortedlast), branch-free binary search
+// number of knots <= q (searchsortedlast): fixed-trip, branch-free power-of-two descent.  kSearchTop
+// is the largest step; lines hold fewer than 2*kSearchTop points (checked at upload).
+constexpr int kSearchTop = 1024;
 __device__ __forceinline__ int count_le(const double* __restrict__ x, int n, double q) {
-    int lo = 0, len = n;
-    while (len > 0) {
-        int half = len >> 1;
-        bool le = x[lo + half] <= q;
-        lo = le ? lo + half + 1 : lo;
-        len = le ? len - half - 1 : half;
+    int lo = 0;
+#pragma unroll
+    for (int step = kSearchTop; step >= 1; step >>= 1) {
+        const int idx = lo + step - 1;
+        const bool ok = idx < n && x[idx < n ? idx : 0] <= q;
+        lo = ok ? lo + step : lo;
     }
     return lo;
 }
