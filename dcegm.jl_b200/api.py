@@ -1,0 +1,234 @@
+"""Host-side mirror of DCEGM.jl's entry points for the hot path, over the C ABI of include/dcegm.h.
+
+Same names, argument meaning and error behaviour as the reference (no Julia toolchain exists in
+this image, so the host side is Python; the Julia shim a maintainer would write is in
+INTEGRATION.md):
+
+    runf(par=...)       -> (FModel, Param)     src/dc_algo.jl:335-341
+    runfdemo(par=...)   -> (FModel, Param)     src/dc_algo.jl:342-348   (keeps vdirty / cdirty)
+    rung(par=...)       -> (GModel, Param)     src/dc_algo.jl:356-362
+    minimal_EGM(p)      -> (m, c)              src/minimal_EGM.jl:3-43  (data instead of the plot)
+    bm()                -> timing dict         src/bench.jl:3-31        (without the MATLAB shell-out)
+    Point, MLine, Envelope, getx, gety, gets, getr, bound   src/line.jl, src/envelope.jl
+
+Indices are 1-based like the reference: ``m.v[id, it]``, ``m.c[id, it]`` (FModel) and
+``m.v[id, iy, it]`` (GModel).  ``getr`` returns 1-based indices into the line handed to
+``secondary_envelope`` (including bend-back points), like ``Envelope.removed``.
+
+Nothing here computes a solution on the host: every call goes to libdcegm_cuda.so and raises
+if the library or a CUDA device is missing.
+"""
+import time
+
+import numpy as np
+
+from . import _abi
+from .param import Param
+from .solver import Solver
+
+__all__ = ["Point", "MLine", "Envelope", "FModel", "GModel", "runf", "runfdemo", "rung", "minimal_EGM", "bm",
+           "getx", "gety", "gets", "getr", "bound", "DCEGMError", "dc_EGM"]
+
+
+class DCEGMError(RuntimeError):
+    """the exception the reference would have thrown for this model"""
+
+
+class Point:  # line.jl:1-4
+    __slots__ = ("x", "y")
+
+    def __init__(self, x, y):
+        self.x, self.y = float(x), float(y)
+
+    def __eq__(self, o):  # line.jl:37: exact equality on both coordinates
+        return isinstance(o, Point) and self.x == o.x and self.y == o.y
+
+    def __repr__(self):
+        return f"Point({self.x!r}, {self.y!r})"
+
+
+class MLine:  # line.jl:62-87: a vector of Points; stored here as an (n, 2) array view
+    def __init__(self, xy):
+        self.xy = np.asarray(xy, dtype=np.float64).reshape(-1, 2)
+
+    @property
+    def v(self):
+        return [Point(x, y) for x, y in self.xy]
+
+    def __len__(self):
+        return self.xy.shape[0]
+
+    def __getitem__(self, i):  # 1-based like the reference
+        x, y = self.xy[i - 1]
+        return Point(x, y)
+
+    def __repr__(self):
+        return f"{len(self)}-point MLine"
+
+
+def getx(l):  # line.jl:121-124
+    return (l.env if isinstance(l, Envelope) else l).xy[:, 0].copy()
+
+
+def gety(l):
+    return (l.env if isinstance(l, Envelope) else l).xy[:, 1].copy()
+
+
+class Envelope:  # envelope.jl:16-40
+    def __init__(self, env, isects=None, removed=None, vbound=0.0):
+        self.env = env if isinstance(env, MLine) else MLine(env)
+        self._isects = np.zeros((0, 2)) if isects is None else np.asarray(isects, dtype=np.float64).reshape(-1, 2)
+        self.removed = [] if removed is None else [int(i) for i in removed]
+        self.vbound = float(vbound)
+
+    @property
+    def isects(self):
+        return [Point(x, y) for x, y in self._isects]
+
+    def __repr__(self):
+        return f"{len(self.env)}-point Float64 Envelope"
+
+
+def gets(e):  # envelope.jl:52-54
+    return e.isects
+
+
+def getr(e):
+    return e.removed
+
+
+def bound(e):
+    return e.vbound
+
+
+class _Indexed:
+    """1-based [id, it] / [id, iy, it] view building Envelope objects lazily from the flat Solution"""
+
+    def __init__(self, sol, kind, nstate_indexed):
+        self.sol, self.kind, self.g = sol, kind, nstate_indexed
+
+    def __getitem__(self, key):
+        if self.g:
+            id, iy, it = key
+        else:
+            (id, it), iy = key, 1
+        s, k = self.sol, self.kind
+        lay = s.lay
+        if not (1 <= id <= 2 and 1 <= it <= lay.nT and 1 <= iy <= lay.nstate):
+            raise IndexError(f"BoundsError: attempt to access {key}")  # Julia BoundsError
+        if k in (_abi.KIND_CDIRTY, _abi.KIND_VDIRTY):
+            if s.dirty is None or it == lay.nT:
+                raise KeyError("dirty lines exist only after runfdemo, for it < nT")
+            return MLine(s.dirty[0, it - 1, iy - 1, id - 1, k - 2])
+        n = int(s.lens[0, it - 1, iy - 1, id - 1, k])
+        env = MLine(s.lines[0, it - 1, iy - 1, id - 1, k, :n])
+        vb = float(s.vbound[0, it - 1, iy - 1, id - 1])
+        if k == _abi.KIND_V and id == 1:
+            return Envelope(env, s.isect_points(0, it - 1, iy - 1), s.removed_idx(0, it - 1, iy - 1) + 1, vb)
+        return Envelope(env, vbound=vb if k == _abi.KIND_V else 0.0)
+
+
+_STATUS_ERRORS = {
+    _abi.ST_NONMONOTONE: "knot-vectors must be unique and sorted in increasing order",  # Interpolations.jl, line.jl:236
+    _abi.ST_NO_BRACKET: "ArgumentError: The interval [a,b] is not a bracketing interval",  # Roots.fzero, envelope.jl:199
+    _abi.ST_ALL_FALLING: "an upper envelope requires by definition at least 2 lines.",      # envelope.jl:149-151
+    _abi.ST_MISALIGNED: "BoundsError: insert_right shorter than insert_left",               # dc_algo.jl:486-491
+    _abi.ST_INSERT_RANGE: "BoundsError: kink insertion index out of range",                 # dc_algo.jl:472,489
+    _abi.ST_NONFINITE: "non-finite value in a computed line",
+    _abi.ST_ISECT_OVERFLOW: "library capacity: more intersections than isec_cap",
+    _abi.ST_LINE_OVERFLOW: "library capacity: line outgrew its slot",
+    _abi.ST_SEG_OVERFLOW: "library capacity: more sections than seg_cap",
+    _abi.ST_LOOP_LIMIT: "upper_env: third-line loop did not terminate",
+}
+
+
+def _raise_for_status(st):
+    if st:
+        raise DCEGMError("; ".join(t for b, t in _STATUS_ERRORS.items() if st & b) + f" (status 0x{st:x})")
+
+
+class _Model:
+    def __init__(self, p, sol, model):
+        g = model == _abi.MODEL_G
+        self.p, self.solution = p, sol
+        self.v = _Indexed(sol, _abi.KIND_V, g)
+        self.c = _Indexed(sol, _abi.KIND_C, g)
+        self.vdirty = _Indexed(sol, _abi.KIND_VDIRTY, g)
+        self.cdirty = _Indexed(sol, _abi.KIND_CDIRTY, g)
+
+
+class FModel(_Model):  # param.jl:171-224
+    pass
+
+
+class GModel(_Model):  # param.jl:237-311
+    pass
+
+
+_solver = None
+
+
+def _get_solver(device=0):
+    global _solver
+    if _solver is None or _solver.device != device:
+        _solver = Solver(device)
+    return _solver
+
+
+def dc_EGM(p, model=_abi.MODEL_F, demo=False, device=0, strict=True):
+    """dc_EGM!(m, p) of the reference for one Param; returns the flat Solution (dc_algo.jl:8-206)."""
+    sol = _get_solver(device).solve(model, [p], keep_dirty=demo)
+    if strict:
+        _raise_for_status(int(sol.status[0]))
+    return sol
+
+
+def runf(par=None, device=0, strict=True, **kw):
+    p = Param(par=par, **kw)
+    return FModel(p, dc_EGM(p, _abi.MODEL_F, False, device, strict), _abi.MODEL_F), p
+
+
+def runfdemo(par=None, device=0, strict=True, **kw):
+    p = Param(par=par, **kw)
+    return FModel(p, dc_EGM(p, _abi.MODEL_F, True, device, strict), _abi.MODEL_F), p
+
+
+def rung(par=None, device=0, strict=True, **kw):
+    p = Param(par=par, **kw)
+    return GModel(p, dc_EGM(p, _abi.MODEL_G, False, device, strict), _abi.MODEL_G), p
+
+
+def minimal_EGM(p=None, device=0):
+    """minimal_EGM(p) (minimal_EGM.jl:3-43).  The reference returns only a plot; like
+    minimal_EGM_borrow (minimal_EGM.jl:88) this returns the data: lists m[it], c[it], it = 1..nT."""
+    p = p or Param()
+    sol = _get_solver(device).solve(_abi.MODEL_MINIMAL, [p])
+    _raise_for_status(int(sol.status[0]))
+    m, c = [], []
+    for it in range(p.nT):
+        x, y = sol.line(0, _abi.KIND_C, 0, it)
+        m.append(x)
+        c.append(y)
+    return m, c
+
+
+def bm(samples=39, device=0, verbose=True):
+    """bm() (bench.jl:3-31) without the MATLAB shell-out: one warm-up runf, then `samples` timed
+    runf(par=pd) calls end to end (host setup, H2D, kernel, D2H of every line).  Returns the timing
+    summary BenchmarkTools would print (the reference discards it, bench.jl:29)."""
+    pd = dict(na=500, beta=0.95, sigma=0.35, R=1.05)
+    pd["lambda"] = 0.000002
+    runf(par=pd, device=device)
+    ts = []
+    for _ in range(samples):
+        t0 = time.perf_counter()
+        runf(par=pd, device=device)
+        ts.append(1e3 * (time.perf_counter() - t0))
+    ts = np.array(ts)
+    out = dict(samples=samples, min_ms=float(ts.min()), median_ms=float(np.median(ts)), mean_ms=float(ts.mean()),
+               max_ms=float(ts.max()), kernel_ms=float(_get_solver(device).timing().kernel_ms))
+    if verbose:
+        print("dcegm-b200 timing (runf, na=500, 25 periods):")
+        print("  minimum time: %(min_ms).3f ms\n  median time:  %(median_ms).3f ms\n  mean time:    %(mean_ms).3f ms\n"
+              "  maximum time: %(max_ms).3f ms\n  samples: %(samples)d  (kernel only: %(kernel_ms).3f ms)" % out)
+    return out
