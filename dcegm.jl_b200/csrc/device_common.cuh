@@ -62,6 +62,11 @@ __device__ __forceinline__ size_t state_slot(const dcegm_layout& l, int m, int i
     return ((size_t)m * l.nT + it) * l.nstate + iy;
 }
 
+// All kernel scratch lives in the dynamic shared memory and is addressed as integer offsets from
+// this one symbol, so every access compiles to LDS/STS (pointer tables in registers or local
+// memory made the compiler fall back to generic LD/ST).
+extern __shared__ __align__(16) unsigned char dc_smem[];
+
 // ---------------------------------------------------------------------------------------------
 // polyline primitives (line.jl:220-254).  Lines live in shared memory as SoA (x[], y[]).
 // ---------------------------------------------------------------------------------------------
@@ -101,6 +106,56 @@ __device__ __forceinline__ double interp_at(const double* __restrict__ x, const 
 __device__ __forceinline__ double interp_y(const double* __restrict__ x, const double* __restrict__ y, int n, double q) {
     return interp_at(x, y, n, left_knot(x, n, q), q);
 }
+// ---------------------------------------------------------------------------------------------
+// Bucket index over the knots of one line: T[b] = number of knots whose bucket is < b, for the
+// monotone map bucket(q) = round(clamp((q - lo) * inv, 0, nb-1)).  Because the map is monotone in
+// q (each step — subtraction, multiplication by a positive constant, clamp, rounding — is), all
+// knots in lower buckets are <= q and all knots in higher buckets are > q, so count_le(q) is found
+// by scanning only the knots of q's own bucket, starting at T[bucket(q)]: about two dependent
+// shared-memory loads instead of the eleven of a binary search.  Exact for strictly increasing
+// finite knots (lines that are not are flagged in the status word and searched by count_le).
+// ---------------------------------------------------------------------------------------------
+struct KnotIndex {
+    int tab;        // byte offset in dc_smem of unsigned short T[nb + 1]
+    double lo, inv, top;  // top = nb - 1
+};
+__device__ __forceinline__ int knot_bucket(const KnotIndex& K, double q) {
+    double t = (q - K.lo) * K.inv;
+    t = fmin(fmax(t, 0.0), K.top);  // NaN -> 0
+    return __double2loint(t + DC_MAGIC);
+}
+// largest power of two nb such that nlines tables of nb+1 entries fit into `bytes`
+__host__ __device__ inline int knot_index_buckets(int bytes, int nlines) {
+    int nb = 16;
+    while (nb < 2048 && nlines * (2 * nb + 8) * 2 <= bytes) nb *= 2;  // stride (nb + 8) entries: 16-byte aligned
+    return nb;
+}
+// lo / inv / top of the index over knots x[0..n) with nb buckets
+__device__ __forceinline__ void knot_index_range(KnotIndex& K, const double* x, int n, int nb) {
+    K.lo = x[0];
+    K.inv = (double)nb / (x[n - 1] - x[0]);
+    K.top = (double)(nb - 1);
+}
+// block-level build of the table; x = knots at byte offset x_off of dc_smem (strictly increasing,
+// n >= 2).  All threads call; the caller syncs afterwards.
+static __device__ __noinline__ void knot_index_build(KnotIndex K, int x_off, int n, int nb) {
+    const double* x = reinterpret_cast<const double*>(dc_smem + x_off);
+    unsigned short* T = reinterpret_cast<unsigned short*>(dc_smem + K.tab);
+    for (int k = threadIdx.x; k < n; k += kThreads) {
+        const int bk = knot_bucket(K, x[k]);
+        const int bp = k == 0 ? -1 : knot_bucket(K, x[k - 1]);
+        for (int b = bp + 1; b <= bk; b++) T[b] = (unsigned short)k;
+        if (k == n - 1)
+            for (int b = bk + 1; b <= nb; b++) T[b] = (unsigned short)n;
+    }
+}
+// number of knots <= q
+__device__ __forceinline__ int count_le_indexed(const KnotIndex& K, const double* __restrict__ x, int n, double q) {
+    int i = reinterpret_cast<const unsigned short*>(dc_smem + K.tab)[knot_bucket(K, q)];
+    while (i < n && x[i] <= q) i++;
+    return i;
+}
+
 // whole-Point interpolation on a 2-point line (dc_algo.jl:446-478)
 __device__ __forceinline__ double2 interp2pt(double2 a, double2 b, double q) {
     if (b.x < a.x) {  // sortx!(newleft)

@@ -19,10 +19,8 @@
 
 namespace dcegm {
 
-// All scratch of the envelope lives in the kernel's dynamic shared memory and is addressed as
-// integer offsets from the one `extern __shared__` symbol, so every access compiles to LDS/STS
-// (pointer tables in registers or local memory made the compiler fall back to generic LD/ST).
-extern __shared__ __align__(16) unsigned char dc_smem[];
+// All scratch of the envelope lives in the kernel's dynamic shared memory (dc_smem, declared in
+// device_common.cuh) and is addressed as integer offsets from that one symbol.
 
 struct EnvScratch {
     int off;  // byte offset of the region inside dc_smem

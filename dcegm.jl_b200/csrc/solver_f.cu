@@ -68,6 +68,101 @@ __device__ __forceinline__ double vfun_dev(bool worker_line, bool next_terminal,
     return interp_y(vx, vy, n, m1);
 }
 
+struct NodeOut {
+    double mu, ls, v2;
+};
+
+// One quadrature node of the EGM step for ANY input values (dc_algo.jl:33-53): binary searches and
+// the general pow.  Used when the fast path below does not apply (bequest period, delta > 0 for the
+// retiree, cfloor <= 0, non-monotone or non-finite next-period lines, exponents that are not finite).
+static __device__ __noinline__ void egm_node_generic(const LineSet* Np, const DevModel* pp, double m1, int id, bool next_terminal,
+                                              bool beq, NodeOut* out) {
+    const LineSet& N = *Np;
+    const DevModel& p = *pp;
+    const bool can_skip = p.cfloor > 0.0;  // 0*up(c) == 0 exactly when c >= cfloor > 0
+    const bool need_w = (id == 0) || (p.delta != 0.0) || !can_skip;
+    // future retiree (iid = 2): policy and value share their knots
+    const int ir = left_knot(N.r_x(), N.n_r, m1);
+    double c2 = interp_at(N.r_x(), N.rc_y(), N.n_r, ir, m1);
+    c2 = c2 < p.cfloor ? p.cfloor : c2;  // floory! (line.jl:131-139)
+    double v2;
+    if (next_terminal && p.nu > 0)
+        v2 = p.nu * u_plain(c2 + p.bbar, p) - 0.0;
+    else if (next_terminal || m1 < N.r_x()[1])
+        v2 = u_work(c2, false, p) + p.beta * N.vb_r;
+    else
+        v2 = interp_at(N.r_x(), N.rv_y(), N.n_r, ir, m1);
+    double c1 = 0.0, v1 = 0.0;
+    if (need_w) {
+        c1 = interp_y(N.wc_x(), N.wc_y(), N.n_wc, m1);
+        c1 = c1 < p.cfloor ? p.cfloor : c1;
+        v1 = vfun_dev(true, next_terminal, c1, m1, N.wv_x(), N.wv_y(), N.n_wv, N.vb_w, p);
+    }
+    double pw, ls = 0.0;
+    if (id == 0 || p.delta != 0.0) {
+        // ccp / logsum (dc_algo.jl:316-332): the larger value's exp is exp(0) = 1
+        const bool w_hi = v1 > v2;
+        const double mx = w_hi ? v1 : v2;
+        const double d = ((w_hi ? v2 : v1) - mx) / p.lambda;
+        const double e = dc_exp(d);  // exactly 0 below -745.2
+        const double e1 = w_hi ? 1.0 : e, e2 = w_hi ? e : 1.0;
+        const double s = e1 + e2;
+        pw = e1 / s;
+        ls = mx + p.lambda * dc_log(s);
+        if (id == 1) pw = p.delta;  // dc_algo.jl:44
+    } else {
+        pw = p.delta;  // == 0
+    }
+    if (beq) {  // dc_algo.jl:46-48
+        c1 = c1 + p.bbar;
+        c2 = c2 + p.bbar;
+    }
+    double mu;
+    if (can_skip && pw == 1.0)
+        mu = up(c1, p);
+    else if (can_skip && pw == 0.0)
+        mu = up(c2, p);
+    else
+        mu = pw * up(c1, p) + (1.0 - pw) * up(c2, p);
+    out->mu = mu;
+    out->ls = ls;
+    out->v2 = v2;
+}
+
+static __device__ __noinline__ double dc_pow_cold(double x, double y) { return dc_pow(x, y); }
+// x^y; straight-line code for positive normal x (y finite), the general routine otherwise
+__device__ __forceinline__ double pow_hot(double x, double y) {
+    if (!dc_is_norm_pos(x)) return dc_pow_cold(x, y);
+    double lh, ll;
+    dc_log_parts_pos(x, &lh, &ll);
+    return dc_pow_from_log(lh, ll, y);
+}
+// utils.jl:40-46 / 72-78 from ln c = lh + ll (c positive normal)
+__device__ __forceinline__ double u_from_log(double lh, double ll, bool working, const DevModel& p) {
+    const double dis = working ? p.alpha : 0.0;
+    if (p.gamma_is_one) return (lh + ll) - dis;
+    return p.oneover_oneminusgamma * (dc_pow_from_log(lh, ll, p.oneminusgamma) - 1.0) - dis;
+}
+__device__ __forceinline__ double up_from_log(double lh, double ll, double c, const DevModel& p) {
+    if (p.gamma_is_one) return 1.0 / c;
+    return dc_pow_from_log(lh, ll, p.neg_gamma);
+}
+// interp (line.jl:220-254), y only, from cnt = number of knots <= q on a strictly increasing line:
+// cnt == 0 <=> q < x[0] and cnt == n <=> q >= x[n-1] go to the general routine (extrapolation)
+static __device__ __noinline__ double interp_edge(const double* x, const double* y, int n, int cnt, double q) {
+    int i = cnt - 1;
+    i = i < 0 ? 0 : i;
+    i = i > n - 2 ? n - 2 : i;
+    return interp_at(x, y, n, i, q);
+}
+__device__ __forceinline__ double interp_cnt(const double* __restrict__ x, const double* __restrict__ y, int n, int cnt,
+                                             double q) {
+    if (cnt == 0 || cnt == n) return interp_edge(x, y, n, cnt, q);
+    const int i = cnt - 1;
+    const double f = (q - x[i]) / (x[i + 1] - x[i]);
+    return (1.0 - f) * y[i] + f * y[i + 1];
+}
+
 __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
     const int m = blockIdx.x;
     const int tid = threadIdx.x;
@@ -93,6 +188,14 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
     const double a0 = avec[0];
     const double kNaN = __longlong_as_double(0x7ff8000000000000LL);
     const bool can_skip = p.cfloor > 0.0;  // 0*up(c) == 0 exactly when c >= cfloor > 0
+    // the fast EGM path needs finite exponents and a positive normal consumption floor
+    const bool model_fast = isfinite(p.neg_gamma) && isfinite(p.oneminusgamma) && isfinite(p.neg_oneover_gamma) &&
+                            isfinite(p.oneover_oneminusgamma) && dc_is_norm_pos(p.cfloor) && p.lambda > 0.0;
+    // knot-index tables alias the envelope's Tx/Ty arrays (free during the EGM step)
+    const int tab0 = S.o_d(3);
+    const int nbuck = knot_index_buckets(2 * P.cap8, 3);
+    const int tab_stride = (nbuck + 8) * 2;
+    __shared__ int s_same;
 
     if (tid == 0) s_status = 0;
 
@@ -158,87 +261,193 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
         const double scale = beq ? p.betaRnu : p.betaR;
         const double* __restrict__ off_t = offm + (size_t)t * 2 * ny;
 
-        // ---------------- 1. EGM step: thread per (choice, grid point) -------------------------------
-        for (int item = tid; item < 2 * na; item += kThreads) {
-            const int id = item >= na;  // 0 worker today, 1 retiree today
-            const int ia = id ? item - na : item;
-            const double a = avec[ia];
-            const double aR = a * p.R;
-            const double* __restrict__ off = off_t + id * ny;
-            const bool need_w = (id == 0) || (p.delta != 0.0);
-            double acc_mu = 0.0, acc_ls = 0.0, acc_v2 = 0.0;
-            for (int iy = 0; iy < ny; iy++) {
-                const double m1 = aR + off[iy];
-                // future retiree (iid = 2): policy and value share their knots
-                const int ir = left_knot(N.r_x(), N.n_r, m1);
-                double c2 = interp_at(N.r_x(), N.rc_y(), N.n_r, ir, m1);
-                c2 = c2 < p.cfloor ? p.cfloor : c2;  // floory! (line.jl:131-139)
-                double v2;
-                if (next_terminal && p.nu > 0)
-                    v2 = p.nu * u_plain(c2 + p.bbar, p) - 0.0;
-                else if (next_terminal || m1 < N.r_x()[1])
-                    v2 = u_work(c2, false, p) + p.beta * N.vb_r;
+        // ---------------- 1. EGM step -----------------------------------------------------------------
+        // fast path: straight-line node evaluation (bucket-indexed knot search, pow from shared
+        // logarithms); see egm_node_generic for the conditions under which it does not apply
+        const bool fast = model_fast && !beq && !(s_status & (DCEGM_ST_NONMONOTONE | DCEGM_ST_NONFINITE)) && N.n_wc >= 2 &&
+                          N.n_wv >= 2 && N.n_r >= 2;
+        KnotIndex Kr, Kc, Kv;
+        Kr.tab = tab0;
+        Kc.tab = tab0 + tab_stride;
+        Kv.tab = tab0 + 2 * tab_stride;
+        Kr.lo = Kc.lo = Kv.lo = Kr.inv = Kc.inv = Kv.inv = Kr.top = Kc.top = Kv.top = 0.0;
+        if (fast) {
+            knot_index_range(Kr, N.r_x(), N.n_r, nbuck);
+            knot_index_range(Kc, N.wc_x(), N.n_wc, nbuck);
+            knot_index_range(Kv, N.wv_x(), N.n_wv, nbuck);
+            knot_index_build(Kr, N.base + 4 * N.cap8, N.n_r, nbuck);
+            knot_index_build(Kc, N.base + 0 * N.cap8, N.n_wc, nbuck);
+            knot_index_build(Kv, N.base + 2 * N.cap8, N.n_wv, nbuck);
+        }
+        if (tid == 0) {  // retiree: do all nodes see the same next-period cash-on-hand?
+            int same = 1;
+            for (int iy = 1; iy < ny; iy++) same &= off_t[ny + iy] == off_t[ny];
+            s_same = same;
+        }
+        __syncthreads();
+        const double rx1 = N.r_x()[1], wvx1 = N.wv_x()[1];
+
+        // ---- worker today (id = 0): thread per savings grid point, serial over the income nodes ----
+        {
+            const double* __restrict__ rX = N.r_x();
+            const double* __restrict__ rC = N.rc_y();
+            const double* __restrict__ rV = N.rv_y();
+            const double* __restrict__ cX = N.wc_x();
+            const double* __restrict__ cY = N.wc_y();
+            const double* __restrict__ vX = N.wv_x();
+            const double* __restrict__ vY = N.wv_y();
+            const int n_r = N.n_r, n_wc = N.n_wc, n_wv = N.n_wv;
+            const double bvb_r = p.beta * N.vb_r, bvb_w = p.beta * N.vb_w;
+            for (int ia = tid; ia < na; ia += kThreads) {
+                const double a = avec[ia];
+                const double aR = a * p.R;
+                double acc_mu = 0.0, acc_ls = 0.0;
+#pragma unroll 1
+                for (int iy = 0; iy < ny; iy++) {
+                    const double m1 = aR + off_t[iy];
+                    double mu, ls;
+                    bool redo = !fast;
+                    if (fast) {
+                        // future retiree (iid = 2): policy and value share their knots
+                        const int nr = count_le_indexed(Kr, rX, n_r, m1);
+                        const int nc = count_le_indexed(Kc, cX, n_wc, m1);
+                        double c2 = interp_cnt(rX, rC, n_r, nr, m1);
+                        double c1 = interp_cnt(cX, cY, n_wc, nc, m1);
+                        c2 = c2 < p.cfloor ? p.cfloor : c2;  // floory! (line.jl:131-139)
+                        c1 = c1 < p.cfloor ? p.cfloor : c1;
+                        redo = !(dc_is_norm_pos(c1) && dc_is_norm_pos(c2));
+                        double l1h, l1l, l2h, l2l;
+                        dc_log_parts_pos(c1, &l1h, &l1l);
+                        dc_log_parts_pos(c2, &l2h, &l2l);
+                        // vfun (dc_algo.jl:220-251): analytic in the credit-constrained region, else interpolated
+                        const bool mask2 = next_terminal || m1 < rx1, mask1 = next_terminal || m1 < wvx1;
+                        double v1 = 0.0, v2 = 0.0;
+                        if (mask1 || mask2) {  // both evaluated together: two independent chains
+                            v1 = u_from_log(l1h, l1l, true, p) + bvb_w;
+                            v2 = u_from_log(l2h, l2l, false, p) + bvb_r;
+                        }
+                        if (!mask2) v2 = interp_cnt(rX, rV, n_r, nr, m1);
+                        if (!mask1) v1 = interp_cnt(vX, vY, n_wv, count_le_indexed(Kv, vX, n_wv, m1), m1);
+                        // ccp / logsum (dc_algo.jl:316-332): the larger value's exp is exp(0) = 1
+                        const bool w_hi = v1 > v2;
+                        const double mx = w_hi ? v1 : v2;
+                        const double d = ((w_hi ? v2 : v1) - mx) / p.lambda;
+                        // marginal utility of the preferred choice
+                        const double u_hi = up_from_log(w_hi ? l1h : l2h, w_hi ? l1l : l2l, w_hi ? c1 : c2, p);
+                        if (can_skip && d < -745.2) {
+                            // the loser's exp underflows to exactly 0: P(work) is 0 or 1, log(1 + 0) = 0
+                            ls = mx + p.lambda * 0.0;
+                            mu = u_hi;
+                        } else {
+                            const double e = dc_exp(d);
+                            const double u_lo = up_from_log(w_hi ? l2h : l1h, w_hi ? l2l : l1l, w_hi ? c2 : c1, p);
+                            const double e1 = w_hi ? 1.0 : e, e2 = w_hi ? e : 1.0;
+                            const double s = e1 + e2;
+                            const double pw = e1 / s;
+                            redo |= !dc_is_norm_pos(s);
+                            double sh, sl;
+                            dc_log_parts_pos(s, &sh, &sl);
+                            ls = mx + p.lambda * (sh + sl);
+                            const double u1 = w_hi ? u_hi : u_lo, u2 = w_hi ? u_lo : u_hi;
+                            mu = pw * u1 + (1.0 - pw) * u2;
+                            mu = (can_skip && pw == 1.0) ? u1 : mu;
+                            mu = (can_skip && pw == 0.0) ? u2 : mu;
+                        }
+                    }
+                    if (redo) {
+                        const LineSet Ncopy = N;
+                        NodeOut o;
+                        egm_node_generic(&Ncopy, &s_p, m1, 0, next_terminal, beq, &o);
+                        mu = o.mu;
+                        ls = o.ls;
+                    }
+                    const double w = wgt[iy];
+                    // quadrature sums, ascending node order (dc_algo.jl:58,74)
+                    acc_mu = iy == 0 ? w * mu : acc_mu + w * mu;
+                    acc_ls = iy == 0 ? w * ls : acc_ls + w * ls;
+                }
+                const double rhs = scale * acc_mu;  // dc_algo.jl:50,58
+                const double c0 = p.gamma_is_one ? 1.0 / rhs : pow_hot(rhs, p.neg_oneover_gamma);  // iup, dc_algo.jl:62
+                const double x = a + c0;
+                double uc;  // u(c0, working), utils.jl:40-46
+                if (p.gamma_is_one)
+                    uc = dc_log(c0) - p.alpha;
                 else
-                    v2 = interp_at(N.r_x(), N.rv_y(), N.n_r, ir, m1);
-                double c1 = 0.0, v1 = 0.0;
-                if (need_w) {
-                    c1 = interp_y(N.wc_x(), N.wc_y(), N.n_wc, m1);
-                    c1 = c1 < p.cfloor ? p.cfloor : c1;
-                    v1 = vfun_dev(true, next_terminal, c1, m1, N.wv_x(), N.wv_y(), N.n_wv, N.vb_w, p);
-                }
-                double pw, ls = 0.0;
-                if (id == 0 || p.delta != 0.0) {
-                    // ccp / logsum (dc_algo.jl:316-332): the larger value's exp is exp(0) = 1
-                    const bool w_hi = v1 > v2;
-                    const double mx = w_hi ? v1 : v2;
-                    const double d = ((w_hi ? v2 : v1) - mx) / p.lambda;
-                    const double e = dc_exp(d);  // exactly 0 below -745.2
-                    const double e1 = w_hi ? 1.0 : e, e2 = w_hi ? e : 1.0;
-                    const double s = e1 + e2;
-                    pw = e1 / s;
-                    ls = mx + p.lambda * dc_log(s);
-                    if (id == 1) pw = p.delta;  // dc_algo.jl:44
-                } else {
-                    pw = p.delta;  // == 0
-                }
-                if (beq) {  // dc_algo.jl:46-48
-                    c1 = c1 + p.bbar;
-                    c2 = c2 + p.bbar;
-                }
-                double mu;
-                if (can_skip && pw == 1.0)
-                    mu = up(c1, p);
-                else if (can_skip && pw == 0.0)
-                    mu = up(c2, p);
-                else
-                    mu = pw * up(c1, p) + (1.0 - pw) * up(c2, p);
-                const double w = wgt[iy];
-                // quadrature sums, ascending node order (dc_algo.jl:58,74)
-                acc_mu = iy == 0 ? w * mu : acc_mu + w * mu;
-                acc_ls = iy == 0 ? w * ls : acc_ls + w * ls;
-                acc_v2 = iy == 0 ? w * v2 : acc_v2 + w * v2;
-            }
-            const double rhs = scale * acc_mu;  // dc_algo.jl:50,58
-            const double c0 = iup(rhs, p);      // dc_algo.jl:62
-            double ev;
-            if (id == 0)
-                ev = acc_ls;  // dc_algo.jl:74
-            else if (p.delta != 0.0)
-                ev = (1.0 - p.delta) * acc_v2 + p.delta * acc_ls;  // dc_algo.jl:76
-            else
-                ev = acc_v2;
-            const double x = a + c0;
-            const double vy = u_work(c0, id == 0, p) + p.beta * ev;  // dc_algo.jl:78
-            if (id == 0) {
+                    uc = p.oneover_oneminusgamma * (pow_hot(c0, p.oneminusgamma) - 1.0) - p.alpha;
+                const double vy = uc + p.beta * acc_ls;  // dc_algo.jl:74,78
                 S.Dx()[koff + ia] = x;
                 S.Dv()[koff + ia] = vy;
                 S.Dc()[koff + ia] = c0;
-            } else {
+                if (ia == 0) s_ev0[0] = acc_ls;
+            }
+        }
+
+        // ---- retiree today (id = 1) ------------------------------------------------------------------
+        {
+            const double* __restrict__ off = off_t + ny;
+            const bool fast_r = fast && p.delta == 0.0 && can_skip;
+            const bool same = s_same && fast_r;  // one evaluation serves all nodes (same inputs, same bits)
+            const double* __restrict__ rX = N.r_x();
+            const double* __restrict__ rC = N.rc_y();
+            const double* __restrict__ rV = N.rv_y();
+            const int n_r = N.n_r;
+            const double bvb_r = p.beta * N.vb_r;
+            for (int ia = tid; ia < na; ia += kThreads) {
+                const double a = avec[ia];
+                const double aR = a * p.R;
+                double acc_mu = 0.0, acc_ls = 0.0, acc_v2 = 0.0;
+                double mu = 0.0, ls = 0.0, v2 = 0.0;
+#pragma unroll 1
+                for (int iy = 0; iy < ny; iy++) {
+                    if (iy == 0 || !same) {
+                        const double m1 = aR + off[iy];
+                        bool redo = !fast_r;
+                        if (fast_r) {
+                            const int nr = count_le_indexed(Kr, rX, n_r, m1);
+                            double c2 = interp_cnt(rX, rC, n_r, nr, m1);
+                            c2 = c2 < p.cfloor ? p.cfloor : c2;
+                            redo = !dc_is_norm_pos(c2);
+                            double l2h, l2l;
+                            dc_log_parts_pos(c2, &l2h, &l2l);
+                            if (next_terminal || m1 < rx1)
+                                v2 = u_from_log(l2h, l2l, false, p) + bvb_r;
+                            else
+                                v2 = interp_cnt(rX, rV, n_r, nr, m1);
+                            mu = up_from_log(l2h, l2l, c2, p);  // P(work) = delta = 0 (dc_algo.jl:44)
+                        }
+                        if (redo) {
+                            const LineSet Ncopy = N;
+                            NodeOut o;
+                            egm_node_generic(&Ncopy, &s_p, m1, 1, next_terminal, beq, &o);
+                            mu = o.mu;
+                            ls = o.ls;
+                            v2 = o.v2;
+                        }
+                    }
+                    const double w = wgt[iy];
+                    acc_mu = iy == 0 ? w * mu : acc_mu + w * mu;
+                    acc_ls = iy == 0 ? w * ls : acc_ls + w * ls;
+                    acc_v2 = iy == 0 ? w * v2 : acc_v2 + w * v2;
+                }
+                const double rhs = scale * acc_mu;
+                const double c0 = p.gamma_is_one ? 1.0 / rhs : pow_hot(rhs, p.neg_oneover_gamma);
+                double ev;
+                if (p.delta != 0.0)
+                    ev = (1.0 - p.delta) * acc_v2 + p.delta * acc_ls;  // dc_algo.jl:76
+                else
+                    ev = acc_v2;
+                const double x = a + c0;
+                double uc;
+                if (p.gamma_is_one)
+                    uc = dc_log(c0) - 0.0;
+                else
+                    uc = p.oneover_oneminusgamma * (pow_hot(c0, p.oneminusgamma) - 1.0) - 0.0;
+                const double vy = uc + p.beta * ev;  // dc_algo.jl:78
                 C.r_x()[1 + ia] = x;
                 C.rc_y()[1 + ia] = c0;
                 C.rv_y()[1 + ia] = vy;
+                if (ia == 0) s_ev0[1] = ev;
             }
-            if (ia == 0) s_ev0[id] = ev;
         }
         __syncthreads();
         const double ev0w = s_ev0[0], ev0r = s_ev0[1];
