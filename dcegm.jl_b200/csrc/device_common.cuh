@@ -67,6 +67,28 @@ __device__ __forceinline__ size_t state_slot(const dcegm_layout& l, int m, int i
 // memory made the compiler fall back to generic LD/ST).
 extern __shared__ __align__(16) unsigned char dc_smem[];
 
+// Phase clocks (profiling builds only, -DDCEGM_PHASE_CLOCKS; see tools/phase_clocks.py): block-wide
+// barrier, then thread 0 adds the cycles since the previous mark to slot i.  Compiles to nothing in
+// the product build.
+#ifdef DCEGM_PHASE_CLOCKS
+constexpr int kPhaseSlots = 16;
+__device__ __forceinline__ long long* dc_clk() {
+    __shared__ long long s[kPhaseSlots + 1];
+    return s;
+}
+#define DC_CLK(i)                                  \
+    do {                                           \
+        __syncthreads();                           \
+        if (threadIdx.x == 0) {                    \
+            long long c_ = clock64();              \
+            dc_clk()[i] += c_ - dc_clk()[kPhaseSlots]; \
+            dc_clk()[kPhaseSlots] = c_;            \
+        }                                          \
+    } while (0)
+#else
+#define DC_CLK(i) do { } while (0)
+#endif
+
 // ---------------------------------------------------------------------------------------------
 // polyline primitives (line.jl:220-254).  Lines live in shared memory as SoA (x[], y[]).
 // ---------------------------------------------------------------------------------------------

@@ -214,6 +214,7 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
     const double* V = S.Dv() + s0;
     const double* Cc = S.Dc() + s0;
     const int n = na + npre;
+    DC_CLK(4);
     if (tid == 0) {
         S.cnt()[0] = 0;
         S.cnt()[1] = 0;
@@ -264,6 +265,7 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
         for (int k = tid; k < n; k += kThreads) S.order()[k] = 0;
         __syncthreads();
 
+        DC_CLK(5);
         // ---- every point: sorted position, winning section, top Point (envelope.jl:154-164) ----
         for (int k = tid; k < n; k += kThreads) {
             const double xk = X[k];
@@ -319,6 +321,7 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
             S.fknot()[k] = knot;
         }
         __syncthreads();
+        DC_CLK(6);
         for (int k = tid; k < n; k += kThreads) S.order()[S.pos()[k]] = (unsigned short)k;
         __syncthreads();
         // unique(xx)
@@ -337,6 +340,7 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
         }
         __syncthreads();
 
+        DC_CLK(7);
         // ---- changes of winner (envelope.jl:173-243) ---------------------------------------------
         for (int j = tid; j < nu; j += kThreads) {
             S.cntI()[j] = 0;
@@ -365,6 +369,7 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
             }
         }
         __syncthreads();
+        DC_CLK(8);
         nis = S.cnt()[1];
         if (nis > S.isec_cap) {
             status |= DCEGM_ST_ISECT_OVERFLOW;
@@ -416,6 +421,7 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
         }
         __syncthreads();
     }
+    DC_CLK(9);
     {
         int local = 0;
         for (int k = tid; k < n; k += kThreads) local += S.frem()[k];
@@ -431,6 +437,7 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
     for (int t = tid; t < S.isec_cap; t += kThreads)
         isects_out[t] = t < nis ? make_double2(S.isl2x()[t], S.isl2y()[t]) : make_double2(0.0, 0.0);
 
+    DC_CLK(5);
     // ---- policy repair (dc_algo.jl:423-493) -----------------------------------------------------
     int ncur;
     if (nrem > 0) {
@@ -550,6 +557,7 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
         ncur = n;
     }
 
+    DC_CLK(10);
     // ---- tail of the step (dc_algo.jl:94-101) ----------------------------------------------------
     if (tid == 0) {
         Vx[0] = a0;

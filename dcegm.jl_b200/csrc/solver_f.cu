@@ -147,25 +147,57 @@ __device__ __forceinline__ double up_from_log(double lh, double ll, double c, co
     if (p.gamma_is_one) return 1.0 / c;
     return dc_pow_from_log(lh, ll, p.neg_gamma);
 }
-// interp (line.jl:220-254), y only, from cnt = number of knots <= q on a strictly increasing line:
-// cnt == 0 <=> q < x[0] and cnt == n <=> q >= x[n-1] go to the general routine (extrapolation)
-static __device__ __noinline__ double interp_edge(const double* x, const double* y, int n, int cnt, double q) {
+// interp (line.jl:220-254), y only, on a strictly increasing finite line, branch-free.  cnt = number
+// of knots <= q.  Interior: f = (q - x0)/(x1 - x0), (1-f) y0 + f y1.  Outside the knots Julia's
+// extrapolate(.., Line()) is y_end + ((y1 - y0)/(x1 - x0)) (q - x_end) on the first / last interval: the
+// same divisor, another numerator — so one reciprocal serves both forms and the choice is a select.
+struct KnotCell {
+    int i;             // left knot of the interval used
+    double x0, x1, r;  // its abscissae, r = 1/(x1 - x0)
+    double dq;         // q - x0 (interior, left of the line) or q - x1 (right of the line)
+    bool lo, ext;      // q < x[0]; q outside [x[0], x[n-1]]
+};
+__device__ __forceinline__ KnotCell knot_cell(const double* __restrict__ x, int n, int cnt, double q) {
+    KnotCell c;
     int i = cnt - 1;
     i = i < 0 ? 0 : i;
     i = i > n - 2 ? n - 2 : i;
-    return interp_at(x, y, n, i, q);
+    c.i = i;
+    c.x0 = x[i];
+    c.x1 = x[i + 1];
+    c.lo = cnt == 0;
+    const bool hi = q > c.x1;  // only possible on the last interval
+    c.ext = c.lo | hi;
+    c.dq = q - (hi ? c.x1 : c.x0);
+    c.r = dc_rcp_fast(c.x1 - c.x0);
+    return c;
+}
+__device__ __forceinline__ double interp_cell(const KnotCell& c, const double* __restrict__ y) {
+    const double y0 = y[c.i], y1 = y[c.i + 1];
+    const double d = c.x1 - c.x0;
+    const double t = dc_div_with_rcp(c.ext ? y1 - y0 : c.dq, d, c.r);
+    const double inner = (1.0 - t) * y0 + t * y1;
+    const double outer = (c.lo ? y0 : y1) + t * c.dq;
+    return c.ext ? outer : inner;
 }
 __device__ __forceinline__ double interp_cnt(const double* __restrict__ x, const double* __restrict__ y, int n, int cnt,
                                              double q) {
-    if (cnt == 0 || cnt == n) return interp_edge(x, y, n, cnt, q);
-    const int i = cnt - 1;
-    const double f = (q - x[i]) / (x[i + 1] - x[i]);
-    return (1.0 - f) * y[i] + f * y[i + 1];
+    return interp_cell(knot_cell(x, n, cnt, q), y);
 }
+
+#ifdef DCEGM_PHASE_CLOCKS
+__device__ unsigned long long dc_phase_total[kPhaseSlots];
+#endif
 
 __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
     const int m = blockIdx.x;
     const int tid = threadIdx.x;
+#ifdef DCEGM_PHASE_CLOCKS
+    if (tid == 0) {
+        for (int i = 0; i < kPhaseSlots; i++) dc_clk()[i] = 0;
+        dc_clk()[kPhaseSlots] = clock64();
+    }
+#endif
     __shared__ DevModel s_p;
     if (tid == 0) s_p = B.models[m];
     __syncthreads();
@@ -190,7 +222,7 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
     const bool can_skip = p.cfloor > 0.0;  // 0*up(c) == 0 exactly when c >= cfloor > 0
     // the fast EGM path needs finite exponents and a positive normal consumption floor
     const bool model_fast = isfinite(p.neg_gamma) && isfinite(p.oneminusgamma) && isfinite(p.neg_oneover_gamma) &&
-                            isfinite(p.oneover_oneminusgamma) && dc_is_norm_pos(p.cfloor) && p.lambda > 0.0;
+                            isfinite(p.oneover_oneminusgamma) && dc_is_norm_pos(p.cfloor) && p.lambda > 1e-100 && p.lambda < 1e100;
     // knot-index tables alias the envelope's Tx/Ty arrays (free during the EGM step)
     const int tab0 = S.o_d(3);
     const int nbuck = knot_index_buckets(2 * P.cap8, 3);
@@ -256,6 +288,7 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
             continue;
         }
 
+        DC_CLK(0);
         const bool next_terminal = (t + 1 == nT - 1);
         const bool beq = (t == nT - 2) && p.nu > 0;
         const double scale = beq ? p.betaRnu : p.betaR;
@@ -285,6 +318,7 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
             s_same = same;
         }
         __syncthreads();
+        DC_CLK(1);
         const double rx1 = N.r_x()[1], wvx1 = N.wv_x()[1];
 
         // ---- worker today (id = 0): thread per savings grid point, serial over the income nodes ----
@@ -311,7 +345,8 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
                         // future retiree (iid = 2): policy and value share their knots
                         const int nr = count_le_indexed(Kr, rX, n_r, m1);
                         const int nc = count_le_indexed(Kc, cX, n_wc, m1);
-                        double c2 = interp_cnt(rX, rC, n_r, nr, m1);
+                        const KnotCell kr = knot_cell(rX, n_r, nr, m1);
+                        double c2 = interp_cell(kr, rC);
                         double c1 = interp_cnt(cX, cY, n_wc, nc, m1);
                         c2 = c2 < p.cfloor ? p.cfloor : c2;  // floory! (line.jl:131-139)
                         c1 = c1 < p.cfloor ? p.cfloor : c1;
@@ -326,12 +361,12 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
                             v1 = u_from_log(l1h, l1l, true, p) + bvb_w;
                             v2 = u_from_log(l2h, l2l, false, p) + bvb_r;
                         }
-                        if (!mask2) v2 = interp_cnt(rX, rV, n_r, nr, m1);
+                        if (!mask2) v2 = interp_cell(kr, rV);
                         if (!mask1) v1 = interp_cnt(vX, vY, n_wv, count_le_indexed(Kv, vX, n_wv, m1), m1);
                         // ccp / logsum (dc_algo.jl:316-332): the larger value's exp is exp(0) = 1
                         const bool w_hi = v1 > v2;
                         const double mx = w_hi ? v1 : v2;
-                        const double d = ((w_hi ? v2 : v1) - mx) / p.lambda;
+                        const double d = dc_div_fast((w_hi ? v2 : v1) - mx, p.lambda);
                         // marginal utility of the preferred choice
                         const double u_hi = up_from_log(w_hi ? l1h : l2h, w_hi ? l1l : l2l, w_hi ? c1 : c2, p);
                         if (can_skip && d < -745.2) {
@@ -343,7 +378,7 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
                             const double u_lo = up_from_log(w_hi ? l2h : l1h, w_hi ? l2l : l1l, w_hi ? c2 : c1, p);
                             const double e1 = w_hi ? 1.0 : e, e2 = w_hi ? e : 1.0;
                             const double s = e1 + e2;
-                            const double pw = e1 / s;
+                            const double pw = dc_div_fast(e1, s);  // s in [1, 2]
                             redo |= !dc_is_norm_pos(s);
                             double sh, sl;
                             dc_log_parts_pos(s, &sh, &sl);
@@ -382,6 +417,7 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
             }
         }
 
+        DC_CLK(2);
         // ---- retiree today (id = 1) ------------------------------------------------------------------
         {
             const double* __restrict__ off = off_t + ny;
@@ -404,7 +440,8 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
                         bool redo = !fast_r;
                         if (fast_r) {
                             const int nr = count_le_indexed(Kr, rX, n_r, m1);
-                            double c2 = interp_cnt(rX, rC, n_r, nr, m1);
+                            const KnotCell kr = knot_cell(rX, n_r, nr, m1);
+                            double c2 = interp_cell(kr, rC);
                             c2 = c2 < p.cfloor ? p.cfloor : c2;
                             redo = !dc_is_norm_pos(c2);
                             double l2h, l2l;
@@ -412,7 +449,7 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
                             if (next_terminal || m1 < rx1)
                                 v2 = u_from_log(l2h, l2l, false, p) + bvb_r;
                             else
-                                v2 = interp_cnt(rX, rV, n_r, nr, m1);
+                                v2 = interp_cell(kr, rV);
                             mu = up_from_log(l2h, l2l, c2, p);  // P(work) = delta = 0 (dc_algo.jl:44)
                         }
                         if (redo) {
@@ -450,6 +487,7 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
             }
         }
         __syncthreads();
+        DC_CLK(3);
         const double ev0w = s_ev0[0], ev0r = s_ev0[1];
 
         if (B.dirty) {  // runfdemo: vdirty / cdirty (dc_algo.jl:79-82)
@@ -470,6 +508,7 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
         C.n_wv = s_n[0];
         C.n_wc = s_n[1];
         C.vb_w = ev0w;
+        DC_CLK(12);
 
         // ---------------- 3. retiree: credit-constraint point and checks (dc_algo.jl:90-101) --------
         if (tid == 0) {
@@ -506,6 +545,7 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
             sum_pts += C.n_wc + C.n_wv + 2 * C.n_r;
         }
         __syncthreads();
+        DC_CLK(13);
         {
             const LineSet tmp = N;
             N = C;
@@ -559,7 +599,24 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
         B.summaries[m] = sm;
         B.status[m] = s_status;
     }
+#ifdef DCEGM_PHASE_CLOCKS
+    DC_CLK(14);
+    if (tid == 0)
+        for (int i = 0; i < kPhaseSlots; i++) atomicAdd(&dc_phase_total[i], (unsigned long long)dc_clk()[i]);
+#endif
 }
+
+#ifdef DCEGM_PHASE_CLOCKS
+// profiling builds only: cycles per phase summed over all CTAs since the last reset
+extern "C" int dcegm_debug_phase_clocks(unsigned long long* out, int reset) {
+    if (out && cudaMemcpyFromSymbol(out, dc_phase_total, sizeof(unsigned long long) * kPhaseSlots) != cudaSuccess) return -2;
+    if (reset) {
+        unsigned long long z[kPhaseSlots] = {0};
+        if (cudaMemcpyToSymbol(dc_phase_total, z, sizeof z) != cudaSuccess) return -2;
+    }
+    return 0;
+}
+#endif
 
 cudaError_t launch_solve_f(const DeviceBatch& B, cudaStream_t stream) {
     const size_t smem = FPlan(B.lay.cap, B.lay.isec_cap).bytes();

@@ -119,4 +119,48 @@ cudaError_t launch_pack_lines(const DeviceBatch& B, int first, int count, const 
     return cudaGetLastError();
 }
 
+// ---- diagnostics: device arithmetic of dc_math.h against the IEEE operations -------------------
+// Operands are drawn (counter-based splitmix64) from the ranges the solver kernels use; which[0]
+// counts dc_div_fast(a,b) != a/b, which[1] dc_rcp_fast(b) != 1/b.
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+    z += 0x9e3779b97f4a7c15ULL;
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL;
+    z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
+    return z ^ (z >> 31);
+}
+__global__ void math_check_kernel(unsigned long long n, unsigned long long seed, int emin, int emax,
+                                  unsigned long long* which) {
+    unsigned long long bad_div = 0, bad_rcp = 0;
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned long long u = mix64(seed + 3 * i), v = mix64(seed + 3 * i + 1), w = mix64(seed + 3 * i + 2);
+        const int span = emax - emin + 1;
+        const long long ea = emin + (long long)(w % (unsigned)span), eb = emin + (long long)((w >> 20) % (unsigned)span);
+        double a = __longlong_as_double(((ea + 1023) << 52) | (long long)(u >> 12));
+        double b = __longlong_as_double(((eb + 1023) << 52) | (long long)(v >> 12));
+        if (w >> 63) a = -a;
+        if ((w >> 62) & 1) b = -b;
+        if (((w >> 40) & 1023) == 0) a = 0.0;          // exact hits of a knot
+        if (((w >> 50) & 255) == 0) a = b * (double)((u >> 60) + 1);  // exact quotients
+        bad_div += dc_div_fast(a, b) != a / b;
+        bad_rcp += dc_rcp_fast(b) != 1.0 / b;
+    }
+    if (bad_div) atomicAdd(&which[0], bad_div);
+    if (bad_rcp) atomicAdd(&which[1], bad_rcp);
+}
+
 }  // namespace dcegm
+
+extern "C" int dcegm_debug_math_check(unsigned long long n, unsigned long long seed, int emin, int emax,
+                                      unsigned long long* mismatches2) {
+    if (!mismatches2 || emin < -1000 || emax > 1000 || emin > emax) return DCEGM_E_INVALID;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return DCEGM_E_NODEVICE;
+    unsigned long long* d = nullptr;
+    if (cudaMalloc(&d, 16) != cudaSuccess) return DCEGM_E_CUDA;
+    cudaMemset(d, 0, 16);
+    dcegm::math_check_kernel<<<148 * 8, 256>>>(n, seed, emin, emax, d);
+    cudaError_t e = cudaMemcpy(mismatches2, d, 16, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    return e == cudaSuccess ? DCEGM_OK : DCEGM_E_CUDA;
+}

@@ -231,6 +231,13 @@ int  dcegm_upload_g(dcegm_handle h, const dcegm_param* params, int nmodels, unsi
 int  dcegm_upload_minimal(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
 int  dcegm_run(dcegm_handle h);
 
+/* ---- diagnostics ---------------------------------------------------------------------
+ * Runs n random operand pairs with binary exponents in [emin, emax] (plus exact zeros and exact
+ * quotients) through the kernels' branch-free division / reciprocal (csrc/dc_math.h) and counts
+ * results that differ from the IEEE operations: mismatches2[0] divisions, [1] reciprocals. */
+int  dcegm_debug_math_check(unsigned long long n, unsigned long long seed, int emin, int emax,
+                            unsigned long long* mismatches2);
+
 #ifdef __cplusplus
 }
 #endif
