@@ -8,7 +8,8 @@ import os
 from . import _abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libdcegm_cuda.so")
+# DCEGM_CUDA_LIB selects another build of the same library (kernel A/B experiments, profiling build)
+LIB_PATH = os.environ.get("DCEGM_CUDA_LIB") or os.path.join(_HERE, "csrc", "libdcegm_cuda.so")
 _lib = None
 
 EXPORTS = [

@@ -84,6 +84,7 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
     const int na = params[0].na, ny = params[0].ny, nT = params[0].nT;
     dcegm_layout lay;
     make_layout(model, nmodels, na, ny, nT, (flags & DCEGM_KEEP_DIRTY) ? 1 : 0, (flags & DCEGM_SUMMARY_ONLY) ? 0 : 1, &lay);
+    if (model == DCEGM_MODEL_F && ny > kMaxNy) return fail(h, DCEGM_E_INVALID, "ny > 64 is not supported by the retirement-model solver");
     if (lay.cap >= 2 * kSearchTop) return fail(h, DCEGM_E_INVALID, "na too large for the shared-memory resident solver");
     size_t smem = model == DCEGM_MODEL_F   ? solver_f_smem_bytes(lay.cap, lay.isec_cap)
                   : model == DCEGM_MODEL_G ? solver_g_smem_bytes(lay.cap, lay.isec_cap, na, ny)

@@ -112,10 +112,12 @@ __device__ __forceinline__ double seg_interp_y(const SegView& v, double q) {
     return (1.0 - f) * seg_y(v, i) + f * seg_y(v, i + 1);
 }
 
-// One change of winner between union-grid cells j-1 and j (envelope.jl:174-243).  Returns the
-// number of intersections found; points go to px/py (at most kSwitchMaxIsect are stored).
+// One change of winner between union-grid cells j-1 and j (envelope.jl:174-243), resolved by one
+// warp: all lanes follow the same control flow, the scan over all sections is split across lanes.
+// Returns the number of intersections found; points go to px/py (at most kSwitchMaxIsect are stored).
 __device__ inline int resolve_switch(const EnvScratch& S, const double* X, const double* V, int nseg, int k0, int k1,
                                      double xl, double xr, double* px, double* py, unsigned* status) {
+    const int lane = threadIdx.x & 31;
     int ln1 = k0, ln2 = k1;
     double pt1 = xl, pt2 = xr;
     SegView A = seg_view(S, X, V, ln1), B = seg_view(S, X, V, ln2);
@@ -149,16 +151,34 @@ __device__ inline int resolve_switch(const EnvScratch& S, const double* X, const
             if (pt3 < pt1) pt3 = pt1;
             if (pt3 > pt2) pt3 = pt2;
         }
-        // all sections at pt3, extrap=false, first arg-max (envelope.jl:205-206)
-        int ln3 = -1;
-        double y3 = 0.0;
-        for (int s = 0; s < nseg; s++) {
+        // all sections at pt3, extrap=false, first arg-max (envelope.jl:205-206): the lanes of the warp
+        // share the sections; ties go to the lowest index and a NaN only wins as section 0, exactly
+        // like the sequential scan `if (ln3 < 0 || y > y3)`
+        int ln3 = 0x7fffffff;
+        double y3 = -CUDART_INF, y_first = 0.0;
+        for (int s = lane; s < nseg; s += 32) {
             SegView C = seg_view(S, X, V, s);
             double y = seg_in_domain(C, pt3) ? seg_interp_y(C, pt3) : -CUDART_INF;
-            if (ln3 < 0 || y > y3) {
+            if (s == 0) y_first = y;
+            if (y != y) y = -CUDART_INF;
+            if (y > y3 || ln3 == 0x7fffffff) {
                 y3 = y;
                 ln3 = s;
             }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double yo = __shfl_xor_sync(0xffffffffu, y3, o);
+            const int so = __shfl_xor_sync(0xffffffffu, ln3, o);
+            if (yo > y3 || (yo == y3 && so < ln3)) {
+                y3 = yo;
+                ln3 = so;
+            }
+        }
+        y_first = __shfl_sync(0xffffffffu, y_first, 0);
+        if (y_first != y_first) {
+            ln3 = 0;
+            y3 = y_first;
         }
         if (ln3 == ln2 || ln3 == ln1) {
             if (cnt < kSwitchMaxIsect) {
@@ -351,11 +371,12 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
         }
         __syncthreads();
         const int nsw = S.cnt()[0];
-        for (int t = tid; t < nsw; t += kThreads) {
+        for (int t = tid >> 5; t < nsw; t += kWarps) {  // warp per change of winner
             const int j = S.swj()[t];
             double px[kSwitchMaxIsect], py[kSwitchMaxIsect];
             int c = resolve_switch(S, X, V, nseg, S.win()[S.ord2()[j - 1]], S.win()[S.ord2()[j]], X[S.ord2()[j - 1]], X[S.ord2()[j]],
                                    px, py, &status);
+            if ((tid & 31) != 0) c = 0;  // lane 0 publishes
             if (c > 0) {
                 int base = atomicAdd(&S.cnt()[1], c);
                 for (int q = 0; q < c; q++) {

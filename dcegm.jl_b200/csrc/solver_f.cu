@@ -137,6 +137,19 @@ __device__ __forceinline__ double pow_hot(double x, double y) {
     dc_log_parts_pos(x, &lh, &ll);
     return dc_pow_from_log(lh, ll, y);
 }
+// two powers with one exponent, evaluated together (independent chains interleave); one cold branch
+__device__ __forceinline__ void pow_hot2(double x1, double x2, double y, double* r1, double* r2) {
+    const bool ok = dc_is_norm_pos(x1) && dc_is_norm_pos(x2);
+    double h1, l1, h2, l2;
+    dc_log_parts_pos(ok ? x1 : 1.0, &h1, &l1);
+    dc_log_parts_pos(ok ? x2 : 1.0, &h2, &l2);
+    *r1 = dc_pow_from_log(h1, l1, y);
+    *r2 = dc_pow_from_log(h2, l2, y);
+    if (!ok) {
+        *r1 = dc_pow_cold(x1, y);
+        *r2 = dc_pow_cold(x2, y);
+    }
+}
 // utils.jl:40-46 / 72-78 from ln c = lh + ll (c positive normal)
 __device__ __forceinline__ double u_from_log(double lh, double ll, bool working, const DevModel& p) {
     const double dis = working ? p.alpha : 0.0;
@@ -227,7 +240,12 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
     const int tab0 = S.o_d(3);
     const int nbuck = knot_index_buckets(2 * P.cap8, 3);
     const int tab_stride = (nbuck + 8) * 2;
-    __shared__ int s_same;
+    // this period's income offsets and the quadrature weights, staged once (the EGM loops read them per node)
+    __shared__ double s_off[2 * kMaxNy], s_wgt[kMaxNy];
+    if (tid < ny) s_wgt[tid] = wgt[tid];
+    // this thread's savings grid points stay in registers across the periods
+    const double a_reg0 = tid < na ? avec[tid] : 0.0;
+    const double a_reg1 = tid + kThreads < na ? avec[tid + kThreads] : 0.0;
 
     if (tid == 0) s_status = 0;
 
@@ -292,7 +310,7 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
         const bool next_terminal = (t + 1 == nT - 1);
         const bool beq = (t == nT - 2) && p.nu > 0;
         const double scale = beq ? p.betaRnu : p.betaR;
-        const double* __restrict__ off_t = offm + (size_t)t * 2 * ny;
+        if (tid < 2 * ny) s_off[tid] = offm[(size_t)t * 2 * ny + tid];  // visible after the barrier below
 
         // ---------------- 1. EGM step -----------------------------------------------------------------
         // fast path: straight-line node evaluation (bucket-indexed knot search, pow from shared
@@ -308,20 +326,20 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
             knot_index_range(Kr, N.r_x(), N.n_r, nbuck);
             knot_index_range(Kc, N.wc_x(), N.n_wc, nbuck);
             knot_index_range(Kv, N.wv_x(), N.n_wv, nbuck);
-            knot_index_build(Kr, N.base + 4 * N.cap8, N.n_r, nbuck);
-            knot_index_build(Kc, N.base + 0 * N.cap8, N.n_wc, nbuck);
-            knot_index_build(Kv, N.base + 2 * N.cap8, N.n_wv, nbuck);
-        }
-        if (tid == 0) {  // retiree: do all nodes see the same next-period cash-on-hand?
-            int same = 1;
-            for (int iy = 1; iy < ny; iy++) same &= off_t[ny + iy] == off_t[ny];
-            s_same = same;
+            const int nmax = max(N.n_r, max(N.n_wc, N.n_wv));
+            for (int k = tid; k < nmax; k += kThreads) {  // the three tables in one pass
+                if (k < N.n_r) knot_index_build_step(Kr, N.r_x(), N.n_r, nbuck, k);
+                if (k < N.n_wc) knot_index_build_step(Kc, N.wc_x(), N.n_wc, nbuck, k);
+                if (k < N.n_wv) knot_index_build_step(Kv, N.wv_x(), N.n_wv, nbuck, k);
+            }
         }
         __syncthreads();
         DC_CLK(1);
+        bool same_nodes = true;  // retiree: do all nodes see the same next-period cash-on-hand?
+        for (int iy = 1; iy < ny; iy++) same_nodes &= s_off[ny + iy] == s_off[ny];
         const double rx1 = N.r_x()[1], wvx1 = N.wv_x()[1];
 
-        // ---- worker today (id = 0): thread per savings grid point, serial over the income nodes ----
+        // ---- thread per savings grid point: worker today (id = 0), serial over the income nodes ----
         {
             const double* __restrict__ rX = N.r_x();
             const double* __restrict__ rC = N.rc_y();
@@ -332,13 +350,15 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
             const double* __restrict__ vY = N.wv_y();
             const int n_r = N.n_r, n_wc = N.n_wc, n_wv = N.n_wv;
             const double bvb_r = p.beta * N.vb_r, bvb_w = p.beta * N.vb_w;
+            const bool fast_r = fast && p.delta == 0.0 && can_skip;
+            const bool same = same_nodes && fast_r;  // one evaluation serves all nodes (same inputs, same bits)
             for (int ia = tid; ia < na; ia += kThreads) {
-                const double a = avec[ia];
+                const double a = ia == tid ? a_reg0 : (ia == tid + kThreads ? a_reg1 : avec[ia]);
                 const double aR = a * p.R;
                 double acc_mu = 0.0, acc_ls = 0.0;
 #pragma unroll 1
                 for (int iy = 0; iy < ny; iy++) {
-                    const double m1 = aR + off_t[iy];
+                    const double m1 = aR + s_off[iy];
                     double mu, ls;
                     bool redo = !fast;
                     if (fast) {
@@ -396,96 +416,86 @@ __global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
                         mu = o.mu;
                         ls = o.ls;
                     }
-                    const double w = wgt[iy];
+                    const double w = s_wgt[iy];
                     // quadrature sums, ascending node order (dc_algo.jl:58,74)
                     acc_mu = iy == 0 ? w * mu : acc_mu + w * mu;
                     acc_ls = iy == 0 ? w * ls : acc_ls + w * ls;
                 }
-                const double rhs = scale * acc_mu;  // dc_algo.jl:50,58
-                const double c0 = p.gamma_is_one ? 1.0 / rhs : pow_hot(rhs, p.neg_oneover_gamma);  // iup, dc_algo.jl:62
-                const double x = a + c0;
-                double uc;  // u(c0, working), utils.jl:40-46
-                if (p.gamma_is_one)
-                    uc = dc_log(c0) - p.alpha;
-                else
-                    uc = p.oneover_oneminusgamma * (pow_hot(c0, p.oneminusgamma) - 1.0) - p.alpha;
-                const double vy = uc + p.beta * acc_ls;  // dc_algo.jl:74,78
-                S.Dx()[koff + ia] = x;
-                S.Dv()[koff + ia] = vy;
-                S.Dc()[koff + ia] = c0;
-                if (ia == 0) s_ev0[0] = acc_ls;
-            }
-        }
-
-        DC_CLK(2);
-        // ---- retiree today (id = 1) ------------------------------------------------------------------
-        {
-            const double* __restrict__ off = off_t + ny;
-            const bool fast_r = fast && p.delta == 0.0 && can_skip;
-            const bool same = s_same && fast_r;  // one evaluation serves all nodes (same inputs, same bits)
-            const double* __restrict__ rX = N.r_x();
-            const double* __restrict__ rC = N.rc_y();
-            const double* __restrict__ rV = N.rv_y();
-            const int n_r = N.n_r;
-            const double bvb_r = p.beta * N.vb_r;
-            for (int ia = tid; ia < na; ia += kThreads) {
-                const double a = avec[ia];
-                const double aR = a * p.R;
-                double acc_mu = 0.0, acc_ls = 0.0, acc_v2 = 0.0;
-                double mu = 0.0, ls = 0.0, v2 = 0.0;
+                // ---- retiree today (id = 1) at the same grid point ------------------------------------
+                double acc_mu_r = 0.0, acc_ls_r = 0.0, acc_v2 = 0.0;
+                {
+                    double mu = 0.0, ls = 0.0, v2 = 0.0;
 #pragma unroll 1
-                for (int iy = 0; iy < ny; iy++) {
-                    if (iy == 0 || !same) {
-                        const double m1 = aR + off[iy];
-                        bool redo = !fast_r;
-                        if (fast_r) {
-                            const int nr = count_le_indexed(Kr, rX, n_r, m1);
-                            const KnotCell kr = knot_cell(rX, n_r, nr, m1);
-                            double c2 = interp_cell(kr, rC);
-                            c2 = c2 < p.cfloor ? p.cfloor : c2;
-                            redo = !dc_is_norm_pos(c2);
-                            double l2h, l2l;
-                            dc_log_parts_pos(c2, &l2h, &l2l);
-                            if (next_terminal || m1 < rx1)
-                                v2 = u_from_log(l2h, l2l, false, p) + bvb_r;
-                            else
-                                v2 = interp_cell(kr, rV);
-                            mu = up_from_log(l2h, l2l, c2, p);  // P(work) = delta = 0 (dc_algo.jl:44)
+                    for (int iy = 0; iy < ny; iy++) {
+                        if (iy == 0 || !same) {
+                            const double m1 = aR + s_off[ny + iy];
+                            bool redo = !fast_r;
+                            if (fast_r) {
+                                const int nr = count_le_indexed(Kr, rX, n_r, m1);
+                                const KnotCell kr = knot_cell(rX, n_r, nr, m1);
+                                double c2 = interp_cell(kr, rC);
+                                c2 = c2 < p.cfloor ? p.cfloor : c2;
+                                redo = !dc_is_norm_pos(c2);
+                                double l2h, l2l;
+                                dc_log_parts_pos(c2, &l2h, &l2l);
+                                if (next_terminal || m1 < rx1)
+                                    v2 = u_from_log(l2h, l2l, false, p) + bvb_r;
+                                else
+                                    v2 = interp_cell(kr, rV);
+                                mu = up_from_log(l2h, l2l, c2, p);  // P(work) = delta = 0 (dc_algo.jl:44)
+                            }
+                            if (redo) {
+                                const LineSet Ncopy = N;
+                                NodeOut o;
+                                egm_node_generic(&Ncopy, &s_p, m1, 1, next_terminal, beq, &o);
+                                mu = o.mu;
+                                ls = o.ls;
+                                v2 = o.v2;
+                            }
                         }
-                        if (redo) {
-                            const LineSet Ncopy = N;
-                            NodeOut o;
-                            egm_node_generic(&Ncopy, &s_p, m1, 1, next_terminal, beq, &o);
-                            mu = o.mu;
-                            ls = o.ls;
-                            v2 = o.v2;
-                        }
+                        const double w = s_wgt[iy];
+                        acc_mu_r = iy == 0 ? w * mu : acc_mu_r + w * mu;
+                        acc_ls_r = iy == 0 ? w * ls : acc_ls_r + w * ls;
+                        acc_v2 = iy == 0 ? w * v2 : acc_v2 + w * v2;
                     }
-                    const double w = wgt[iy];
-                    acc_mu = iy == 0 ? w * mu : acc_mu + w * mu;
-                    acc_ls = iy == 0 ? w * ls : acc_ls + w * ls;
-                    acc_v2 = iy == 0 ? w * v2 : acc_v2 + w * v2;
                 }
-                const double rhs = scale * acc_mu;
-                const double c0 = p.gamma_is_one ? 1.0 / rhs : pow_hot(rhs, p.neg_oneover_gamma);
+                // ---- Euler inversion and today's values, both choices together (dc_algo.jl:50-78) -----
+                const double rhs_w = scale * acc_mu, rhs_r = scale * acc_mu_r;
+                double c0_w, c0_r, pw_w, pw_r;  // iup (dc_algo.jl:62), c0^(1-gamma)
+                if (p.gamma_is_one) {
+                    c0_w = 1.0 / rhs_w;
+                    c0_r = 1.0 / rhs_r;
+                    pw_w = pw_r = 0.0;
+                } else {
+                    pow_hot2(rhs_w, rhs_r, p.neg_oneover_gamma, &c0_w, &c0_r);
+                    pow_hot2(c0_w, c0_r, p.oneminusgamma, &pw_w, &pw_r);
+                }
+                double uc_w, uc_r;  // u(c0, working), utils.jl:40-46
+                if (p.gamma_is_one) {
+                    uc_w = dc_log(c0_w) - p.alpha;
+                    uc_r = dc_log(c0_r) - 0.0;
+                } else {
+                    uc_w = p.oneover_oneminusgamma * (pw_w - 1.0) - p.alpha;
+                    uc_r = p.oneover_oneminusgamma * (pw_r - 1.0) - 0.0;
+                }
                 double ev;
                 if (p.delta != 0.0)
-                    ev = (1.0 - p.delta) * acc_v2 + p.delta * acc_ls;  // dc_algo.jl:76
+                    ev = (1.0 - p.delta) * acc_v2 + p.delta * acc_ls_r;  // dc_algo.jl:76
                 else
                     ev = acc_v2;
-                const double x = a + c0;
-                double uc;
-                if (p.gamma_is_one)
-                    uc = dc_log(c0) - 0.0;
-                else
-                    uc = p.oneover_oneminusgamma * (pow_hot(c0, p.oneminusgamma) - 1.0) - 0.0;
-                const double vy = uc + p.beta * ev;  // dc_algo.jl:78
-                C.r_x()[1 + ia] = x;
-                C.rc_y()[1 + ia] = c0;
-                C.rv_y()[1 + ia] = vy;
-                if (ia == 0) s_ev0[1] = ev;
+                S.Dx()[koff + ia] = a + c0_w;
+                S.Dv()[koff + ia] = uc_w + p.beta * acc_ls;  // dc_algo.jl:74,78
+                S.Dc()[koff + ia] = c0_w;
+                C.r_x()[1 + ia] = a + c0_r;
+                C.rc_y()[1 + ia] = c0_r;
+                C.rv_y()[1 + ia] = uc_r + p.beta * ev;  // dc_algo.jl:78
+                if (ia == 0) {
+                    s_ev0[0] = acc_ls;
+                    s_ev0[1] = ev;
+                }
             }
         }
+        DC_CLK(2);
         __syncthreads();
         DC_CLK(3);
         const double ev0w = s_ev0[0], ev0r = s_ev0[1];

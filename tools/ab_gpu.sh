@@ -1,0 +1,6 @@
+#!/bin/bash
+# A/B of two builds of the library on the C3 bench (value only), alternating runs
+for i in 1 2; do
+for lib in libdcegm_cuda.so libdcegm_cuda_var.so; do
+DCEGM_CUDA_LIB=$PWD/dcegm.jl_b200/csrc/$lib python bench.py --no-cpu --steps 5 2>&1 | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('$lib','value',round(d['value']),'ms',round(d['ms_per_step'],2))"
+done; done
