@@ -233,9 +233,8 @@ def main():
     h2d = C.sizeof(arr) + 8 * (lay.nT - 1) * 2 * lay.ny * nper + 8 * lay.ny * nper + 8 * lay.na + 200 * nper
 
     def e2e_step():
-        rc = lib.dcegm_solve_f(h, arr, nper, 0)
-        assert rc == 0, lib.dcegm_last_error(h)
-        rc = lib.dcegm_fetch_packed(h, 0, nper, C.cast(pinned, C.POINTER(C.c_double)), cap_pts, op, C.byref(npts))
+        # one public call: host setup + H2D + chunked solve, packing and D2H overlapped with the kernels
+        rc = lib.dcegm_solve_f_packed(h, arr, nper, 0, C.cast(pinned, C.POINTER(C.c_double)), cap_pts, op, C.byref(npts))
         assert rc == 0, lib.dcegm_last_error(h)
         lib.dcegm_status(h, stat_h.ctypes.data_as(C.POINTER(C.c_int32)))
         return npts.value * 16 + nslots * 4 + nper * 4

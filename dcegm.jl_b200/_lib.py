@@ -18,7 +18,7 @@ EXPORTS = [
     "dcegm_get_layout", "dcegm_fetch_line", "dcegm_fetch_lines", "dcegm_fetch_lens", "dcegm_fetch_vbound",
     "dcegm_fetch_meta", "dcegm_fetch_isects", "dcegm_fetch_removed", "dcegm_fetch_dirty", "dcegm_fetch_packed",
     "dcegm_status", "dcegm_summaries", "dcegm_summaries_to_device", "dcegm_last_timing", "dcegm_upload_f",
-    "dcegm_upload_g", "dcegm_upload_minimal", "dcegm_run", "dcegm_debug_math_check",
+    "dcegm_upload_g", "dcegm_upload_minimal", "dcegm_run", "dcegm_debug_math_check", "dcegm_solve_f_packed", "dcegm_solve_g_packed",
 ]
 
 
@@ -52,6 +52,8 @@ def load():
     for f in ("dcegm_solve_f", "dcegm_solve_g", "dcegm_solve_minimal", "dcegm_upload_f", "dcegm_upload_g",
               "dcegm_upload_minimal"):
         getattr(lib, f).argtypes = [H, PP, C.c_int, C.c_uint]
+    for f in ("dcegm_solve_f_packed", "dcegm_solve_g_packed"):
+        getattr(lib, f).argtypes = [H, PP, C.c_int, C.c_uint, dp, C.c_size_t, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     lib.dcegm_run.argtypes = [H]
     lib.dcegm_get_layout.argtypes = [H, C.POINTER(_abi.dcegm_layout)]
     lib.dcegm_fetch_line.argtypes = [H, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, dp, C.c_int, C.POINTER(C.c_int)]

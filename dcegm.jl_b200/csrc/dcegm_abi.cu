@@ -14,9 +14,9 @@
 #include "host_setup.hpp"
 
 namespace dcegm {
-cudaError_t launch_solve_f(const DeviceBatch& B, cudaStream_t stream);
-cudaError_t launch_solve_g(const DeviceBatch& B, cudaStream_t stream);
-cudaError_t launch_solve_minimal(const DeviceBatch& B, cudaStream_t stream);
+cudaError_t launch_solve_f(const DeviceBatch& B, int first, int count, cudaStream_t stream);
+cudaError_t launch_solve_g(const DeviceBatch& B, int first, int count, cudaStream_t stream);
+cudaError_t launch_solve_minimal(const DeviceBatch& B, int first, int count, cudaStream_t stream);
 cudaError_t launch_pack_lines(const DeviceBatch& B, int first, int count, const long long* d_offsets, double2* d_dst,
                               cudaStream_t stream);
 size_t solver_f_smem_bytes(int cap, int isec_cap);
@@ -33,7 +33,13 @@ struct DevBuf {
 struct dcegm_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t s_pack = nullptr, s_copy = nullptr;  // pipelined solve-to-host: packing and D2H streams
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    std::vector<cudaEvent_t> ev_pool;                 // per-chunk events of the pipelined solve
+    int32_t* pin_lens = nullptr;                      // pinned staging: one chunk of lens / offsets
+    long long* pin_off = nullptr;
+    size_t pin_slots = 0;
+    DevBuf pack_xy2;
     std::string err;
     DevBuf models, grids, off, wgt, lines, lens, vbound, meta, isects, removed, dirty, status, summaries, pack_off, pack_xy;
     DeviceBatch batch{};
@@ -146,6 +152,12 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
     return DCEGM_OK;
 }
 
+cudaError_t launch_range(const DeviceBatch& B, int first, int count, cudaStream_t stream) {
+    if (B.lay.model == DCEGM_MODEL_F) return launch_solve_f(B, first, count, stream);
+    if (B.lay.model == DCEGM_MODEL_G) return launch_solve_g(B, first, count, stream);
+    return launch_solve_minimal(B, first, count, stream);
+}
+
 int run(dcegm_ctx* h) {
     if (!h) return DCEGM_E_INVALID;
     if (!h->uploaded) return fail(h, DCEGM_E_NOSOLUTION, "dcegm_run before dcegm_upload_*");
@@ -159,13 +171,7 @@ int run(dcegm_ctx* h) {
     CK(cudaMemsetAsync(B.lens, 0, sizeof(int32_t) * nstates * 4, h->stream));
     CK(cudaMemsetAsync(B.meta, 0, sizeof(dcegm_env_meta) * nstates, h->stream));
     CK(cudaMemsetAsync(B.vbound, 0, sizeof(double) * nstates * 2, h->stream));
-    cudaError_t e;
-    if (B.lay.model == DCEGM_MODEL_F)
-        e = launch_solve_f(B, h->stream);
-    else if (B.lay.model == DCEGM_MODEL_G)
-        e = launch_solve_g(B, h->stream);
-    else
-        e = launch_solve_minimal(B, h->stream);
+    cudaError_t e = launch_range(B, 0, B.lay.nmodels, h->stream);
     if (e != cudaSuccess) return cuda_fail(h, e, "kernel launch");
     CK(cudaEventRecord(h->ev[3], h->stream));
     CK(cudaStreamSynchronize(h->stream));
@@ -173,6 +179,110 @@ int run(dcegm_ctx* h) {
     h->timing.n_launches = 1;
     h->solved = true;
     return DCEGM_OK;
+}
+
+// Pipelined solve-to-host: the batch is solved in chunks on the compute stream while finished chunks
+// are packed densely (s_pack) and copied to the caller's buffer (s_copy), so that the D2H transfer of
+// chunk c overlaps the kernels of chunk c+1...  The only host round trip per chunk is its line lengths
+// (for the prefix offsets the caller gets back anyway).
+int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsigned flags, double* xy,
+                 size_t cap_points, int64_t* offsets, int64_t* npoints) {
+    if (!h) return DCEGM_E_INVALID;
+    if (!xy || !offsets || !npoints) return fail(h, DCEGM_E_INVALID, "xy/offsets/npoints is null");
+    if (flags & DCEGM_SUMMARY_ONLY) return fail(h, DCEGM_E_INVALID, "DCEGM_SUMMARY_ONLY keeps no lines to pack");
+    int rc = upload(h, model, params, nmodels, flags);
+    if (rc) return rc;
+    const DeviceBatch& B = h->batch;
+    const dcegm_layout& l = B.lay;
+    const size_t per = (size_t)l.nT * l.nstate * 4;
+    const size_t nstates = (size_t)nmodels * l.nT * l.nstate;
+    // chunks of whole waves (2 CTAs x 148 SMs), at most 16 of them
+    const int wave = 296;
+    int nchunks = (nmodels + 2 * wave - 1) / (2 * wave);
+    nchunks = nchunks > 16 ? 16 : nchunks;
+    int chunk = (nmodels + nchunks - 1) / nchunks;
+    chunk = (chunk + wave - 1) / wave * wave;
+    nchunks = (nmodels + chunk - 1) / chunk;
+    if (!h->s_pack) {
+        CK(cudaStreamCreateWithFlags(&h->s_pack, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking));
+    }
+    while (h->ev_pool.size() < (size_t)3 * nchunks) {
+        cudaEvent_t e;
+        CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        h->ev_pool.push_back(e);
+    }
+    const size_t cslots = per * chunk;
+    if (h->pin_slots < cslots) {
+        if (h->pin_lens) cudaFreeHost(h->pin_lens);
+        if (h->pin_off) cudaFreeHost(h->pin_off);
+        h->pin_lens = nullptr;
+        h->pin_off = nullptr;
+        h->pin_slots = 0;
+        CK(cudaHostAlloc((void**)&h->pin_lens, sizeof(int32_t) * cslots, cudaHostAllocDefault));
+        CK(cudaHostAlloc((void**)&h->pin_off, sizeof(long long) * (cslots + 1), cudaHostAllocDefault));
+        h->pin_slots = cslots;
+    }
+    if ((rc = ensure(h, h->pack_off, sizeof(long long) * (cslots + 1), false))) return rc;
+    const size_t pack_bytes = sizeof(double2) * cslots * l.cap;
+    if ((rc = ensure(h, h->pack_xy, pack_bytes, false))) return rc;
+    if ((rc = ensure(h, h->pack_xy2, pack_bytes, false))) return rc;
+
+    CK(cudaEventRecord(h->ev[2], h->stream));
+    CK(cudaMemsetAsync(B.isects, 0, sizeof(double2) * nstates * l.isec_cap, h->stream));
+    CK(cudaMemsetAsync(B.removed, 0, sizeof(uint32_t) * nstates * l.rem_words, h->stream));
+    CK(cudaMemsetAsync(B.lens, 0, sizeof(int32_t) * nstates * 4, h->stream));
+    CK(cudaMemsetAsync(B.meta, 0, sizeof(dcegm_env_meta) * nstates, h->stream));
+    CK(cudaMemsetAsync(B.vbound, 0, sizeof(double) * nstates * 2, h->stream));
+    for (int c = 0; c < nchunks; c++) {
+        const int c0 = c * chunk, cnt = (nmodels - c0 < chunk) ? nmodels - c0 : chunk;
+        cudaError_t e = launch_range(B, c0, cnt, h->stream);
+        if (e != cudaSuccess) return cuda_fail(h, e, "kernel launch");
+        CK(cudaEventRecord(h->ev_pool[3 * c], h->stream));
+    }
+    CK(cudaEventRecord(h->ev[3], h->stream));
+
+    int64_t base = 0;
+    offsets[0] = 0;
+    int err = DCEGM_OK;
+    for (int c = 0; c < nchunks && err == DCEGM_OK; c++) {
+        const int c0 = c * chunk, cnt = (nmodels - c0 < chunk) ? nmodels - c0 : chunk;
+        const size_t nsl = per * cnt;
+        CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * c], 0));
+        CK(cudaMemcpyAsync(h->pin_lens, B.lens + per * c0, sizeof(int32_t) * nsl, cudaMemcpyDeviceToHost, h->s_pack));
+        CK(cudaStreamSynchronize(h->s_pack));
+        long long run_ = 0;
+        int64_t* go = offsets + per * c0;
+        for (size_t s = 0; s < nsl; s++) {
+            h->pin_off[s] = run_;
+            go[s] = base + run_;
+            run_ += h->pin_lens[s] < l.cap ? h->pin_lens[s] : l.cap;
+        }
+        h->pin_off[nsl] = run_;
+        go[nsl] = base + run_;
+        if ((size_t)(base + run_) > cap_points) {
+            err = fail(h, DCEGM_E_CAPACITY, "dcegm_solve_*_packed: destination too small");
+            break;
+        }
+        double2* buf = (double2*)((c & 1) ? h->pack_xy2.p : h->pack_xy.p);
+        CK(cudaMemcpyAsync(h->pack_off.p, h->pin_off, sizeof(long long) * (nsl + 1), cudaMemcpyHostToDevice, h->s_pack));
+        if (c >= 2) CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * (c - 2) + 2], 0));  // buffer free again
+        cudaError_t e = launch_pack_lines(B, c0, cnt, (const long long*)h->pack_off.p, buf, h->s_pack);
+        if (e != cudaSuccess) return cuda_fail(h, e, "pack kernel");
+        CK(cudaEventRecord(h->ev_pool[3 * c + 1], h->s_pack));
+        CK(cudaStreamWaitEvent(h->s_copy, h->ev_pool[3 * c + 1], 0));
+        CK(cudaMemcpyAsync(xy + 2 * base, buf, sizeof(double2) * (size_t)run_, cudaMemcpyDeviceToHost, h->s_copy));
+        CK(cudaEventRecord(h->ev_pool[3 * c + 2], h->s_copy));
+        base += run_;
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaStreamSynchronize(h->s_pack));
+    CK(cudaStreamSynchronize(h->s_copy));
+    CK(cudaEventElapsedTime(&h->timing.kernel_ms, h->ev[2], h->ev[3]));
+    h->timing.n_launches = 2 * nchunks;
+    h->solved = true;
+    *npoints = base;
+    return err;
 }
 
 int need_solution(dcegm_ctx* h) {
@@ -268,11 +378,16 @@ int dcegm_destroy(dcegm_handle h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     DevBuf* bufs[] = {&h->models, &h->grids, &h->off, &h->wgt, &h->lines, &h->lens, &h->vbound, &h->meta, &h->isects,
-                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy};
+                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     for (auto& ev : h->ev)
         if (ev) cudaEventDestroy(ev);
+    for (auto& ev : h->ev_pool) cudaEventDestroy(ev);
+    if (h->pin_lens) cudaFreeHost(h->pin_lens);
+    if (h->pin_off) cudaFreeHost(h->pin_off);
+    if (h->s_pack) cudaStreamDestroy(h->s_pack);
+    if (h->s_copy) cudaStreamDestroy(h->s_copy);
     cudaStreamDestroy(h->stream);
     delete h;
     return DCEGM_OK;
@@ -304,6 +419,15 @@ int dcegm_solve_g(dcegm_handle h, const dcegm_param* p, int n, unsigned flags) {
 int dcegm_solve_minimal(dcegm_handle h, const dcegm_param* p, int n, unsigned flags) {
     int rc = upload(h, DCEGM_MODEL_MINIMAL, p, n, flags);
     return rc ? rc : run(h);
+}
+
+int dcegm_solve_f_packed(dcegm_handle h, const dcegm_param* p, int n, unsigned flags, double* xy, size_t cap_points,
+                         int64_t* offsets, int64_t* npoints) {
+    return solve_packed(h, DCEGM_MODEL_F, p, n, flags, xy, cap_points, offsets, npoints);
+}
+int dcegm_solve_g_packed(dcegm_handle h, const dcegm_param* p, int n, unsigned flags, double* xy, size_t cap_points,
+                         int64_t* offsets, int64_t* npoints) {
+    return solve_packed(h, DCEGM_MODEL_G, p, n, flags, xy, cap_points, offsets, npoints);
 }
 
 int dcegm_get_layout(dcegm_handle h, dcegm_layout* out) {

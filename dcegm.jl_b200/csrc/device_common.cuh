@@ -14,7 +14,13 @@
 
 namespace dcegm {
 
-constexpr int kThreads = 256;   // threads per CTA of the persistent solver kernels
+#ifdef DC_T512
+constexpr int kThreads = 512;
+constexpr int kCtasPerSm = 1;
+#else
+constexpr int kThreads = 256;
+constexpr int kCtasPerSm = 2;
+#endif   // threads per CTA of the persistent solver kernels
 constexpr int kWarps = kThreads / 32;
 constexpr int kMaxNy = 64;     // income nodes staged in shared memory by solve_f_kernel
 constexpr int kSegCap = 192;    // max sections of one splitLine
@@ -54,6 +60,7 @@ struct DeviceBatch {
     double2* dirty;          // [nmodels][nT][nstate][2][2][na] or null
     int32_t* status;         // [nmodels]
     dcegm_summary* summaries;  // [nmodels]
+    int first;               // first model of this launch (grid = number of models of the launch)
 };
 
 __device__ __forceinline__ size_t line_slot(const dcegm_layout& l, int m, int it, int iy, int id, int kind) {

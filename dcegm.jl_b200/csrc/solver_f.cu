@@ -202,8 +202,8 @@ __device__ __forceinline__ double interp_cnt(const double* __restrict__ x, const
 __device__ unsigned long long dc_phase_total[kPhaseSlots];
 #endif
 
-__global__ void __launch_bounds__(kThreads, 2) solve_f_kernel(DeviceBatch B) {
-    const int m = blockIdx.x;
+__global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_f_kernel(DeviceBatch B) {
+    const int m = B.first + blockIdx.x;
     const int tid = threadIdx.x;
 #ifdef DCEGM_PHASE_CLOCKS
     if (tid == 0) {
@@ -628,7 +628,9 @@ extern "C" int dcegm_debug_phase_clocks(unsigned long long* out, int reset) {
 }
 #endif
 
-cudaError_t launch_solve_f(const DeviceBatch& B, cudaStream_t stream) {
+cudaError_t launch_solve_f(const DeviceBatch& B0, int first, int count, cudaStream_t stream) {
+    DeviceBatch B = B0;
+    B.first = first;
     const size_t smem = FPlan(B.lay.cap, B.lay.isec_cap).bytes();
     static size_t configured = 0;
     if (smem > configured) {
@@ -636,7 +638,7 @@ cudaError_t launch_solve_f(const DeviceBatch& B, cudaStream_t stream) {
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    solve_f_kernel<<<B.lay.nmodels, kThreads, smem, stream>>>(B);
+    solve_f_kernel<<<count, kThreads, smem, stream>>>(B);
     return cudaGetLastError();
 }
 

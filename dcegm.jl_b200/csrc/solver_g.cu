@@ -67,8 +67,8 @@ __device__ inline void store_line_g(const DeviceBatch& B, int m, int it, int iy,
     for (int k = threadIdx.x; k < nn; k += kThreads) dst[k] = make_double2(x[k], y[k]);
 }
 
-__global__ void __launch_bounds__(kThreads, 2) solve_g_kernel(DeviceBatch B) {
-    const int m = blockIdx.x;
+__global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBatch B) {
+    const int m = B.first + blockIdx.x;
     const int tid = threadIdx.x;
     __shared__ DevModel s_p;
     __shared__ int s_status;
@@ -326,7 +326,9 @@ __global__ void __launch_bounds__(kThreads, 2) solve_g_kernel(DeviceBatch B) {
     }
 }
 
-cudaError_t launch_solve_g(const DeviceBatch& B, cudaStream_t stream) {
+cudaError_t launch_solve_g(const DeviceBatch& B0, int first, int count, cudaStream_t stream) {
+    DeviceBatch B = B0;
+    B.first = first;
     const size_t smem = GPlan(B.lay.cap, B.lay.isec_cap, B.lay.na, B.lay.ny).bytes();
     static size_t configured = 0;
     if (smem > configured) {
@@ -334,7 +336,7 @@ cudaError_t launch_solve_g(const DeviceBatch& B, cudaStream_t stream) {
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    solve_g_kernel<<<B.lay.nmodels, kThreads, smem, stream>>>(B);
+    solve_g_kernel<<<count, kThreads, smem, stream>>>(B);
     return cudaGetLastError();
 }
 

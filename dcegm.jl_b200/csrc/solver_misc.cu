@@ -10,7 +10,7 @@ namespace dcegm {
 // Output: kind C lines of (m[it], c[it]) for id 0.
 __global__ void __launch_bounds__(kThreads) solve_minimal_kernel(DeviceBatch B) {
     extern __shared__ __align__(16) unsigned char smem[];
-    const int m = blockIdx.x, tid = threadIdx.x;
+    const int m = B.first + blockIdx.x, tid = threadIdx.x;
     __shared__ DevModel s_p;
     __shared__ int s_status;
     if (tid == 0) {
@@ -89,7 +89,9 @@ __global__ void __launch_bounds__(kThreads) solve_minimal_kernel(DeviceBatch B) 
     }
 }
 
-cudaError_t launch_solve_minimal(const DeviceBatch& B, cudaStream_t stream) {
+cudaError_t launch_solve_minimal(const DeviceBatch& B0, int first, int count, cudaStream_t stream) {
+    DeviceBatch B = B0;
+    B.first = first;
     const size_t smem = (size_t)4 * (B.lay.na + 1) * sizeof(double);
     static size_t configured = 48 * 1024;
     if (smem > configured) {
@@ -97,7 +99,7 @@ cudaError_t launch_solve_minimal(const DeviceBatch& B, cudaStream_t stream) {
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    solve_minimal_kernel<<<B.lay.nmodels, kThreads, smem, stream>>>(B);
+    solve_minimal_kernel<<<count, kThreads, smem, stream>>>(B);
     return cudaGetLastError();
 }
 

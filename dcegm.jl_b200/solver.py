@@ -114,6 +114,25 @@ class Solver:
         self._ck(self.lib.dcegm_fetch_packed(self.h, first, count, _dp(xy), npts.value, op, C.byref(npts)))
         return xy, offsets
 
+    def solve_packed(self, model, params, keep_dirty=False, xy=None):
+        """Solve and return (xy, offsets): all stored polylines densely packed, copied to the host while
+        later chunks of the batch are still being solved (dcegm_solve_*_packed)."""
+        arr = params if isinstance(params, C.Array) else params_array(params)
+        fn = {_abi.MODEL_F: self.lib.dcegm_solve_f_packed, _abi.MODEL_G: self.lib.dcegm_solve_g_packed}[model]
+        lay = _abi.dcegm_layout()
+        n = len(arr)
+        nstate = arr[0].ny if model == _abi.MODEL_G else 1
+        nsl = n * arr[0].nT * nstate * 4
+        na = arr[0].na
+        cap = (na + na // 10 + 2 * max(na // 16, 32) + 2 + 7) // 8 * 8
+        if xy is None:
+            xy = np.empty((nsl * cap, 2))
+        offsets = np.zeros(nsl + 1, np.int64)
+        npts = C.c_int64()
+        flags = _abi.KEEP_DIRTY if keep_dirty else 0
+        self._ck(fn(self.h, arr, n, flags, _dp(xy), xy.shape[0], offsets.ctypes.data_as(C.POINTER(C.c_int64)), C.byref(npts)))
+        return xy[: npts.value], offsets
+
     def status(self):
         lay = self.layout()
         st = np.zeros(lay.nmodels, np.int32)

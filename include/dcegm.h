@@ -188,6 +188,18 @@ int  dcegm_solve_f(dcegm_handle h, const dcegm_param* params, int nmodels, unsig
 int  dcegm_solve_g(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
 int  dcegm_solve_minimal(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
 
+/* Solve and deliver every stored polyline densely packed into caller-owned host memory in one call
+ * (what runf/rung return to the caller: all of m.c / m.v).  xy receives the concatenated (x,y) points
+ * of all lines in layout order, offsets[(nmodels*nT*nstate*4)+1] their prefix offsets in points,
+ * *npoints the total.  The batch is solved in chunks so that packing and the device-to-host copy of
+ * one chunk overlap the kernels of the next; xy from dcegm_host_alloc (pinned) makes the copies
+ * asynchronous.  DCEGM_E_CAPACITY if cap_points is too small (nmodels*nT*nstate*4*cap always fits).
+ * The solution also stays resident for the fetch calls below. */
+int  dcegm_solve_f_packed(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags,
+                          double* xy, size_t cap_points, int64_t* offsets, int64_t* npoints);
+int  dcegm_solve_g_packed(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags,
+                          double* xy, size_t cap_points, int64_t* offsets, int64_t* npoints);
+
 /* ---- results -------------------------------------------------------------------- */
 int  dcegm_get_layout(dcegm_handle h, dcegm_layout* out);
 /* one polyline; replaces getx/gety(m.c[id,it].env) etc. (line.jl:121-124).  xy receives len

@@ -185,3 +185,21 @@ def test_errors_are_codes_not_crashes(solver):
     with pytest.raises(_lib.DcegmError) as e:
         solver.solve(_abi.MODEL_F, [Param(par=dict(na=5000))])
     assert e.value.code == _abi.E_INVALID
+
+
+@pytest.mark.parametrize("n,na", [(5, 120), (700, 40)])
+def test_packed_pipelined_solve_equals_resident_solution(solver, n, na):
+    """dcegm_solve_f_packed (chunked solve overlapped with packing + D2H) delivers bit for bit what
+    dcegm_solve_f + dcegm_fetch_packed deliver."""
+    from dcegm_jl_b200 import _abi
+
+    ps = c3_batch(n, na=na, seed=7)
+    solver.solve(_abi.MODEL_F, ps, fetch=False)
+    xy0, off0 = solver.fetch_packed()
+    st0 = solver.status()
+    xy1, off1 = solver.solve_packed(_abi.MODEL_F, ps)
+    st1 = solver.status()
+    assert np.array_equal(off0, off1)
+    assert xy0.shape == xy1.shape
+    assert np.array_equal(np.ascontiguousarray(xy0).view(np.uint64), np.ascontiguousarray(xy1).view(np.uint64))
+    assert np.array_equal(st0, st1)
