@@ -147,12 +147,16 @@ __device__ __forceinline__ double interp_y(const double* __restrict__ x, const d
 // ---------------------------------------------------------------------------------------------
 struct KnotIndex {
     int tab;        // byte offset in dc_smem of unsigned short T[nb + 1]
-    double lo, inv, top;  // top = nb - 1
+    double lo, inv;
+    int topi;       // nb - 1
 };
 __device__ __forceinline__ int knot_bucket(const KnotIndex& K, double q) {
-    double t = (q - K.lo) * K.inv;
-    t = fmin(fmax(t, 0.0), K.top);  // NaN -> 0
-    return __double2loint(t + DC_MAGIC);
+    // round to nearest by the magic-number addition, then clamp as an integer (two ALU min/max instead
+    // of FP64 compare-select chains).  Monotone in q as long as |t| < 2^31 — knot_index_covers() checks
+    // the queries of a period against that; NaN / Inf give bucket 0 (low word of the sum is 0).
+    const double t = (q - K.lo) * K.inv;
+    const int b = __double2loint(t + DC_MAGIC);
+    return min(max(b, 0), K.topi);
 }
 // largest power of two nb such that nlines tables of nb+1 entries fit into `bytes`
 __host__ __device__ inline int knot_index_buckets(int bytes, int nlines) {
@@ -164,7 +168,12 @@ __host__ __device__ inline int knot_index_buckets(int bytes, int nlines) {
 __device__ __forceinline__ void knot_index_range(KnotIndex& K, const double* x, int n, int nb) {
     K.lo = x[0];
     K.inv = (double)nb / (x[n - 1] - x[0]);
-    K.top = (double)(nb - 1);
+    K.topi = nb - 1;
+}
+// true iff every query in [qmin, qmax] maps to a bucket number that fits the integer conversion of knot_bucket
+__device__ __forceinline__ bool knot_index_covers(const KnotIndex& K, double qmin, double qmax) {
+    const double t0 = (qmin - K.lo) * K.inv, t1 = (qmax - K.lo) * K.inv;
+    return t0 > -1e9 && t1 < 1e9;  // false for NaN
 }
 // one knot's share of the table build (x strictly increasing, n >= 2): the buckets between the
 // previous knot's and this knot's get this knot's index.  Block-level: every k in [0, n) once; the

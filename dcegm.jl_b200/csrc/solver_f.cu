@@ -315,13 +315,14 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_f_kernel(DeviceBat
         // ---------------- 1. EGM step -----------------------------------------------------------------
         // fast path: straight-line node evaluation (bucket-indexed knot search, pow from shared
         // logarithms); see egm_node_generic for the conditions under which it does not apply
-        const bool fast = model_fast && !beq && !(s_status & (DCEGM_ST_NONMONOTONE | DCEGM_ST_NONFINITE)) && N.n_wc >= 2 &&
+        bool fast = model_fast && !beq && !(s_status & (DCEGM_ST_NONMONOTONE | DCEGM_ST_NONFINITE)) && N.n_wc >= 2 &&
                           N.n_wv >= 2 && N.n_r >= 2;
         KnotIndex Kr, Kc, Kv;
         Kr.tab = tab0;
         Kc.tab = tab0 + tab_stride;
         Kv.tab = tab0 + 2 * tab_stride;
-        Kr.lo = Kc.lo = Kv.lo = Kr.inv = Kc.inv = Kv.inv = Kr.top = Kc.top = Kv.top = 0.0;
+        Kr.lo = Kc.lo = Kv.lo = Kr.inv = Kc.inv = Kv.inv = 0.0;
+        Kr.topi = Kc.topi = Kv.topi = 0;
         if (fast) {
             knot_index_range(Kr, N.r_x(), N.n_r, nbuck);
             knot_index_range(Kc, N.wc_x(), N.n_wc, nbuck);
@@ -337,6 +338,16 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_f_kernel(DeviceBat
         DC_CLK(1);
         bool same_nodes = true;  // retiree: do all nodes see the same next-period cash-on-hand?
         for (int iy = 1; iy < ny; iy++) same_nodes &= s_off[ny + iy] == s_off[ny];
+        if (fast) {  // all queries of this period inside the range the bucket map handles exactly
+            double omin = s_off[0], omax = s_off[0];
+            for (int k = 1; k < 2 * ny; k++) {
+                omin = s_off[k] < omin ? s_off[k] : omin;
+                omax = s_off[k] > omax ? s_off[k] : omax;
+            }
+            const double ra0 = avec[0] * p.R, ra1 = avec[na - 1] * p.R;
+            const double qmin = (ra0 < ra1 ? ra0 : ra1) + omin, qmax = (ra0 < ra1 ? ra1 : ra0) + omax;
+            fast = knot_index_covers(Kr, qmin, qmax) && knot_index_covers(Kc, qmin, qmax) && knot_index_covers(Kv, qmin, qmax);
+        }
         const double rx1 = N.r_x()[1], wvx1 = N.wv_x()[1];
 
         // ---- thread per savings grid point: worker today (id = 0), serial over the income nodes ----
