@@ -19,6 +19,8 @@ cudaError_t launch_solve_g(const DeviceBatch& B, int first, int count, cudaStrea
 cudaError_t launch_solve_minimal(const DeviceBatch& B, int first, int count, cudaStream_t stream);
 cudaError_t launch_pack_lines(const DeviceBatch& B, int first, int count, const long long* d_offsets, double2* d_dst,
                               cudaStream_t stream);
+cudaError_t launch_sim(const DeviceBatch& B, const SimBatch& Sb, int first, int count, cudaStream_t stream);
+size_t sim_smem_bytes(const dcegm_layout& l);
 size_t solver_f_smem_bytes(int cap, int isec_cap);
 size_t solver_g_smem_bytes(int cap, int isec_cap, int na, int ny);
 }  // namespace dcegm
@@ -40,6 +42,10 @@ struct dcegm_ctx {
     long long* pin_off = nullptr;
     size_t pin_slots = 0;
     DevBuf pack_xy2;
+    DevBuf simm, yvec, mom, rhist, sstat, pan_d, pan_i, pan_ret, sh_w, sh_d, sh_r, sh_w0, sh_y0;
+    bool simulated = false;
+    int sim_nsims = 0;      // panel geometry of the last simulation (0 = no panel kept)
+    float sim_ms = 0.f;
     std::string err;
     DevBuf models, grids, off, wgt, lines, lens, vbound, meta, isects, removed, dirty, status, summaries, pack_off, pack_xy;
     DeviceBatch batch{};
@@ -128,9 +134,14 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
     CK(cudaMemcpyAsync(h->grids.p, h->tab.grids.data(), sizeof(double) * h->tab.grids.size(), cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(h->off.p, h->tab.off.data(), sizeof(double) * h->tab.off.size(), cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(h->wgt.p, h->tab.wgt.data(), sizeof(double) * h->tab.wgt.size(), cudaMemcpyHostToDevice, h->stream));
+    if ((rc = ensure(h, h->simm, sizeof(SimModel) * nmodels, false))) return rc;
+    if ((rc = ensure(h, h->yvec, sizeof(double) * h->tab.yvec.size(), false))) return rc;
+    CK(cudaMemcpyAsync(h->simm.p, h->tab.sim.data(), sizeof(SimModel) * nmodels, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->yvec.p, h->tab.yvec.data(), sizeof(double) * h->tab.yvec.size(), cudaMemcpyHostToDevice, h->stream));
     CK(cudaEventRecord(h->ev[1], h->stream));
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaEventElapsedTime(&h->timing.h2d_ms, h->ev[0], h->ev[1]));
+    h->simulated = false;
 
     DeviceBatch& B = h->batch;
     B.lay = lay;
@@ -378,7 +389,9 @@ int dcegm_destroy(dcegm_handle h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     DevBuf* bufs[] = {&h->models, &h->grids, &h->off, &h->wgt, &h->lines, &h->lens, &h->vbound, &h->meta, &h->isects,
-                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2};
+                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2,
+                      &h->simm, &h->yvec, &h->mom, &h->rhist, &h->sstat, &h->pan_d, &h->pan_i, &h->pan_ret,
+                      &h->sh_w, &h->sh_d, &h->sh_r, &h->sh_w0, &h->sh_y0};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     for (auto& ev : h->ev)
@@ -544,6 +557,115 @@ int dcegm_summaries_to_device(dcegm_handle h, void* dst_device, size_t bytes) {
     const size_t need = sizeof(dcegm_summary) * (size_t)h->batch.lay.nmodels;
     if (!dst_device || bytes < need) return fail(h, DCEGM_E_CAPACITY, "dcegm_summaries_to_device: destination too small");
     CK(cudaMemcpyAsync(dst_device, h->batch.summaries, need, cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return DCEGM_OK;
+}
+
+int dcegm_simulate(dcegm_handle h, unsigned flags, const dcegm_sim_shocks* sh) {
+    int rc = need_solution(h);
+    if (rc) return rc;
+    const DeviceBatch& B = h->batch;
+    const dcegm_layout& l = B.lay;
+    if (l.model != DCEGM_MODEL_F && l.model != DCEGM_MODEL_G) return fail(h, DCEGM_E_INVALID, "dcegm_simulate: the resident solution is not an FModel / GModel");
+    if (!B.lines) return fail(h, DCEGM_E_NOSOLUTION, "dcegm_simulate needs the stored lines (solve without DCEGM_SUMMARY_ONLY)");
+    if ((long long)sim_smem_bytes(l) > (long long)h->max_smem_optin) return fail(h, DCEGM_E_INVALID, "dcegm_simulate: lines of one period do not fit into shared memory");
+    const int n = l.nmodels, nT = l.nT;
+    const bool panel = flags & DCEGM_SIM_PANEL;
+    int nsims = sh ? sh->nsims : h->tab.sim[0].nsims;
+    if (sh) {
+        if (nsims <= 0 || !sh->wshocks || !sh->dshocks || !sh->w0shocks || (l.model == DCEGM_MODEL_G && !sh->ystate0))
+            return fail(h, DCEGM_E_INVALID, "dcegm_simulate: incomplete shock arrays");
+    } else {
+        for (int m = 0; m < n; m++) {
+            if (h->tab.sim[m].nsims <= 0) return fail(h, DCEGM_E_INVALID, "dcegm_simulate: nsims must be positive");
+            if (panel && h->tab.sim[m].nsims != nsims) return fail(h, DCEGM_E_INVALID, "DCEGM_SIM_PANEL needs one nsims for all models");
+        }
+    }
+    SimBatch Sb{};
+    Sb.sim = (const SimModel*)h->simm.p;
+    Sb.yvec = (const double*)h->yvec.p;
+    if ((rc = ensure(h, h->mom, sizeof(double) * (size_t)n * nT * DCEGM_SIM_NMOM, false))) return rc;
+    if ((rc = ensure(h, h->rhist, sizeof(int32_t) * (size_t)n * (nT + 1), false))) return rc;
+    if ((rc = ensure(h, h->sstat, sizeof(int32_t) * (size_t)n, false))) return rc;
+    Sb.moments = (double*)h->mom.p;
+    Sb.ret_hist = (int32_t*)h->rhist.p;
+    Sb.sim_status = (int32_t*)h->sstat.p;
+    const size_t npan = (size_t)nsims * nT;
+    if (panel) {
+        if ((rc = ensure(h, h->pan_d, sizeof(double) * 6 * npan * n, false))) return rc;
+        if ((rc = ensure(h, h->pan_i, sizeof(int32_t) * 2 * npan * n, false))) return rc;
+        if ((rc = ensure(h, h->pan_ret, sizeof(int32_t) * (size_t)nsims * n, false))) return rc;
+        Sb.pan_d = (double*)h->pan_d.p;
+        Sb.pan_i = (int32_t*)h->pan_i.p;
+        Sb.pan_ret = (int32_t*)h->pan_ret.p;
+    }
+    if (sh) {
+        Sb.given = 1;
+        Sb.nsims_given = nsims;
+        auto up = [&](DevBuf& b, const void* src, size_t bytes, const void** dst) -> int {
+            *dst = nullptr;
+            if (!src) return DCEGM_OK;
+            int r = ensure(h, b, bytes, false);
+            if (r) return r;
+            if (cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, h->stream) != cudaSuccess) return fail(h, DCEGM_E_CUDA, "shock upload");
+            *dst = b.p;
+            return DCEGM_OK;
+        };
+        if ((rc = up(h->sh_w, sh->wshocks, sizeof(double) * npan, (const void**)&Sb.wsh))) return rc;
+        if ((rc = up(h->sh_d, sh->dshocks, sizeof(double) * npan, (const void**)&Sb.dsh))) return rc;
+        if ((rc = up(h->sh_r, sh->rshocks, sizeof(double) * npan, (const void**)&Sb.rsh))) return rc;
+        if ((rc = up(h->sh_w0, sh->w0shocks, sizeof(double) * nsims, (const void**)&Sb.w0sh))) return rc;
+        if ((rc = up(h->sh_y0, sh->ystate0, sizeof(int32_t) * nsims, (const void**)&Sb.y0))) return rc;
+    }
+    CK(cudaEventRecord(h->ev[0], h->stream));
+    cudaError_t e = launch_sim(B, Sb, 0, n, h->stream);
+    if (e != cudaSuccess) return cuda_fail(h, e, "simulation kernel launch");
+    CK(cudaEventRecord(h->ev[1], h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaEventElapsedTime(&h->sim_ms, h->ev[0], h->ev[1]));
+    h->simulated = true;
+    h->sim_nsims = panel ? nsims : 0;
+    return DCEGM_OK;
+}
+
+int dcegm_fetch_sim_moments(dcegm_handle h, int first, int count, double* moments, int32_t* ret_hist, int32_t* sim_status) {
+    int rc = need_solution(h);
+    if (rc) return rc;
+    if (!h->simulated) return fail(h, DCEGM_E_NOSOLUTION, "no simulation: call dcegm_simulate first");
+    if ((rc = check_range(h, first, count))) return rc;
+    const int nT = h->batch.lay.nT;
+    if (moments)
+        CK(cudaMemcpyAsync(moments, (const double*)h->mom.p + (size_t)first * nT * DCEGM_SIM_NMOM,
+                           sizeof(double) * (size_t)count * nT * DCEGM_SIM_NMOM, cudaMemcpyDeviceToHost, h->stream));
+    if (ret_hist)
+        CK(cudaMemcpyAsync(ret_hist, (const int32_t*)h->rhist.p + (size_t)first * (nT + 1), sizeof(int32_t) * (size_t)count * (nT + 1),
+                           cudaMemcpyDeviceToHost, h->stream));
+    if (sim_status)
+        CK(cudaMemcpyAsync(sim_status, (const int32_t*)h->sstat.p + first, sizeof(int32_t) * (size_t)count, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return DCEGM_OK;
+}
+
+int dcegm_fetch_sim_panel(dcegm_handle h, int model, double* w0, double* w1, double* cons, double* util, double* inc,
+                          double* prob_work, int32_t* ystate, int32_t* worker, int32_t* ret_age) {
+    int rc = need_solution(h);
+    if (rc) return rc;
+    if (!h->simulated || h->sim_nsims == 0) return fail(h, DCEGM_E_NOSOLUTION, "no panel: call dcegm_simulate with DCEGM_SIM_PANEL");
+    if (model < 0 || model >= h->batch.lay.nmodels) return fail(h, DCEGM_E_INVALID, "model out of range");
+    const size_t npan = (size_t)h->sim_nsims * h->batch.lay.nT;
+    double* dst[6] = {w0, w1, cons, util, inc, prob_work};
+    for (int k = 0; k < 6; k++)
+        if (dst[k])
+            CK(cudaMemcpyAsync(dst[k], (const double*)h->pan_d.p + ((size_t)model * 6 + k) * npan, sizeof(double) * npan,
+                               cudaMemcpyDeviceToHost, h->stream));
+    int32_t* di[2] = {ystate, worker};
+    for (int k = 0; k < 2; k++)
+        if (di[k])
+            CK(cudaMemcpyAsync(di[k], (const int32_t*)h->pan_i.p + ((size_t)model * 2 + k) * npan, sizeof(int32_t) * npan,
+                               cudaMemcpyDeviceToHost, h->stream));
+    if (ret_age)
+        CK(cudaMemcpyAsync(ret_age, (const int32_t*)h->pan_ret.p + (size_t)model * h->sim_nsims, sizeof(int32_t) * h->sim_nsims,
+                           cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     return DCEGM_OK;
 }

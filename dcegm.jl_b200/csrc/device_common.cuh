@@ -63,6 +63,22 @@ struct DeviceBatch {
     int first;               // first model of this launch (grid = number of models of the launch)
 };
 
+// inputs / outputs of the forward simulator (solver_sim.cu)
+struct SimBatch {
+    const SimModel* sim;
+    const double* yvec;  // [nmodels][ny]
+    const double *wsh, *dsh, *rsh, *w0sh;  // given shocks (device) or null
+    const int32_t* y0;
+    int given;           // 1: shocks given, all models share nsims_given
+    int nsims_given;
+    double* moments;     // [nmodels][nT][DCEGM_SIM_NMOM]
+    int32_t* ret_hist;   // [nmodels][nT+1]
+    int32_t* sim_status; // [nmodels]
+    double* pan_d;       // [nmodels][6][nsims*nT] or null
+    int32_t* pan_i;      // [nmodels][2][nsims*nT]
+    int32_t* pan_ret;    // [nmodels][nsims]
+};
+
 __device__ __forceinline__ size_t line_slot(const dcegm_layout& l, int m, int it, int iy, int id, int kind) {
     return ((((size_t)m * l.nT + it) * l.nstate + iy) * 2 + id) * 2 + kind;
 }

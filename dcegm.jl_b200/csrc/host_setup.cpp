@@ -281,6 +281,8 @@ bool build_tables(int model, const dcegm_param* params, int nmodels, HostTables&
 
     const size_t off_per = model == DCEGM_MODEL_MINIMAL ? (size_t)ny : (size_t)(nT - 1) * 2 * ny;
     const size_t wgt_per = model == DCEGM_MODEL_G ? (size_t)ny * ny : (size_t)ny;
+    out.sim.assign(nmodels, SimModel{});
+    out.yvec.assign((size_t)ny * nmodels, 0.0);
     out.off.assign(off_per * nmodels, 0.0);
     out.wgt.assign(wgt_per * nmodels, 0.0);
 
@@ -289,6 +291,16 @@ bool build_tables(int model, const dcegm_param* params, int nmodels, HostTables&
         double* off = out.off.data() + off_per * m;
         double* wgt = out.wgt.data() + wgt_per * m;
         std::vector<double> yvec(ny);
+        SimModel& sm = out.sim[m];
+        sm.inc0 = p.inc0;
+        sm.inc1 = p.inc1;
+        sm.inc2 = p.inc2;
+        sm.sigma = p.sigma;
+        sm.initw0 = p.initw0;
+        sm.initw1 = p.initw1;
+        sm.rseed = p.rseed;
+        sm.retage = p.retage;
+        sm.nsims = p.nsims;
         if (model == DCEGM_MODEL_F) {
             for (int i = 0; i < ny; i++) {
                 yvec[i] = zq[i] * p.sigma;  // param.jl:197
@@ -322,6 +334,7 @@ bool build_tables(int model, const dcegm_param* params, int nmodels, HostTables&
                 off[i] = 0.0 + std::exp(yvec[i]);             // minimal_EGM.jl:21
             }
         }
+        std::copy(yvec.begin(), yvec.end(), out.yvec.begin() + (size_t)ny * m);
     };
     unsigned hw = std::thread::hardware_concurrency();
     int nt = (int)std::min<unsigned>(hw ? hw : 1, 16);

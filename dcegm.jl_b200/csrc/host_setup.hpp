@@ -43,8 +43,17 @@ struct DevModel {
     int32_t _pad[2];
 };
 
+// Scalars only the forward simulator needs (simulate.jl:61-203, utils.jl:243-250)
+struct SimModel {
+    double inc0, inc1, inc2, sigma, initw0, initw1;
+    int64_t rseed;
+    int32_t retage, nsims;
+};
+
 struct HostTables {
     std::vector<DevModel> models;
+    std::vector<SimModel> sim;
+    std::vector<double> yvec;    // G: [nmodels][ny] income support (param.jl:279-285); F/minimal: sigma-scaled nodes
     std::vector<double> grids;   // [ngrids][na]
     int ngrids = 0;
     // F: off [nmodels][nT-1][2 id][ny]   m1 = a*R + off          (param.jl:212-213)

@@ -1,0 +1,277 @@
+// solver_sim.cu — forward panel simulation of the resident solution.
+//
+// Replaces sim(m::FModel,p) (src/simulate.jl:61-130) and sim(m::GModel,p) (simulate.jl:133-203).
+// One CTA per model.  Agents are processed in tiles of kSimTile (4 per thread, state in registers);
+// for every tile the CTA walks the periods forward, staging that period's policy/value polylines
+// (all income states) from HBM/L2 into shared memory as SoA, so nothing per-agent is ever written to
+// memory unless the caller asked for the panel.  Shocks are counter-based (dc_rng.h) or given.
+// Per-period sums are reduced tile by tile in a fixed order (the CPU oracle reproduces it).
+#include <math_constants.h>
+
+#include "dc_rng.h"
+#include "device_common.cuh"
+
+namespace dcegm {
+
+constexpr int kSimAgents = 4;                    // agents per thread and tile
+constexpr int kSimTile = kThreads * kSimAgents;  // agents per tile
+
+
+size_t sim_smem_bytes(const dcegm_layout& l) {
+    const size_t lines = (size_t)l.nstate * 8 * l.cap * sizeof(double);
+    const size_t tabs = ((size_t)l.ny * l.ny + (size_t)l.nT * l.ny + (size_t)l.nT * DCEGM_SIM_NMOM + kWarps * DCEGM_SIM_NMOM +
+                         (size_t)l.nstate * 2) * sizeof(double);
+    const size_t ints = ((size_t)l.nT + 1 + (size_t)l.nstate * 4 + 4) * sizeof(int);
+    return lines + tabs + ints + 64;
+}
+
+// vfun (dc_algo.jl:220-251) on the value line of period `it` (0-based)
+__device__ __forceinline__ double sim_vfun(bool worker_line, bool terminal, double c1, double m1, const double* vx,
+                                           const double* vy, int n, double vb, const DevModel& p) {
+    if (terminal && p.nu > 0) return p.nu * u_plain(c1 + p.bbar, p) - 0.0;  // bequest(c1,false,p)
+    const bool mask = terminal || (m1 < vx[1]);
+    if (mask) return u_work(c1, worker_line, p) + p.beta * vb;
+    return interp_y(vx, vy, n, m1);
+}
+
+template <int MODEL>
+__global__ void __launch_bounds__(kThreads) sim_kernel(DeviceBatch B, SimBatch Sb) {
+    const int m = B.first + blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    __shared__ DevModel s_p;
+    __shared__ SimModel s_sp;
+    __shared__ int s_status;
+    if (tid == 0) {
+        s_p = B.models[m];
+        s_sp = Sb.sim[m];
+        s_status = 0;
+    }
+    __syncthreads();
+    const DevModel& p = s_p;
+    const SimModel& sp = s_sp;
+    const dcegm_layout& L = B.lay;
+    const int nT = L.nT, ny = L.ny, nstate = L.nstate, cap = L.cap;
+    const int nsims = Sb.given ? Sb.nsims_given : sp.nsims;
+
+    // shared-memory map
+    double* ln = reinterpret_cast<double*>(dc_smem);                 // [nstate][id][kind][x|y][cap]
+    double* gg = ln + (size_t)nstate * 8 * cap;                      // [ny][ny] cumulative transition rows
+    double* inctab = gg + ny * ny;                                   // [nT][ny] income(it+1, yvec)
+    double* mom = inctab + nT * ny;                                  // [nT][NMOM]
+    double* red = mom + nT * DCEGM_SIM_NMOM;                         // [kWarps][NMOM]
+    double* vb = red + kWarps * DCEGM_SIM_NMOM;                      // [nstate][2]
+    int* hist = reinterpret_cast<int*>(vb + nstate * 2);             // [nT+1]
+    int* lens = hist + nT + 1;                                       // [nstate][id][kind]
+    auto line = [&](int st, int id, int kind, int xy) { return ln + ((((size_t)st * 2 + id) * 2 + kind) * 2 + xy) * cap; };
+
+    for (int k = tid; k < nT + 1; k += kThreads) hist[k] = 0;
+    for (int k = tid; k < nT * DCEGM_SIM_NMOM; k += kThreads) mom[k] = 0.0;
+    if (MODEL == DCEGM_MODEL_G) {
+        // GG = cumsum(m.ywgt, dims=2) (simulate.jl:145), sequential like Julia's cumsum
+        const double* w = B.wgt + (size_t)m * ny * ny;
+        for (int r = tid; r < ny; r += kThreads) {
+            double acc = 0.0;
+            for (int j = 0; j < ny; j++) {
+                acc = j == 0 ? w[r * ny + j] : acc + w[r * ny + j];
+                gg[r * ny + j] = acc;
+            }
+        }
+        // income(it, p, yvec[iy]) (utils.jl:243-250), it 1-based
+        const double* yv = Sb.yvec + (size_t)m * ny;
+        for (int k = tid; k < nT * ny; k += kThreads) {
+            const int it1 = k / ny + 1, iy = k % ny;
+            const int age = it1 + 19;
+            inctab[k] = it1 > sp.retage ? p.pension
+                                        : dc_exp(sp.inc0 + sp.inc1 * (double)age - sp.inc2 * (double)(age * age) + yv[iy]);
+        }
+    }
+    const double a_lo = p.a_low, a_hi = p.a_high;
+    const size_t npan = (size_t)nsims * nT;
+    double* pd = Sb.pan_d ? Sb.pan_d + (size_t)m * 6 * npan : nullptr;
+    int32_t* pi = Sb.pan_i ? Sb.pan_i + (size_t)m * 2 * npan : nullptr;
+
+    for (int tile0 = 0; tile0 < nsims; tile0 += kSimTile) {
+        double w1[kSimAgents];
+        int ys[kSimAgents], ret[kSimAgents];
+        bool working[kSimAgents], prev_worker[kSimAgents];
+#pragma unroll
+        for (int a = 0; a < kSimAgents; a++) {
+            w1[a] = 0.0;
+            ys[a] = 0;
+            ret[a] = 0;
+            working[a] = true;
+            prev_worker[a] = true;
+        }
+        for (int it = 0; it < nT; it++) {
+            __syncthreads();
+            // ---- stage the lines of period `it` (AoS in HBM -> SoA in shared memory) ----
+            for (int s = tid; s < nstate * 4; s += kThreads) {
+                const size_t slot = ((size_t)m * nT + it) * nstate * 4 + s;
+                const int n = B.lens[slot];
+                lens[s] = n < cap ? n : cap;
+            }
+            for (int s = tid; s < nstate * 2; s += kThreads) vb[s] = B.vbound[((size_t)m * nT + it) * nstate * 2 + s];
+            for (int s = 0; s < nstate * 4; s++) {
+                const size_t slot = ((size_t)m * nT + it) * nstate * 4 + s;
+                const int n = min(B.lens[slot], cap);
+                const double2* src = B.lines + slot * (size_t)cap;
+                double* dx = ln + ((size_t)s * 2) * cap;
+                double* dy = dx + cap;
+                for (int k = tid; k < n; k += kThreads) {
+                    const double2 v = src[k];
+                    dx[k] = v.x;
+                    dy[k] = v.y;
+                }
+            }
+            __syncthreads();
+            double sum[DCEGM_SIM_NMOM];
+#pragma unroll
+            for (int k = 0; k < DCEGM_SIM_NMOM; k++) sum[k] = 0.0;
+            int flags = 0;
+#pragma unroll
+            for (int a = 0; a < kSimAgents; a++) {
+                const int i = tile0 + a * kThreads + tid;
+                if (i >= nsims) continue;
+                const size_t at = (size_t)i + (size_t)nsims * it;
+                // ---- state at the start of the period (simulate.jl:82-101, 160-178) ----
+                double w0, inc;
+                const bool wk = working[a];
+                const int worker = wk ? 1 : 2;
+                if (MODEL == DCEGM_MODEL_G) {
+                    if (it == 0) {
+                        int y0;
+                        if (Sb.given)
+                            y0 = Sb.y0[i] - 1;
+                        else
+                            y0 = (int)(dc_sim_uniform(sp.rseed, (uint32_t)i, 0u, DC_STREAM_Y0) * (double)ny);
+                        y0 = y0 < 0 ? 0 : (y0 > ny - 1 ? ny - 1 : y0);
+                        ys[a] = y0;
+                    } else {
+                        // searchsortedfirst(GG[ystate[i,it-1],:], wshocks[i,it]) (simulate.jl:148)
+                        const double uw = Sb.given ? Sb.wsh[at] : dc_sim_uniform(sp.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_W);
+                        const double* row = gg + ys[a] * ny;
+                        int j = 0;
+                        while (j < ny && !(row[j] >= uw)) j++;
+                        if (j >= ny) {
+                            flags |= DCEGM_ST_YSTATE_RANGE;
+                            j = ny - 1;
+                        }
+                        ys[a] = j;
+                    }
+                }
+                if (it == 0) {
+                    const double u0 = Sb.given ? Sb.w0sh[i] : dc_sim_uniform(sp.rseed, (uint32_t)i, 0u, DC_STREAM_W0);
+                    w0 = sp.initw0 + u0 * (sp.initw1 - sp.initw0);
+                    inc = MODEL == DCEGM_MODEL_G ? inctab[ys[a]] : CUDART_NAN;
+                } else {
+                    if (prev_worker[a] && !wk) ret[a] = it + 1;  // simulate.jl:95
+                    if (!wk) {
+                        inc = p.pension;
+                    } else if (MODEL == DCEGM_MODEL_G) {
+                        inc = inctab[it * ny + ys[a]];
+                    } else {
+                        const double uw = Sb.given ? Sb.wsh[at] : dc_sim_uniform(sp.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_W);
+                        const double shock = dc_norm_quantile(uw) * sp.sigma;  // simulate.jl:73
+                        const int it1 = it + 1, age = it1 + 19;
+                        inc = it1 > sp.retage ? p.pension
+                                              : dc_exp(sp.inc0 + sp.inc1 * (double)age - sp.inc2 * (double)(age * age) + shock);
+                    }
+                    w0 = w1[a] * p.R + inc;  // simulate.jl:103
+                }
+                // ---- consumption, utility, end-of-period wealth (simulate.jl:106-110) ----
+                const int st = MODEL == DCEGM_MODEL_G ? ys[a] : 0;
+                const int id = wk ? 0 : 1;
+                const double cons = interp_y(line(st, id, 0, 0), line(st, id, 0, 1), lens[(st * 2 + id) * 2 + 0], w0);
+                const double util = u_work(cons, wk, p);
+                double w1n = w0 - cons;
+                if (MODEL == DCEGM_MODEL_F) w1n = w1n > a_hi ? a_hi : (w1n < a_lo ? a_lo : w1n);  // clamp!, simulate.jl:109
+                const bool negc = cons < 0.0;
+                if (negc && MODEL == DCEGM_MODEL_F) flags |= DCEGM_ST_NEG_CONS;
+                // ---- probability to remain worker (simulate.jl:119-121) ----
+                const bool term = it == nT - 1;
+                const double v1 = sim_vfun(true, term, cons, w0, line(st, 0, 1, 0), line(st, 0, 1, 1), lens[(st * 2 + 0) * 2 + 1],
+                                           vb[st * 2 + 0], p);
+                const double v2 = sim_vfun(false, term, cons, w0, line(st, 1, 1, 0), line(st, 1, 1, 1), lens[(st * 2 + 1) * 2 + 1],
+                                           vb[st * 2 + 1], p);
+                const double mx = v1 > v2 ? v1 : v2;
+                const double e1 = dc_exp((v1 - mx) / p.lambda), e2 = dc_exp((v2 - mx) / p.lambda);
+                const double pw = wk ? e1 / (e1 + e2) : 0.0;
+                // ---- next period's state (simulate.jl:124-127, 201) ----
+                const double ud = Sb.given ? Sb.dsh[at] : dc_sim_uniform(sp.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_D);
+                bool next = pw > ud;
+                if (MODEL == DCEGM_MODEL_F && !wk) {
+                    const double ur = Sb.given ? (Sb.rsh ? Sb.rsh[at] : 1.0) : dc_sim_uniform(sp.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_R);
+                    next = p.delta > ur;
+                }
+                prev_worker[a] = wk;
+                working[a] = next;
+                w1[a] = w1n;
+                sum[0] += w0;
+                sum[1] += w1n;
+                sum[2] += cons;
+                sum[3] += util;
+                sum[4] += inc;
+                sum[5] += pw;
+                sum[6] += wk ? 1.0 : 0.0;
+                sum[7] += negc ? 1.0 : 0.0;
+                if (pd) {
+                    pd[0 * npan + at] = w0;
+                    pd[1 * npan + at] = w1n;
+                    pd[2 * npan + at] = cons;
+                    pd[3 * npan + at] = util;
+                    pd[4 * npan + at] = inc;
+                    pd[5 * npan + at] = pw;
+                    pi[0 * npan + at] = MODEL == DCEGM_MODEL_G ? ys[a] + 1 : 0;
+                    pi[1 * npan + at] = worker;
+                }
+            }
+            if (flags) atomicOr(&s_status, flags);
+            // ---- tile sums: shuffle tree, warps ascending, added to the running per-period sums ----
+#pragma unroll
+            for (int k = 0; k < DCEGM_SIM_NMOM; k++) {
+                double v = sum[k];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane == 0) red[wid * DCEGM_SIM_NMOM + k] = v;
+            }
+            __syncthreads();
+            if (tid < DCEGM_SIM_NMOM) {
+                double t = red[tid];
+                for (int w = 1; w < kWarps; w++) t += red[w * DCEGM_SIM_NMOM + tid];
+                mom[it * DCEGM_SIM_NMOM + tid] = tile0 == 0 ? t : mom[it * DCEGM_SIM_NMOM + tid] + t;
+            }
+        }
+#pragma unroll
+        for (int a = 0; a < kSimAgents; a++) {
+            const int i = tile0 + a * kThreads + tid;
+            if (i < nsims) {
+                atomicAdd(&hist[ret[a]], 1);
+                if (Sb.pan_ret) Sb.pan_ret[(size_t)m * nsims + i] = ret[a];
+            }
+        }
+    }
+    __syncthreads();
+    const double dn = (double)nsims;
+    for (int k = tid; k < nT * DCEGM_SIM_NMOM; k += kThreads) Sb.moments[(size_t)m * nT * DCEGM_SIM_NMOM + k] = mom[k] / dn;
+    for (int k = tid; k < nT + 1; k += kThreads) Sb.ret_hist[(size_t)m * (nT + 1) + k] = hist[k];
+    if (tid == 0) Sb.sim_status[m] = s_status;
+}
+
+cudaError_t launch_sim(const DeviceBatch& B0, const SimBatch& Sb, int first, int count, cudaStream_t stream) {
+    DeviceBatch B = B0;
+    B.first = first;
+    const size_t smem = sim_smem_bytes(B.lay);
+    cudaError_t e;
+    if (B.lay.model == DCEGM_MODEL_F) {
+        e = cudaFuncSetAttribute(sim_kernel<DCEGM_MODEL_F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        sim_kernel<DCEGM_MODEL_F><<<count, kThreads, smem, stream>>>(B, Sb);
+    } else {
+        e = cudaFuncSetAttribute(sim_kernel<DCEGM_MODEL_G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        sim_kernel<DCEGM_MODEL_G><<<count, kThreads, smem, stream>>>(B, Sb);
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace dcegm

@@ -57,6 +57,8 @@ extern "C" {
 #define DCEGM_ST_SEG_OVERFLOW    (1u << 7) /* more sections than seg_cap */
 #define DCEGM_ST_INSERT_RANGE    (1u << 8) /* kink insertion index out of range (dc_algo.jl:472,489) */
 #define DCEGM_ST_LOOP_LIMIT      (1u << 9) /* third-line loop did not terminate (envelope.jl:197-240) */
+#define DCEGM_ST_NEG_CONS        (1u << 10) /* simulator: negative consumption, the reference calls error() (simulate.jl:111-116) */
+#define DCEGM_ST_YSTATE_RANGE    (1u << 11) /* simulator: Markov draw beyond the last cumulative weight (simulate.jl:148 would index out of bounds) */
 
 /* ---- model parameters: POD mirror of `mutable struct Param` ----------------
  * reference: src/param.jl:33-70, defaults src/param.json, SURVEY.md App. C.
@@ -242,6 +244,47 @@ int  dcegm_upload_f(dcegm_handle h, const dcegm_param* params, int nmodels, unsi
 int  dcegm_upload_g(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
 int  dcegm_upload_minimal(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
 int  dcegm_run(dcegm_handle h);
+
+/* ---- forward simulation of the resident solution ------------------------------------------
+ * Replaces sim(m::FModel,p) (simulate.jl:61-130) and sim(m::GModel,p) (simulate.jl:133-203) for every
+ * model of the resident batch: p.nsims agents per model, initial wealth U(initw0,initw1), policies
+ * and choice probabilities interpolated from the stored polylines (interp, vfun, ccp as in the solver).
+ *
+ * Shocks.  shocks == NULL: counter-based Philox4x32-10 draws keyed by p.rseed with counter (agent,
+ * period, stream) — see csrc/dc_rng.h; like the reference's Random.seed!(p.rseed) the model index does
+ * not enter.  Otherwise host arrays of the reference's raw rand() draws, column-major [agent + nsims*it]
+ * (all models then share nsims): wshocks (FModel: pushed through the normal quantile and scaled by
+ * sigma, simulate.jl:73; GModel: Markov transition draws, simulate.jl:138,148), dshocks, rshocks
+ * (FModel only, may be NULL when delta == 0), w0shocks [nsims], ystate0 [nsims] (GModel, 1-based).
+ *
+ * Results.  Always: per (model, period) means (moments) and the histogram of retirement ages.
+ * With DCEGM_SIM_PANEL (all models must share nsims) the full Simulation panel (simulate.jl:1-28) is
+ * kept on the device for dcegm_fetch_sim_panel.
+ */
+#define DCEGM_SIM_PANEL (1u << 0)
+#define DCEGM_SIM_NMOM 8
+/* moment k of period it: mean over agents of  0 w0, 1 w1, 2 cons, 3 util, 4 inc, 5 prob_work,
+ * 6 share with worker == 1, 7 share with negative consumption.  Sums run over tiles of 1024 agents
+ * (4 per thread of a 256-thread block, ascending), each tile reduced by the fixed shuffle tree, tiles
+ * added in ascending order — the CPU oracle reproduces the same order bit for bit. */
+typedef struct dcegm_sim_shocks {
+    const double* wshocks;
+    const double* dshocks;
+    const double* rshocks;
+    const double* w0shocks;
+    const int32_t* ystate0;
+    int32_t nsims; /* rows of the matrices above */
+    int32_t _pad;
+} dcegm_sim_shocks;
+int  dcegm_simulate(dcegm_handle h, unsigned flags, const dcegm_sim_shocks* shocks);
+/* moments: double [count][nT][DCEGM_SIM_NMOM]; ret_hist: int32 [count][nT+1], entry a = agents with
+ * ret_age == a (0 = never retired; simulate.jl:95); sim_status: int32 [count] DCEGM_ST_* bits.  Any may be NULL. */
+int  dcegm_fetch_sim_moments(dcegm_handle h, int first, int count, double* moments, int32_t* ret_hist,
+                             int32_t* sim_status);
+/* one model's panel, column-major [agent + nsims*it] like the reference's matrices; ret_age [nsims].
+ * Any destination may be NULL. */
+int  dcegm_fetch_sim_panel(dcegm_handle h, int model, double* w0, double* w1, double* cons, double* util,
+                           double* inc, double* prob_work, int32_t* ystate, int32_t* worker, int32_t* ret_age);
 
 /* ---- diagnostics ---------------------------------------------------------------------
  * Runs n random operand pairs with binary exponents in [emin, emax] (plus exact zeros and exact
