@@ -17,6 +17,8 @@ ST_NONFINITE = 1 << 6
 ST_SEG_OVERFLOW = 1 << 7
 ST_INSERT_RANGE = 1 << 8
 ST_LOOP_LIMIT = 1 << 9
+ST_NEG_CONS = 1 << 10
+ST_YSTATE_RANGE = 1 << 11
 
 STATUS_TEXT = {
     ST_ISECT_OVERFLOW: "more intersections than isec_cap",
@@ -29,6 +31,8 @@ STATUS_TEXT = {
     ST_SEG_OVERFLOW: "more sections than seg_cap",
     ST_INSERT_RANGE: "kink insertion index out of range (dc_algo.jl:472,489)",
     ST_LOOP_LIMIT: "third-line loop did not terminate (envelope.jl:197-240)",
+    ST_NEG_CONS: "simulator: negative consumption (simulate.jl:111-116 calls error())",
+    ST_YSTATE_RANGE: "simulator: Markov draw beyond the last cumulative weight (simulate.jl:148)",
 }
 
 MODEL_F, MODEL_G, MODEL_MINIMAL = 1, 2, 3
@@ -36,6 +40,9 @@ KIND_C, KIND_V, KIND_CDIRTY, KIND_VDIRTY = 0, 1, 2, 3
 KEEP_DIRTY = 1 << 0
 SUMMARY_ONLY = 1 << 1
 SUMMARY_NPROBE = 8
+SIM_PANEL = 1 << 0
+SIM_NMOM = 8
+SIM_MOMENTS = ("w0", "w1", "cons", "util", "inc", "prob_work", "share_worker", "share_neg_cons")
 
 _DOUBLES = [
     "gamma", "beta", "sigma", "lambda_", "R", "a_high", "a_low", "a_lowT", "cfloor", "cfloor_plot",
@@ -76,3 +83,37 @@ class dcegm_timing(C.Structure):
 
 assert C.sizeof(dcegm_param) == 23 * 8 + 8 * 4 + 8
 assert C.sizeof(dcegm_summary) == 6 * 4 + 8 + 2 * 8 * SUMMARY_NPROBE + 16
+
+
+class dcegm_sim_shocks(C.Structure):
+    _fields_ = [("wshocks", C.POINTER(C.c_double)), ("dshocks", C.POINTER(C.c_double)), ("rshocks", C.POINTER(C.c_double)),
+                ("w0shocks", C.POINTER(C.c_double)), ("ystate0", C.POINTER(C.c_int32)), ("nsims", C.c_int32), ("_pad", C.c_int32)]
+
+
+def make_sim_shocks(shocks, nT):
+    """dict(wshocks, dshocks, w0shocks[, rshocks][, ystate0]) of the reference's raw rand() draws, matrices
+    (nsims, nT) -> (struct, keep-alive list).  Matrices are laid out column-major like Julia's."""
+    import numpy as np
+
+    keep = []
+
+    def mat(name):
+        a = shocks.get(name)
+        if a is None:
+            return None
+        a = np.asfortranarray(np.asarray(a, float))
+        keep.append(a)
+        return a.ctypes.data_as(C.POINTER(C.c_double))
+
+    s = dcegm_sim_shocks()
+    w0 = np.ascontiguousarray(shocks["w0shocks"], float)
+    keep.append(w0)
+    s.nsims = len(w0)
+    assert np.asarray(shocks["wshocks"]).shape == (s.nsims, nT)
+    s.wshocks, s.dshocks, s.rshocks = mat("wshocks"), mat("dshocks"), mat("rshocks")
+    s.w0shocks = w0.ctypes.data_as(C.POINTER(C.c_double))
+    if shocks.get("ystate0") is not None:
+        y0 = np.ascontiguousarray(shocks["ystate0"], np.int32)
+        keep.append(y0)
+        s.ystate0 = y0.ctypes.data_as(C.POINTER(C.c_int32))
+    return s, keep

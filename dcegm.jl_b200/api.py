@@ -27,7 +27,7 @@ from .param import Param
 from .solver import Solver
 
 __all__ = ["Point", "MLine", "Envelope", "FModel", "GModel", "runf", "runfdemo", "rung", "minimal_EGM", "bm",
-           "getx", "gety", "gets", "getr", "bound", "DCEGMError", "dc_EGM"]
+           "getx", "gety", "gets", "getr", "bound", "DCEGMError", "dc_EGM", "Simulation", "sim", "rs", "rsg"]
 
 
 class DCEGMError(RuntimeError):
@@ -166,6 +166,7 @@ class GModel(_Model):  # param.jl:237-311
 
 
 _solver = None
+_resident = {"token": None}
 
 
 def _get_solver(device=0):
@@ -178,6 +179,7 @@ def _get_solver(device=0):
 def dc_EGM(p, model=_abi.MODEL_F, demo=False, device=0, strict=True):
     """dc_EGM!(m, p) of the reference for one Param; returns the flat Solution (dc_algo.jl:8-206)."""
     sol = _get_solver(device).solve(model, [p], keep_dirty=demo)
+    _resident["token"] = sol  # the solution now resident on the device (sim() reuses it)
     if strict:
         _raise_for_status(int(sol.status[0]))
     return sol
@@ -232,3 +234,41 @@ def bm(samples=39, device=0, verbose=True):
         print("  minimum time: %(min_ms).3f ms\n  median time:  %(median_ms).3f ms\n  mean time:    %(mean_ms).3f ms\n"
               "  maximum time: %(max_ms).3f ms\n  samples: %(samples)d  (kernel only: %(kernel_ms).3f ms)" % out)
     return out
+
+
+class Simulation:  # simulate.jl:1-28
+    """Panel of one simulated model: matrices (nsims, nT) w0, w1, cons, util, inc, prob_work (float),
+    ystate, worker (int), ret_age (nsims), plus the per-period means the sweep summaries use."""
+
+    def __init__(self, p, panel, moments, ret_hist):
+        self.p = p
+        for k, v in panel.items():
+            setattr(self, k, v)
+        self.moments = {k: moments[:, j] for j, k in enumerate(_abi.SIM_MOMENTS)}
+        self.ret_hist = ret_hist
+
+
+def sim(m, p, shocks=None, device=0, strict=True):
+    """sim(m::FModel,p) / sim(m::GModel,p) (simulate.jl:61-203) on the GPU.  shocks=None draws the
+    counter-based shocks keyed by p.rseed; pass the reference's raw rand() matrices to follow a Julia run."""
+    model = _abi.MODEL_G if isinstance(m, GModel) else _abi.MODEL_F
+    s = _get_solver(device)
+    if _resident["token"] is not m.solution:  # another solve replaced it on the device
+        m.solution = s.solve(model, [p])
+        _resident["token"] = m.solution
+    s.simulate(panel=True, shocks=shocks)
+    mom, hist, st = s.sim_moments()
+    if strict:
+        _raise_for_status(int(st[0]))
+    nsims = p.nsims if shocks is None else len(shocks["w0shocks"])
+    return Simulation(p, s.sim_panel(0, nsims), mom[0], hist[0])
+
+
+def rs(par=None, **kw):  # simulate.jl:271-274
+    m, p = runf(par=par, **kw)
+    return sim(m, p)
+
+
+def rsg(par=None, **kw):  # simulate.jl:279-282
+    m, p = rung(par=par, **kw)
+    return sim(m, p)

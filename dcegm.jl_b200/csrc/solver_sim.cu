@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(kThreads) sim_kernel(DeviceBatch B, SimBatch S
                 if (it == 0) {
                     const double u0 = Sb.given ? Sb.w0sh[i] : dc_sim_uniform(sp.rseed, (uint32_t)i, 0u, DC_STREAM_W0);
                     w0 = sp.initw0 + u0 * (sp.initw1 - sp.initw0);
-                    inc = MODEL == DCEGM_MODEL_G ? inctab[ys[a]] : CUDART_NAN;
+                    inc = MODEL == DCEGM_MODEL_G ? inctab[ys[a]] : __longlong_as_double(0x7ff8000000000000LL);  // stays NaN, simulate.jl:18
                 } else {
                     if (prev_worker[a] && !wk) ret[a] = it + 1;  // simulate.jl:95
                     if (!wk) {

@@ -133,6 +133,39 @@ class Solver:
         self._ck(fn(self.h, arr, n, flags, _dp(xy), xy.shape[0], offsets.ctypes.data_as(C.POINTER(C.c_int64)), C.byref(npts)))
         return xy[: npts.value], offsets
 
+    # ---- forward simulation of the resident solution (simulate.jl:61-203) -----------------------
+    def simulate(self, panel=False, shocks=None):
+        """shocks: None (counter-based draws keyed by Param.rseed) or a dict of the reference's raw rand()
+        matrices, see _abi.make_sim_shocks."""
+        sp, keep = None, None
+        if shocks is not None:
+            st, keep = _abi.make_sim_shocks(shocks, self.layout().nT)
+            sp = C.byref(st)
+        self._ck(self.lib.dcegm_simulate(self.h, _abi.SIM_PANEL if panel else 0, sp))
+        del keep
+
+    def sim_moments(self, first=0, count=None):
+        lay = self.layout()
+        count = lay.nmodels - first if count is None else count
+        mom = np.zeros((count, lay.nT, _abi.SIM_NMOM))
+        hist = np.zeros((count, lay.nT + 1), np.int32)
+        st = np.zeros(count, np.int32)
+        ip = C.POINTER(C.c_int32)
+        self._ck(self.lib.dcegm_fetch_sim_moments(self.h, first, count, _dp(mom), hist.ctypes.data_as(ip), st.ctypes.data_as(ip)))
+        return mom, hist, st
+
+    def sim_panel(self, model, nsims):
+        lay = self.layout()
+        d = {k: np.zeros((nsims, lay.nT), order="F") for k in ("w0", "w1", "cons", "util", "inc", "prob_work")}
+        i = {k: np.zeros((nsims, lay.nT), np.int32, order="F") for k in ("ystate", "worker")}
+        ret = np.zeros(nsims, np.int32)
+        ip = C.POINTER(C.c_int32)
+        self._ck(self.lib.dcegm_fetch_sim_panel(self.h, model, *[_dp(d[k]) for k in ("w0", "w1", "cons", "util", "inc", "prob_work")],
+                                                i["ystate"].ctypes.data_as(ip), i["worker"].ctypes.data_as(ip), ret.ctypes.data_as(ip)))
+        d.update(i)
+        d["ret_age"] = ret
+        return d
+
     def status(self):
         lay = self.layout()
         st = np.zeros(lay.nmodels, np.int32)

@@ -25,6 +25,7 @@
 // Build: see oracle/Makefile (g++ -O2 -ffp-contract=off -pthread).
 #include "../include/dcegm.h"
 #include "../dcegm.jl_b200/csrc/dc_math.h"  // shared reproducible math (portable mode only)
+#include "../dcegm.jl_b200/csrc/dc_rng.h"   // shared definition of the simulator's counter-based shocks
 
 #include <algorithm>
 #include <atomic>
@@ -1089,12 +1090,233 @@ void solve_minimal_one(const dcegm_param& pin, int m, const OutView& o) {
     o.status[m] = (int32_t)status;
 }
 
+
+// ---------------------------------------------------------------------------------------
+// forward simulation — simulate.jl:61-130 (FModel) and :133-203 (GModel)
+// ---------------------------------------------------------------------------------------
+// Parity unpinned: the reference has no test of sim(), and its shocks come from Julia's global RNG.
+// Shocks here are either given (the raw rand() draws, column-major [agent + nsims*it]) or the
+// counter-based draws of dc_rng.h (the CUDA library's definition, shared header).  Per-period sums
+// follow the CUDA kernel's fixed order: tiles of 1024 agents, thread t of 256 owns agents
+// tile0 + a*256 + t (a = 0..3, ascending), 32-lane xor butterfly, warps ascending, tiles ascending.
+struct SimLines {
+    const dcegm_layout* lay;
+    const double* lines;
+    const int32_t* lens;
+    const double* vbound;
+    int m;
+    const Pt* line(int it, int st, int id, int kind, int* n) const {
+        size_t slot = ((((size_t)m * lay->nT + it) * lay->nstate + st) * 2 + id) * 2 + kind;
+        *n = lens[slot] < lay->cap ? lens[slot] : lay->cap;
+        return reinterpret_cast<const Pt*>(lines + slot * (size_t)lay->cap * 2);
+    }
+    double vb(int it, int st, int id) const { return vbound[(((size_t)m * lay->nT + it) * lay->nstate + st) * 2 + id]; }
+};
+
+// vfun (dc_algo.jl:220-251) on a flat line; it0 is the 0-based period of the line
+double sim_vfun(bool worker_line, bool terminal, double c1, double m1, const Pt* v, int n, double vb, const Par& p) {
+    if (terminal && p.nu > 0) return bequest_work(c1, false, p);
+    bool mask = terminal || (m1 < v[1].x);
+    if (mask) return u_work(c1, worker_line, p) + p.beta * vb;
+    return interp_pt(v, n, m1).y;
+}
+
+double sim_income(int it1, const Par& p, double shock) {  // utils.jl:243-250
+    int age = it1 + 19;
+    if (it1 > p.retage) return p.pension;
+    return m_exp(p.inc0 + p.inc1 * (double)age - p.inc2 * (double)(age * age) + shock, p.portable);
+}
+
+void simulate_one(int model, const dcegm_param& pin, const SimLines& S, int portable, const dcegm_sim_shocks* sh,
+                  double* moments /*[nT][8]*/, int32_t* ret_hist /*[nT+1]*/, int32_t* status_out, double* pan_d,
+                  int32_t* pan_i, int32_t* pan_ret) {
+    Par p = derive(pin, portable);
+    const int nT = p.nT, ny = p.ny;
+    const int nsims = sh ? sh->nsims : p.nsims;
+    const bool G = model == DCEGM_MODEL_G;
+    const int TPB = 256, APT = 4, TILE = TPB * APT, NM = DCEGM_SIM_NMOM;
+    unsigned status = 0;
+    std::vector<double> gg, inctab;
+    if (G) {
+        std::vector<double> yvec, ywgt;
+        if (p.rho == 0) {  // param.jl:278-281
+            std::vector<double> nodes, w;
+            gauss_hermite(ny, nodes, w);
+            yvec.resize(ny);
+            ywgt.resize((size_t)ny * ny);
+            const double pi = 3.141592653589793;
+            for (int i = 0; i < ny; i++) yvec[i] = std::sqrt(2.0) * p.sigma * nodes[i];
+            for (int iy = 0; iy < ny; iy++)
+                for (int jy = 0; jy < ny; jy++) ywgt[(size_t)iy * ny + jy] = w[jy] * std::pow(pi, -0.5);
+        } else {
+            rouwenhorst(p.rho, 0.0, p.sigma, ny, yvec, ywgt);
+        }
+        gg.resize((size_t)ny * ny);  // cumsum(m.ywgt, dims=2), simulate.jl:145
+        for (int r = 0; r < ny; r++) {
+            double acc = 0.0;
+            for (int j = 0; j < ny; j++) {
+                acc = j == 0 ? ywgt[(size_t)r * ny + j] : acc + ywgt[(size_t)r * ny + j];
+                gg[(size_t)r * ny + j] = acc;
+            }
+        }
+        inctab.resize((size_t)nT * ny);
+        for (int it = 0; it < nT; it++)
+            for (int iy = 0; iy < ny; iy++) inctab[(size_t)it * ny + iy] = sim_income(it + 1, p, yvec[iy]);
+    }
+    std::vector<double> mom((size_t)nT * NM, 0.0);
+    std::vector<int32_t> hist(nT + 1, 0);
+    const size_t npan = (size_t)nsims * nT;
+    const double NaN = std::numeric_limits<double>::quiet_NaN();
+    std::vector<double> part((size_t)nT * NM * TPB);  // per-thread partial sums of the current tile
+    for (int tile0 = 0; tile0 < nsims; tile0 += TILE) {
+        std::fill(part.begin(), part.end(), 0.0);
+        for (int t = 0; t < TPB; t++)
+            for (int a = 0; a < APT; a++) {
+                const int i = tile0 + a * TPB + t;
+                if (i >= nsims) continue;
+                double w1 = 0.0;
+                int ys = 0, ret = 0;
+                bool working = true, prev_worker = true;
+                for (int it = 0; it < nT; it++) {
+                    const size_t at = (size_t)i + (size_t)nsims * it;
+                    const bool wk = working;
+                    double w0, inc;
+                    if (G) {
+                        if (it == 0) {
+                            int y0 = sh ? sh->ystate0[i] - 1
+                                        : (int)(dc_sim_uniform(p.rseed, (uint32_t)i, 0u, DC_STREAM_Y0) * (double)ny);  // rand(1:ny), simulate.jl:141
+                            ys = y0 < 0 ? 0 : (y0 > ny - 1 ? ny - 1 : y0);
+                        } else {  // simulate.jl:148
+                            const double uw = sh ? sh->wshocks[at] : dc_sim_uniform(p.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_W);
+                            const double* row = &gg[(size_t)ys * ny];
+                            int j = 0;
+                            while (j < ny && !(row[j] >= uw)) j++;
+                            if (j >= ny) {
+                                status |= DCEGM_ST_YSTATE_RANGE;
+                                j = ny - 1;
+                            }
+                            ys = j;
+                        }
+                    }
+                    if (it == 0) {  // simulate.jl:82-86, 160-164
+                        const double u0 = sh ? sh->w0shocks[i] : dc_sim_uniform(p.rseed, (uint32_t)i, 0u, DC_STREAM_W0);
+                        w0 = p.initw0 + u0 * (p.initw1 - p.initw0);
+                        inc = G ? inctab[ys] : NaN;
+                    } else {
+                        if (prev_worker && !wk) ret = it + 1;  // simulate.jl:95
+                        if (!wk) {
+                            inc = p.pension;
+                        } else if (G) {
+                            inc = inctab[(size_t)it * ny + ys];
+                        } else {
+                            const double uw = sh ? sh->wshocks[at] : dc_sim_uniform(p.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_W);
+                            inc = sim_income(it + 1, p, dc_norm_quantile(uw) * p.sigma);  // simulate.jl:73,99
+                        }
+                        w0 = w1 * p.R + inc;  // simulate.jl:103
+                    }
+                    const int st = G ? ys : 0, id = wk ? 0 : 1;
+                    int n;
+                    const Pt* cl = S.line(it, st, id, 0, &n);
+                    const double cons = interp_pt(cl, n, w0).y;  // simulate.jl:106-110
+                    const double util = u_work(cons, wk, p);
+                    double w1n = w0 - cons;
+                    if (!G) w1n = w1n > p.a_high ? p.a_high : (w1n < p.a_low ? p.a_low : w1n);  // clamp!, simulate.jl:109
+                    const bool negc = cons < 0.0;
+                    if (negc && !G) status |= DCEGM_ST_NEG_CONS;
+                    const bool term = it == nT - 1;
+                    int n1, n2;
+                    const Pt* l1 = S.line(it, st, 0, 1, &n1);
+                    const Pt* l2 = S.line(it, st, 1, 1, &n2);
+                    const double v1 = sim_vfun(true, term, cons, w0, l1, n1, S.vb(it, st, 0), p);
+                    const double v2 = sim_vfun(false, term, cons, w0, l2, n2, S.vb(it, st, 1), p);
+                    const double pw = wk ? ccp2(v1, v2, p.lambda, p.portable) : 0.0;  // simulate.jl:121
+                    const double ud = sh ? sh->dshocks[at] : dc_sim_uniform(p.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_D);
+                    bool next = pw > ud;  // simulate.jl:124
+                    if (!G && !wk) {      // simulate.jl:127
+                        const double ur = sh ? (sh->rshocks ? sh->rshocks[at] : 1.0) : dc_sim_uniform(p.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_R);
+                        next = p.delta > ur;
+                    }
+                    prev_worker = wk;
+                    working = next;
+                    w1 = w1n;
+                    double* ps = &part[((size_t)it * NM) * TPB + t];
+                    const double vals[8] = {w0, w1n, cons, util, inc, pw, wk ? 1.0 : 0.0, negc ? 1.0 : 0.0};
+                    for (int k = 0; k < NM; k++) ps[(size_t)k * TPB] += vals[k];
+                    if (pan_d) {
+                        for (int k = 0; k < 6; k++) pan_d[(size_t)k * npan + at] = vals[k];
+                        pan_i[at] = G ? ys + 1 : 0;
+                        pan_i[npan + at] = wk ? 1 : 2;
+                    }
+                }
+                hist[ret]++;
+                if (pan_ret) pan_ret[i] = ret;
+            }
+        for (int it = 0; it < nT; it++)
+            for (int k = 0; k < NM; k++) {
+                const double* v = &part[((size_t)it * NM + k) * TPB];
+                double tsum = 0.0;
+                for (int w = 0; w < TPB / 32; w++) {
+                    double lane[32], nxt[32];
+                    for (int l = 0; l < 32; l++) lane[l] = v[w * 32 + l];
+                    for (int o = 16; o > 0; o >>= 1) {
+                        for (int l = 0; l < 32; l++) nxt[l] = lane[l] + lane[l ^ o];
+                        for (int l = 0; l < 32; l++) lane[l] = nxt[l];
+                    }
+                    tsum = w == 0 ? lane[0] : tsum + lane[0];
+                }
+                mom[(size_t)it * NM + k] = tile0 == 0 ? tsum : mom[(size_t)it * NM + k] + tsum;
+            }
+    }
+    const double dn = (double)nsims;
+    for (size_t k = 0; k < mom.size(); k++) moments[k] = mom[k] / dn;
+    for (int k = 0; k <= nT; k++) ret_hist[k] = hist[k];
+    *status_out = (int32_t)status;
+}
+
 }  // namespace
 
 // =========================================================================================
 // exported C interface of the oracle (ctypes: oracle/oracle.py)
 // =========================================================================================
 extern "C" {
+void oracle_philox(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* out) {
+    dc_philox4x32_10(c0, c1, c2, c3, k0, k1, out);
+}
+double oracle_sim_uniform(int64_t seed, uint32_t agent, uint32_t period, uint32_t stream) {
+    return dc_sim_uniform(seed, agent, period, stream);
+}
+double oracle_norm_quantile(double p) { return dc_norm_quantile(p); }
+
+// forward simulation of models solved in the shared flat layout (lines/lens/vbound as written by
+// oracle_solve or fetched from the CUDA library).  panel_model >= 0 also fills that model's panel.
+int oracle_simulate(int model, const dcegm_param* params, int nmodels, int portable, const dcegm_layout* lay,
+                    const double* lines, const int32_t* lens, const double* vbound, const dcegm_sim_shocks* shocks,
+                    int nthreads, double* moments, int32_t* ret_hist, int32_t* sim_status, int panel_model, double* pan_d,
+                    int32_t* pan_i, int32_t* pan_ret) {
+    if (model != DCEGM_MODEL_F && model != DCEGM_MODEL_G) return -1;
+    const int nT = lay->nT;
+    std::atomic<int> next(0);
+    auto work = [&]() {
+        for (;;) {
+            int m = next.fetch_add(1);
+            if (m >= nmodels) break;
+            SimLines S{lay, lines, lens, vbound, m};
+            const bool pan = m == panel_model;
+            simulate_one(model, params[m], S, portable, shocks, moments + (size_t)m * nT * DCEGM_SIM_NMOM,
+                         ret_hist + (size_t)m * (nT + 1), sim_status + m, pan ? pan_d : nullptr, pan ? pan_i : nullptr,
+                         pan ? pan_ret : nullptr);
+        }
+    };
+    if (nthreads <= 1)
+        work();
+    else {
+        std::vector<std::thread> pool;
+        for (int t = 0; t < nthreads; t++) pool.emplace_back(work);
+        for (auto& th : pool) th.join();
+    }
+    return 0;
+}
+
 
 // geometry shared with the CUDA library (same formula as dcegm.jl_b200/csrc): the tests
 // compare flat buffers slot by slot.

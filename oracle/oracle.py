@@ -22,7 +22,8 @@ def build(force=False):
     src = os.path.join(_HERE, "dcegm_oracle.cpp")
     hdr = os.path.join(_HERE, "..", "include", "dcegm.h")
     mth = os.path.join(_HERE, "..", "dcegm.jl_b200", "csrc", "dc_math.h")
-    srcs = [f for f in (src, hdr, mth) if os.path.exists(f)]
+    rng = os.path.join(_HERE, "..", "dcegm.jl_b200", "csrc", "dc_rng.h")
+    srcs = [f for f in (src, hdr, mth, rng) if os.path.exists(f)]
     if force or not os.path.exists(so) or (srcs and os.path.getmtime(so) < max(os.path.getmtime(f) for f in srcs)):
         subprocess.check_call(["make", "-C", _HERE, "-B" if force else "-s"], stdout=subprocess.DEVNULL)
     return so
@@ -208,3 +209,40 @@ def linrange(lo, hi, n):
     out = np.zeros(n)
     lib().oracle_linrange(C.c_double(lo), C.c_double(hi), n, _p(out))
     return out
+
+
+def simulate(model, params, sol, shocks=None, portable=False, nthreads=1, panel_model=-1):
+    """Forward simulation (simulate.jl:61-203) of the models in `sol` (a Solution in the shared layout).
+    Returns (moments [n,nT,8], ret_hist [n,nT+1], status [n], panel dict or None)."""
+    from dcegm_jl_b200 import _abi as A
+
+    arr = params_array(params)
+    n = len(arr)
+    nT = arr[0].nT
+    mom = np.zeros((n, nT, A.SIM_NMOM))
+    hist = np.zeros((n, nT + 1), np.int32)
+    st = np.zeros(n, np.int32)
+    sp, keep = None, None
+    nsims = arr[max(panel_model, 0)].nsims
+    if shocks is not None:
+        ss, keep = A.make_sim_shocks(shocks, nT)
+        sp = C.byref(ss)
+        nsims = ss.nsims
+    pd = pi = pr = None
+    if panel_model >= 0:
+        pd = np.zeros((6, nT, nsims))
+        pi = np.zeros((2, nT, nsims), np.int32)
+        pr = np.zeros(nsims, np.int32)
+    lay = sol.lay
+    rc = lib().oracle_simulate(
+        C.c_int(model), arr, C.c_int(n), C.c_int(int(portable)), C.byref(lay), _p(sol.lines), _p(sol.lens, C.c_int32),
+        _p(sol.vbound), sp, C.c_int(nthreads), _p(mom), _p(hist, C.c_int32), _p(st, C.c_int32), C.c_int(panel_model),
+        _p(pd) if pd is not None else None, _p(pi, C.c_int32) if pi is not None else None,
+        _p(pr, C.c_int32) if pr is not None else None)
+    assert rc == 0
+    panel = None
+    if panel_model >= 0:
+        names = ("w0", "w1", "cons", "util", "inc", "prob_work")
+        panel = {k: pd[j].T for j, k in enumerate(names)}  # (nsims, nT) views of column-major storage
+        panel["ystate"], panel["worker"], panel["ret_age"] = pi[0].T, pi[1].T, pr
+    return mom, hist, st, panel
