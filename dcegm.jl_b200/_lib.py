@@ -19,7 +19,7 @@ EXPORTS = [
     "dcegm_fetch_meta", "dcegm_fetch_isects", "dcegm_fetch_removed", "dcegm_fetch_dirty", "dcegm_fetch_packed",
     "dcegm_status", "dcegm_summaries", "dcegm_summaries_to_device", "dcegm_last_timing", "dcegm_upload_f",
     "dcegm_upload_g", "dcegm_upload_minimal", "dcegm_run", "dcegm_debug_math_check", "dcegm_solve_f_packed", "dcegm_solve_g_packed",
-    "dcegm_simulate", "dcegm_fetch_sim_moments", "dcegm_fetch_sim_panel",
+    "dcegm_simulate", "dcegm_fetch_sim_moments", "dcegm_fetch_sim_panel", "dcegm_sim_moments_to_device",
 ]
 
 
@@ -58,6 +58,7 @@ def load():
     lib.dcegm_simulate.argtypes = [H, C.c_uint, C.POINTER(_abi.dcegm_sim_shocks)]
     lib.dcegm_fetch_sim_moments.argtypes = [H, C.c_int, C.c_int, dp, ip, ip]
     lib.dcegm_fetch_sim_panel.argtypes = [H, C.c_int, dp, dp, dp, dp, dp, dp, ip, ip, ip]
+    lib.dcegm_sim_moments_to_device.argtypes = [H, C.c_void_p, C.c_size_t]
     lib.dcegm_run.argtypes = [H]
     lib.dcegm_get_layout.argtypes = [H, C.POINTER(_abi.dcegm_layout)]
     lib.dcegm_fetch_line.argtypes = [H, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, dp, C.c_int, C.POINTER(C.c_int)]

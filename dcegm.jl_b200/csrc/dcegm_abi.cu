@@ -646,6 +646,17 @@ int dcegm_fetch_sim_moments(dcegm_handle h, int first, int count, double* moment
     return DCEGM_OK;
 }
 
+int dcegm_sim_moments_to_device(dcegm_handle h, void* dst_device, size_t bytes) {
+    int rc = need_solution(h);
+    if (rc) return rc;
+    if (!h->simulated) return fail(h, DCEGM_E_NOSOLUTION, "no simulation: call dcegm_simulate first");
+    const size_t need = sizeof(double) * (size_t)h->batch.lay.nmodels * h->batch.lay.nT * DCEGM_SIM_NMOM;
+    if (!dst_device || bytes < need) return fail(h, DCEGM_E_CAPACITY, "dcegm_sim_moments_to_device: destination too small");
+    CK(cudaMemcpyAsync(dst_device, h->mom.p, need, cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return DCEGM_OK;
+}
+
 int dcegm_fetch_sim_panel(dcegm_handle h, int model, double* w0, double* w1, double* cons, double* util, double* inc,
                           double* prob_work, int32_t* ystate, int32_t* worker, int32_t* ret_age) {
     int rc = need_solution(h);

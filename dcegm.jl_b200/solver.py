@@ -154,6 +154,9 @@ class Solver:
         self._ck(self.lib.dcegm_fetch_sim_moments(self.h, first, count, _dp(mom), hist.ctypes.data_as(ip), st.ctypes.data_as(ip)))
         return mom, hist, st
 
+    def sim_moments_to_device(self, ptr, nbytes):
+        self._ck(self.lib.dcegm_sim_moments_to_device(self.h, C.c_void_p(ptr), nbytes))
+
     def sim_panel(self, model, nsims):
         lay = self.layout()
         d = {k: np.zeros((nsims, lay.nT), order="F") for k in ("w0", "w1", "cons", "util", "inc", "prob_work")}

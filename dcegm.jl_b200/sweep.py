@@ -48,3 +48,41 @@ def summaries_from_bytes(t):
     from .solver import SUMMARY_DTYPE
 
     return np.frombuffer(t.cpu().numpy().tobytes(), dtype=SUMMARY_DTYPE)
+
+
+def run_sweep(model, params, simulate=False, dist=None, device=0, keep_lines=False):
+    """One parameter sweep on the ranks of `dist` (or one GPU): rank r solves the contiguous shard
+    shard_range(len(params), r, world) of the batch on its GPU, optionally simulates it forward
+    (simulate.jl:61-203), and the per-model summary records — plus the per-period simulation moments — are
+    all-gathered once over NCCL from device buffers.  Returns (summaries [n], moments [n,nT,8] or None)
+    in global model order on every rank."""
+    import torch
+
+    from . import _abi
+    from .param import params_array
+    from .solver import SUMMARY_DTYPE, Solver
+
+    world = dist.get_world_size() if dist is not None and dist.is_initialized() else 1
+    rank = dist.get_rank() if world > 1 else 0
+    n = len(params)
+    lo, hi = shard_range(n, rank, world)
+    arr = params_array(list(params[lo:hi]))
+    cnt = hi - lo
+    dev = torch.device("cuda", device)
+    with Solver(device) as s:
+        s.solve(model, arr, summary_only=not (keep_lines or simulate), fetch=False)
+        nT = s.layout().nT
+        sb = SUMMARY_DTYPE.itemsize * cnt
+        send = torch.empty(sb, dtype=torch.uint8, device=dev)
+        s.summaries_to_device(send.data_ptr(), sb)
+        out = gather_summaries(send, n, SUMMARY_DTYPE.itemsize, dist if world > 1 else None)
+        summ = summaries_from_bytes(out)
+        mom = None
+        if simulate:
+            s.simulate()
+            rec = nT * _abi.SIM_NMOM * 8
+            sendm = torch.empty(rec * cnt, dtype=torch.uint8, device=dev)
+            s.sim_moments_to_device(sendm.data_ptr(), rec * cnt)
+            outm = gather_summaries(sendm, n, rec, dist if world > 1 else None)
+            mom = np.frombuffer(outm.cpu().numpy().tobytes(), dtype=np.float64).reshape(n, nT, _abi.SIM_NMOM)
+    return summ, mom

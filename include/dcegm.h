@@ -281,6 +281,9 @@ int  dcegm_simulate(dcegm_handle h, unsigned flags, const dcegm_sim_shocks* shoc
  * ret_age == a (0 = never retired; simulate.jl:95); sim_status: int32 [count] DCEGM_ST_* bits.  Any may be NULL. */
 int  dcegm_fetch_sim_moments(dcegm_handle h, int first, int count, double* moments, int32_t* ret_hist,
                              int32_t* sim_status);
+/* device-to-device copy of the moments (nmodels*nT*DCEGM_SIM_NMOM doubles) into caller-provided device
+ * memory: the second part of the allgather payload of a multi-GPU sweep */
+int  dcegm_sim_moments_to_device(dcegm_handle h, void* dst_device, size_t bytes);
 /* one model's panel, column-major [agent + nsims*it] like the reference's matrices; ret_age [nsims].
  * Any destination may be NULL. */
 int  dcegm_fetch_sim_panel(dcegm_handle h, int model, double* w0, double* w1, double* cons, double* util,
