@@ -25,6 +25,9 @@ NA, NT, NY = 500, 25, 5
 BATCH = 4096
 # 2 lines x 2 choices x 24 periods x 501 points x 16 B + terminal 128 B + param 248 B
 ALGO_BYTES_PER_MODEL = 2 * 2 * 24 * 501 * 16 + 128 + 248
+# dram__bytes_read.sum + dram__bytes_write.sum of solve_f_kernel per model, from the `ncu --set full` capture
+# summarised in profiles/r1d_solve_f_ncu_summary.md (904.3 MB for 1184 models)
+NCU_DRAM_BYTES_PER_MODEL = 904.3e6 / 1184
 WORKLOAD = "C3: retirement model (FModel) batch, na=500, nT=25, ny=5, log10(lambda)~U(log10 2e-6, log10 0.2), sigma~U(0,0.6)"
 
 
@@ -112,7 +115,7 @@ def run_reference(args):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    sample = 64 * threads
+    sample = min(BATCH, 256 * threads)  # a few seconds of CPU work per step
     for _ in range(args.warmup):
         cpu_reference_run(min(sample, 4 * threads), threads)
     tot_t, tot_n = 0.0, 0
@@ -268,7 +271,8 @@ def main():
                        "vs_baseline_ref": "README.md:118-128: 125.947 ms median per solve = 7.94 models/s, 1 laptop core, Julia",
                        "flagged_models": n_flagged},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src,
+                         "traffic": NCU_DRAM_BYTES_PER_MODEL * nper, "traffic_source": "ncu --set full, profiles/r1d_solve_f_ncu_summary.md, bytes per launch scaled to this batch",
+                         "peak_source": peak_src,
                          "note": "dominant kernel solve_f_kernel is FP64-pipe bound by construction (SURVEY.md §8d): "
                                  "~70 FP64 instr per algorithmic byte; HBM fraction reported as the metric asks"},
             "e2e": {"value": e2e_value, "unit": "models/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
@@ -277,7 +281,7 @@ def main():
         }
         if not args.no_cpu:
             threads = os.cpu_count() or 1
-            sample = 64 * threads
+            sample = min(BATCH, 512 * threads)  # ~10-20 s of CPU work
             v, dt = cpu_reference_run(sample, threads)
             out["cpu_baseline"] = {"value": v, "unit": "models/s", "cores": threads, "kind": "port",
                                    "sample": f"first {sample} models of the same C3 batch, C++ restatement of DCEGM.jl "
