@@ -10,8 +10,8 @@ from . import _abi
 from .param import Param, DEFAULTS
 from .solution import Solution
 from .api import (Point, MLine, Envelope, FModel, GModel, runf, runfdemo, rung, minimal_EGM, bm, getx, gety, gets,
-                  getr, bound, DCEGMError, Simulation, sim, rs, rsg)
+                  getr, bound, DCEGMError, Simulation, sim, rs, rsg, minimal_EGM_borrow, minimal_EGM_bequest)
 
 __all__ = ["Param", "DEFAULTS", "Solution", "_abi", "Point", "MLine", "Envelope", "FModel", "GModel", "runf",
            "runfdemo", "rung", "minimal_EGM", "bm", "getx", "gety", "gets", "getr", "bound", "DCEGMError",
-           "Simulation", "sim", "rs", "rsg"]
+           "Simulation", "sim", "rs", "rsg", "minimal_EGM_borrow", "minimal_EGM_bequest"]

@@ -36,6 +36,7 @@ STATUS_TEXT = {
 }
 
 MODEL_F, MODEL_G, MODEL_MINIMAL = 1, 2, 3
+MODEL_MINIMAL_BORROW, MODEL_MINIMAL_BEQUEST = 4, 5
 KIND_C, KIND_V, KIND_CDIRTY, KIND_VDIRTY = 0, 1, 2, 3
 KEEP_DIRTY = 1 << 0
 SUMMARY_ONLY = 1 << 1

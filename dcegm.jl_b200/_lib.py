@@ -19,7 +19,7 @@ EXPORTS = [
     "dcegm_fetch_meta", "dcegm_fetch_isects", "dcegm_fetch_removed", "dcegm_fetch_dirty", "dcegm_fetch_packed",
     "dcegm_status", "dcegm_summaries", "dcegm_summaries_to_device", "dcegm_last_timing", "dcegm_upload_f",
     "dcegm_upload_g", "dcegm_upload_minimal", "dcegm_run", "dcegm_debug_math_check", "dcegm_solve_f_packed", "dcegm_solve_g_packed",
-    "dcegm_simulate", "dcegm_fetch_sim_moments", "dcegm_fetch_sim_panel", "dcegm_sim_moments_to_device",
+    "dcegm_simulate", "dcegm_fetch_sim_moments", "dcegm_fetch_sim_panel", "dcegm_sim_moments_to_device", "dcegm_solve_minimal_borrow", "dcegm_solve_minimal_bequest",
 ]
 
 
@@ -50,7 +50,7 @@ def load():
     lib.dcegm_last_error.restype = C.c_char_p
     lib.dcegm_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
     lib.dcegm_host_free.argtypes = [C.c_void_p]
-    for f in ("dcegm_solve_f", "dcegm_solve_g", "dcegm_solve_minimal", "dcegm_upload_f", "dcegm_upload_g",
+    for f in ("dcegm_solve_f", "dcegm_solve_g", "dcegm_solve_minimal", "dcegm_solve_minimal_borrow", "dcegm_solve_minimal_bequest", "dcegm_upload_f", "dcegm_upload_g",
               "dcegm_upload_minimal"):
         getattr(lib, f).argtypes = [H, PP, C.c_int, C.c_uint]
     for f in ("dcegm_solve_f_packed", "dcegm_solve_g_packed"):

@@ -27,7 +27,8 @@ from .param import Param
 from .solver import Solver
 
 __all__ = ["Point", "MLine", "Envelope", "FModel", "GModel", "runf", "runfdemo", "rung", "minimal_EGM", "bm",
-           "getx", "gety", "gets", "getr", "bound", "DCEGMError", "dc_EGM", "Simulation", "sim", "rs", "rsg"]
+           "getx", "gety", "gets", "getr", "bound", "DCEGMError", "dc_EGM", "Simulation", "sim", "rs", "rsg",
+           "minimal_EGM_borrow", "minimal_EGM_bequest"]
 
 
 class DCEGMError(RuntimeError):
@@ -212,6 +213,32 @@ def minimal_EGM(p=None, device=0):
         m.append(x)
         c.append(y)
     return m, c
+
+
+def _minimal_lines(model, p, device, kinds):
+    p = p or Param()
+    sol = _get_solver(device).solve(model, [p])
+    _resident["token"] = sol
+    _raise_for_status(int(sol.status[0]))
+    out = [[] for _ in range(1 + len(kinds))]
+    for it in range(p.nT):
+        x, y = sol.line(0, kinds[0], 0, it)
+        out[0].append(x)
+        out[1].append(y)
+        for j, k in enumerate(kinds[1:]):
+            out[2 + j].append(sol.line(0, k, 0, it)[1])
+    return tuple(out)
+
+
+def minimal_EGM_borrow(p=None, device=0):
+    """minimal_EGM_borrow(p) (minimal_EGM.jl:49-89): returns (m, c) — the reference's third return value is the plot."""
+    return _minimal_lines(_abi.MODEL_MINIMAL_BORROW, p, device, (_abi.KIND_C,))
+
+
+def minimal_EGM_bequest(p=None, device=0):
+    """minimal_EGM_bequest(p) (minimal_EGM.jl:92-159).  The reference returns only the two-panel plot; this
+    returns the plotted data (m, c, v), lists over it = 1..nT."""
+    return _minimal_lines(_abi.MODEL_MINIMAL_BEQUEST, p, device, (_abi.KIND_C, _abi.KIND_V))
 
 
 def bm(samples=39, device=0, verbose=True):

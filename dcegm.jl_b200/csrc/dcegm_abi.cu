@@ -100,7 +100,7 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
     if (lay.cap >= 2 * kSearchTop) return fail(h, DCEGM_E_INVALID, "na too large for the shared-memory resident solver");
     size_t smem = model == DCEGM_MODEL_F   ? solver_f_smem_bytes(lay.cap, lay.isec_cap)
                   : model == DCEGM_MODEL_G ? solver_g_smem_bytes(lay.cap, lay.isec_cap, na, ny)
-                                           : (size_t)(4 * (na + 1) * 8 + 1024);
+                                           : (size_t)(6 * (na + 1) * 8 + 1024);
     if ((long long)smem > (long long)h->max_smem_optin) {
         char msg[256];
         snprintf(msg, sizeof msg,
@@ -427,6 +427,14 @@ int dcegm_solve_f(dcegm_handle h, const dcegm_param* p, int n, unsigned flags) {
 }
 int dcegm_solve_g(dcegm_handle h, const dcegm_param* p, int n, unsigned flags) {
     int rc = upload(h, DCEGM_MODEL_G, p, n, flags);
+    return rc ? rc : run(h);
+}
+int dcegm_solve_minimal_borrow(dcegm_handle h, const dcegm_param* p, int n, unsigned flags) {
+    int rc = upload(h, DCEGM_MODEL_MINIMAL_BORROW, p, n, flags);
+    return rc ? rc : run(h);
+}
+int dcegm_solve_minimal_bequest(dcegm_handle h, const dcegm_param* p, int n, unsigned flags) {
+    int rc = upload(h, DCEGM_MODEL_MINIMAL_BEQUEST, p, n, flags);
     return rc ? rc : run(h);
 }
 int dcegm_solve_minimal(dcegm_handle h, const dcegm_param* p, int n, unsigned flags) {

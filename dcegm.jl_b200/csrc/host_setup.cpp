@@ -241,7 +241,8 @@ bool build_tables(int model, const dcegm_param* params, int nmodels, HostTables&
             return false;
         }
     }
-    if (model != DCEGM_MODEL_F && model != DCEGM_MODEL_G && model != DCEGM_MODEL_MINIMAL) {
+    const bool minimal = model == DCEGM_MODEL_MINIMAL || model == DCEGM_MODEL_MINIMAL_BORROW || model == DCEGM_MODEL_MINIMAL_BEQUEST;
+    if (model != DCEGM_MODEL_F && model != DCEGM_MODEL_G && !minimal) {
         *why = kWhy[4];
         return false;
     }
@@ -254,7 +255,8 @@ bool build_tables(int model, const dcegm_param* params, int nmodels, HostTables&
     for (int m = 0; m < nmodels; m++) {
         const dcegm_param& p = params[m];
         out.models[m] = make_dev(p);
-        const double glo = model == DCEGM_MODEL_MINIMAL ? 0.0 : p.a_low;  // minimal_EGM.jl:7
+        // minimal_EGM.jl:7 (from 0), :53 (from a_low), :97 (scaleGrid from 0)
+        const double glo = (model == DCEGM_MODEL_MINIMAL || model == DCEGM_MODEL_MINIMAL_BEQUEST) ? 0.0 : p.a_low;
         auto key = std::make_tuple(glo, p.a_high);
         auto it = grid_of.find(key);
         if (it == grid_of.end()) {
@@ -262,6 +264,8 @@ bool build_tables(int model, const dcegm_param* params, int nmodels, HostTables&
             double* g = out.grids.data() + (size_t)out.ngrids * na;
             if (model == DCEGM_MODEL_G)
                 scale_grid(p.a_low, p.a_high, na, 2, g);  // param.jl:288
+            else if (model == DCEGM_MODEL_MINIMAL_BEQUEST)
+                scale_grid(0.0, p.a_high, na, 1, g);      // minimal_EGM.jl:97
             else
                 linrange(glo, p.a_high, na, g);  // param.jl:205
             it = grid_of.emplace(key, out.ngrids++).first;
@@ -279,7 +283,7 @@ bool build_tables(int model, const dcegm_param* params, int nmodels, HostTables&
     }
     const double inv_sqrt_pi = std::pow(kPi, -0.5);
 
-    const size_t off_per = model == DCEGM_MODEL_MINIMAL ? (size_t)ny : (size_t)(nT - 1) * 2 * ny;
+    const size_t off_per = minimal ? (size_t)ny : (size_t)(nT - 1) * 2 * ny;
     const size_t wgt_per = model == DCEGM_MODEL_G ? (size_t)ny * ny : (size_t)ny;
     out.sim.assign(nmodels, SimModel{});
     out.yvec.assign((size_t)ny * nmodels, 0.0);

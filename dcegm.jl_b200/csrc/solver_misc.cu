@@ -5,14 +5,16 @@
 
 namespace dcegm {
 
-// minimal_EGM (src/minimal_EGM.jl:3-43): log utility, no discrete choice, no value function.
-// One CTA per parameterisation; the whole 24-step recursion runs out of shared memory.
-// Output: kind C lines of (m[it], c[it]) for id 0.
+// minimal_EGM (src/minimal_EGM.jl:3-43), minimal_EGM_borrow (:49-89) and minimal_EGM_bequest (:92-159):
+// log-utility Euler equation, no discrete choice.  One CTA per parameterisation; the whole 24-step
+// recursion runs out of shared memory.  Output: kind C lines (m[it], c[it]) for id 0; the bequest
+// variant also keeps the value function as kind V lines (m[it], v[it]).
 __global__ void __launch_bounds__(kThreads) solve_minimal_kernel(DeviceBatch B) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int m = B.first + blockIdx.x, tid = threadIdx.x;
     __shared__ DevModel s_p;
     __shared__ int s_status;
+    __shared__ double s_ev0;
     if (tid == 0) {
         s_p = B.models[m];
         s_status = 0;
@@ -20,45 +22,75 @@ __global__ void __launch_bounds__(kThreads) solve_minimal_kernel(DeviceBatch B) 
     __syncthreads();
     const DevModel& p = s_p;
     const int na = p.na, ny = p.ny, nT = p.nT;
-    double* buf[2][2];
+    const bool borrow = B.lay.model == DCEGM_MODEL_MINIMAL_BORROW, beq = B.lay.model == DCEGM_MODEL_MINIMAL_BEQUEST;
+    double* buf[2][3];  // [set][m | c | v]
     for (int s = 0; s < 2; s++)
-        for (int a = 0; a < 2; a++) buf[s][a] = (double*)smem + (size_t)(s * 2 + a) * (na + 1);
+        for (int a = 0; a < 3; a++) buf[s][a] = (double*)smem + (size_t)(s * 3 + a) * (na + 1);
     const double* __restrict__ avec = B.grids + (size_t)p.grid * na;
     const double* __restrict__ wgt = B.wgt + (size_t)m * ny;
     const double* __restrict__ ey = B.off + (size_t)m * ny;  // 0.0 + exp(yvec)
+    const double m_lo = borrow ? p.a_low : 0.0;               // minimal_EGM.jl:10, 56, 83
     int cur = 0, nnext = 2;
-    if (tid == 0) {  // minimal_EGM.jl:10-11
-        buf[0][0][0] = 0.0; buf[0][1][0] = 0.0;
+    if (beq) {  // minimal_EGM.jl:102-104: terminal lines on the whole savings grid
+        nnext = na;
+        for (int k = tid; k < na; k += kThreads) {
+            buf[0][0][k] = avec[k];
+            buf[0][1][k] = avec[k];
+            buf[0][2][k] = p.nu > 0 ? p.nu * u_plain(avec[k] + p.bbar, p) : 0.0;
+        }
+    } else if (tid == 0) {  // minimal_EGM.jl:10-11, 56-57
+        buf[0][0][0] = m_lo; buf[0][1][0] = 0.0;
         buf[0][0][1] = p.a_high; buf[0][1][1] = p.a_high;
     }
     __syncthreads();
     {
         const size_t slot = line_slot(B.lay, m, nT - 1, 0, 0, DCEGM_KIND_C);
-        if (tid == 0) B.lens[slot] = 2;
-        if (B.lines && tid < 2) B.lines[slot * (size_t)B.lay.cap + tid] = make_double2(buf[0][0][tid], buf[0][1][tid]);
+        if (tid == 0) B.lens[slot] = nnext;
+        if (B.lines)
+            for (int k = tid; k < nnext; k += kThreads) B.lines[slot * (size_t)B.lay.cap + k] = make_double2(buf[0][0][k], buf[0][1][k]);
+        if (beq) {
+            const size_t sv = line_slot(B.lay, m, nT - 1, 0, 0, DCEGM_KIND_V);
+            if (tid == 0) B.lens[sv] = nnext;
+            if (B.lines)
+                for (int k = tid; k < nnext; k += kThreads) B.lines[sv * (size_t)B.lay.cap + k] = make_double2(buf[0][0][k], buf[0][2][k]);
+        }
     }
     for (int t = nT - 2; t >= 0; t--) {
         const double* nx = buf[cur][0];
         const double* nyv = buf[cur][1];
+        const double* nv = buf[cur][2];
         double* cx = buf[cur ^ 1][0];
         double* cy = buf[cur ^ 1][1];
+        double* cv = buf[cur ^ 1][2];
+        const bool beq_period = beq && t == nT - 2 && p.nu > 0;  // minimal_EGM.jl:124-133
         for (int ia = tid; ia < na; ia += kThreads) {
             const double Ra = p.R * avec[ia];
-            double acc = 0.0;
+            double acc = 0.0, accv = 0.0;
             for (int iy = 0; iy < ny; iy++) {
                 const double w1 = ey[iy] + Ra;                 // minimal_EGM.jl:21
                 double c1 = interp_y(nx, nyv, nnext, w1);      // minimal_EGM.jl:25
                 if (c1 < 0) c1 = p.cfloor;                     // minimal_EGM.jl:26
-                acc = iy == 0 ? wgt[iy] * (1.0 / c1) : acc + wgt[iy] * (1.0 / c1);  // minimal_EGM.jl:27
+                const double mu = beq_period ? 1.0 / (c1 + p.bbar) : 1.0 / c1;
+                acc = iy == 0 ? wgt[iy] * mu : acc + wgt[iy] * mu;  // minimal_EGM.jl:27
+                if (beq) {                                     // minimal_EGM.jl:150-151
+                    const double v1 = interp_y(nx, nv, nnext, w1);
+                    accv = iy == 0 ? wgt[iy] * v1 : accv + wgt[iy] * v1;
+                }
             }
-            const double rhs = p.betaR * acc;                  // minimal_EGM.jl:28
+            const double rhs = (beq_period ? p.betaRnu : p.betaR) * acc;  // minimal_EGM.jl:28, 132
             const double c0 = 1.0 / rhs;                       // minimal_EGM.jl:29
             cx[1 + ia] = avec[ia] + c0;                        // minimal_EGM.jl:30
             cy[1 + ia] = c0;
+            if (beq) {
+                cv[1 + ia] = u_plain(c0, p) + p.beta * accv;   // minimal_EGM.jl:152
+                if (ia == 0) s_ev0 = accv;
+            }
         }
-        if (tid == 0) {  // minimal_EGM.jl:36-37
-            cx[0] = 0.0;
+        __syncthreads();
+        if (tid == 0) {  // minimal_EGM.jl:36-37, 82-83, 146, 152
+            cx[0] = m_lo;
             cy[0] = 0.0;
+            if (beq) cv[0] = s_ev0;
         }
         __syncthreads();
         int flag = 0;
@@ -69,6 +101,12 @@ __global__ void __launch_bounds__(kThreads) solve_minimal_kernel(DeviceBatch B) 
         if (tid == 0) B.lens[slot] = na + 1;
         if (B.lines)
             for (int k = tid; k < na + 1; k += kThreads) B.lines[slot * (size_t)B.lay.cap + k] = make_double2(cx[k], cy[k]);
+        if (beq) {
+            const size_t sv = line_slot(B.lay, m, t, 0, 0, DCEGM_KIND_V);
+            if (tid == 0) B.lens[sv] = na + 1;
+            if (B.lines)
+                for (int k = tid; k < na + 1; k += kThreads) B.lines[sv * (size_t)B.lay.cap + k] = make_double2(cx[k], cv[k]);
+        }
         nnext = na + 1;
         cur ^= 1;
         __syncthreads();
@@ -79,7 +117,7 @@ __global__ void __launch_bounds__(kThreads) solve_minimal_kernel(DeviceBatch B) 
         memset(&sm, 0, sizeof sm);
         sm.status = s_status;
         sm.max_len = na + 1;
-        sm.tot_points = (long long)(nT - 1) * (na + 1) + 2;
+        sm.tot_points = ((long long)(nT - 1) * (na + 1) + (beq ? na : 2)) * (beq ? 2 : 1);
         const double fr[DCEGM_SUMMARY_NPROBE] = {0.02, 0.05, 0.1, 0.2, 0.3, 0.5, 0.7, 0.9};
         double cs = 0.0;
         for (int k = 0; k < nnext; k++) cs += buf[cur][1][k];
@@ -92,7 +130,7 @@ __global__ void __launch_bounds__(kThreads) solve_minimal_kernel(DeviceBatch B) 
 cudaError_t launch_solve_minimal(const DeviceBatch& B0, int first, int count, cudaStream_t stream) {
     DeviceBatch B = B0;
     B.first = first;
-    const size_t smem = (size_t)4 * (B.lay.na + 1) * sizeof(double);
+    const size_t smem = (size_t)6 * (B.lay.na + 1) * sizeof(double);
     static size_t configured = 48 * 1024;
     if (smem > configured) {
         cudaError_t e = cudaFuncSetAttribute(solve_minimal_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

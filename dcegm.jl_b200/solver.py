@@ -49,7 +49,8 @@ class Solver:
         arr = params if isinstance(params, C.Array) else params_array(params)
         flags = (_abi.KEEP_DIRTY if keep_dirty else 0) | (_abi.SUMMARY_ONLY if summary_only else 0)
         fn = {_abi.MODEL_F: self.lib.dcegm_solve_f, _abi.MODEL_G: self.lib.dcegm_solve_g,
-              _abi.MODEL_MINIMAL: self.lib.dcegm_solve_minimal}[model]
+              _abi.MODEL_MINIMAL: self.lib.dcegm_solve_minimal, _abi.MODEL_MINIMAL_BORROW: self.lib.dcegm_solve_minimal_borrow,
+              _abi.MODEL_MINIMAL_BEQUEST: self.lib.dcegm_solve_minimal_bequest}[model]
         self._ck(fn(self.h, arr, len(arr), flags))
         return self.fetch() if fetch and not summary_only else None
 

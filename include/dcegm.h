@@ -105,6 +105,9 @@ void dcegm_param_defaults(dcegm_param* p);
 #define DCEGM_MODEL_F       1   /* dc_EGM!(::FModel)  dc_algo.jl:8-105   */
 #define DCEGM_MODEL_G       2   /* dc_EGM!(::GModel)  dc_algo.jl:112-206 */
 #define DCEGM_MODEL_MINIMAL 3   /* minimal_EGM        minimal_EGM.jl:3-43 */
+#define DCEGM_MODEL_MINIMAL_BORROW  4   /* minimal_EGM_borrow   minimal_EGM.jl:49-89: grid and constraint start at a_low */
+#define DCEGM_MODEL_MINIMAL_BEQUEST 5   /* minimal_EGM_bequest  minimal_EGM.jl:92-159: scaleGrid savings grid, bequest
+                                           motive nu in the penultimate period, value function kept as (id 0, kind v) */
 
 /* ---- line kinds ------------------------------------------------------------ */
 #define DCEGM_KIND_C       0   /* m.c[id,it].env  (policy)            */
@@ -189,6 +192,10 @@ int  dcegm_host_free(void* ptr);
 int  dcegm_solve_f(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
 int  dcegm_solve_g(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
 int  dcegm_solve_minimal(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
+/* the two other teaching models of minimal_EGM.jl; results in the same layout (x = m[it], y = c[it] in
+ * (id 0, kind c); minimal_EGM_bequest also y = v[it] in (id 0, kind v)) */
+int  dcegm_solve_minimal_borrow(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
+int  dcegm_solve_minimal_bequest(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags);
 
 /* Solve and deliver every stored polyline densely packed into caller-owned host memory in one call
  * (what runf/rung return to the caller: all of m.c / m.v).  xy receives the concatenated (x,y) points

@@ -1051,10 +1051,13 @@ void solve_g_one(const dcegm_param& pin, int m, const OutView& o, int literal, i
 // ---------------------------------------------------------------------------------------
 // minimal_EGM — minimal_EGM.jl:3-43 (data only; the reference returns a plot)
 // ---------------------------------------------------------------------------------------
-void solve_minimal_one(const dcegm_param& pin, int m, const OutView& o) {
-    Par p = derive(pin);
+// minimal_EGM (minimal_EGM.jl:3-43), minimal_EGM_borrow (:49-89), minimal_EGM_bequest (:92-159).
+// No reference test covers them: parity unpinned.
+void solve_minimal_one(const dcegm_param& pin, int m, const OutView& o, int model, int portable) {
+    Par p = derive(pin, portable);
     unsigned status = 0;
     const int na = p.na, ny = p.ny, nT = p.nT;
+    const bool borrow = model == DCEGM_MODEL_MINIMAL_BORROW, beq = model == DCEGM_MODEL_MINIMAL_BEQUEST;
     std::vector<double> nodes, w, yvec(ny), ywgt(ny), avec;
     gauss_hermite(ny, nodes, w);  // minimal_EGM.jl:4-6
     const double pi = 3.141592653589793;
@@ -1062,29 +1065,57 @@ void solve_minimal_one(const dcegm_param& pin, int m, const OutView& o) {
         yvec[i] = std::sqrt(2.0) * p.sigma * nodes[i];
         ywgt[i] = w[i] * std::pow(pi, -0.5);
     }
-    linrange(0.0, p.a_high, na, avec);  // minimal_EGM.jl:7
-    Line next = {Pt{0.0, 0.0}, Pt{p.a_high, p.a_high}};  // minimal_EGM.jl:10-11
+    const double m_lo = borrow ? p.a_low : 0.0;
+    if (beq)
+        scale_grid(0.0, p.a_high, na, 1, avec);  // minimal_EGM.jl:97
+    else
+        linrange(m_lo, p.a_high, na, avec);      // minimal_EGM.jl:7, 53
+    Line next, nextv;
+    if (beq) {  // minimal_EGM.jl:102-104
+        next.resize(na);
+        nextv.resize(na);
+        for (int k = 0; k < na; k++) {
+            next[k] = Pt{avec[k], avec[k]};
+            nextv[k] = Pt{avec[k], p.nu > 0 ? p.nu * u_plain(avec[k] + p.bbar, p) : 0.0};
+        }
+        store_line(o, m, nT - 1, 0, 0, DCEGM_KIND_V, nextv, &status);
+    } else {
+        next = {Pt{m_lo, 0.0}, Pt{p.a_high, p.a_high}};  // minimal_EGM.jl:10-11, 56-57
+    }
     store_line(o, m, nT - 1, 0, 0, DCEGM_KIND_C, next, &status);
-    std::vector<double> ey(ny), inv(ny);
+    std::vector<double> ey(ny), inv(ny), v1(ny);
     for (int i = 0; i < ny; i++) ey[i] = 0.0 + std::exp(yvec[i]);
     const int G = p.quad_group > 0 ? p.quad_group : 1;
     for (int it = nT - 1; it >= 1; it--) {
-        Line cur(na + 1);
-        cur[0] = Pt{0.0, 0.0};  // minimal_EGM.jl:36-37
+        const bool beq_period = beq && it == nT - 1 && p.nu > 0;  // minimal_EGM.jl:124-133
+        Line cur(na + 1), curv(na + 1);
+        cur[0] = Pt{m_lo, 0.0};  // minimal_EGM.jl:36-37, 82-83
+        double ev0 = 0.0;
         for (int ia = 0; ia < na; ia++) {
             for (int iy = 0; iy < ny; iy++) {
                 double w1 = ey[iy] + p.R * avec[ia];  // minimal_EGM.jl:21
                 double c1 = interp_y(next, w1);        // minimal_EGM.jl:25
                 if (c1 < 0) c1 = p.cfloor;             // minimal_EGM.jl:26
-                inv[iy] = 1.0 / c1;
+                inv[iy] = beq_period ? 1.0 / (c1 + p.bbar) : 1.0 / c1;
+                if (beq) v1[iy] = interp_y(nextv, w1);  // minimal_EGM.jl:150
             }
-            double emu = quad_sum(ywgt.data(), inv.data(), ny, G);  // minimal_EGM.jl:27
-            double rhs = (p.beta * p.R) * emu;                      // minimal_EGM.jl:28
-            double c0 = 1.0 / rhs;                                  // minimal_EGM.jl:29
-            cur[ia + 1] = Pt{avec[ia] + c0, c0};                    // minimal_EGM.jl:30
+            double emu = quad_sum(ywgt.data(), inv.data(), ny, G);            // minimal_EGM.jl:27
+            double rhs = (beq_period ? (p.beta * p.R * p.nu) : (p.beta * p.R)) * emu;  // minimal_EGM.jl:28, 132
+            double c0 = 1.0 / rhs;                                            // minimal_EGM.jl:29
+            cur[ia + 1] = Pt{avec[ia] + c0, c0};                              // minimal_EGM.jl:30
+            if (beq) {
+                double ev = quad_sum(ywgt.data(), v1.data(), ny, G);          // minimal_EGM.jl:151
+                curv[ia + 1] = Pt{avec[ia] + c0, u_plain(c0, p) + p.beta * ev};  // minimal_EGM.jl:152
+                if (ia == 0) ev0 = ev;
+            }
         }
         if (!strictly_increasing(cur)) status |= DCEGM_ST_NONMONOTONE;
         store_line(o, m, it - 1, 0, 0, DCEGM_KIND_C, cur, &status);
+        if (beq) {
+            curv[0] = Pt{m_lo, ev0};
+            store_line(o, m, it - 1, 0, 0, DCEGM_KIND_V, curv, &status);
+            nextv.swap(curv);
+        }
         next.swap(cur);
     }
     o.status[m] = (int32_t)status;
@@ -1365,7 +1396,7 @@ int oracle_solve(int model, const dcegm_param* params, int nmodels, int keep_dir
             else if (model == DCEGM_MODEL_G)
                 solve_g_one(params[m], m, o, literal, portable);
             else
-                solve_minimal_one(params[m], m, o);
+                solve_minimal_one(params[m], m, o, model, portable);
         }
     };
     int nt = nthreads > 0 ? nthreads : 1;

@@ -86,6 +86,14 @@ def solve_minimal(params, **kw):
     return solve(_abi.MODEL_MINIMAL, params, **kw)
 
 
+def solve_minimal_borrow(params, **kw):
+    return solve(_abi.MODEL_MINIMAL_BORROW, params, **kw)
+
+
+def solve_minimal_bequest(params, **kw):
+    return solve(_abi.MODEL_MINIMAL_BEQUEST, params, **kw)
+
+
 def secondary_envelope(x, y, literal=False):
     x = np.ascontiguousarray(x, float)
     y = np.ascontiguousarray(y, float)

@@ -92,3 +92,34 @@ def test_minimal_egm_sizes(solver, oracle):
         for it in range(40):  # slots beyond len keep whatever an earlier solve left there
             n = g.length(m, 0, 0, it)
             assert np.array_equal(g.lines[m, it, 0, 0, 0, :n], r.lines[m, it, 0, 0, 0, :n])
+
+
+@pytest.mark.parametrize("model", ["borrow", "bequest"])
+def test_minimal_variants_bitwise(model):
+    """minimal_EGM_borrow / minimal_EGM_bequest (minimal_EGM.jl:49-159): GPU == oracle bit for bit
+    (portable math for u(c) in the bequest value function)."""
+    from dcegm_jl_b200 import Param, _abi
+    from dcegm_jl_b200.solver import Solver
+    from oracle import oracle
+
+    rng = np.random.default_rng(3)
+    ps = []
+    for k in range(24):
+        d = dict(na=100, beta=float(rng.uniform(0.5, 1.0)), R=float(rng.uniform(1.0, 1.5)), sigma=float(rng.uniform(0.05, 0.5)))
+        if model == "borrow":
+            d["a_low"] = float(-rng.uniform(0, 3))
+        else:
+            d["nu"] = float(rng.uniform(0, 3)) if k % 3 else 0.0
+            d["gamma"] = 1.0 if k % 5 == 0 else float(rng.uniform(1.2, 3))
+        ps.append(Param(par=d))
+    mid = _abi.MODEL_MINIMAL_BORROW if model == "borrow" else _abi.MODEL_MINIMAL_BEQUEST
+    with Solver(0) as s:
+        g = s.solve(mid, ps)
+    r = oracle.solve(mid, ps, portable=True)
+    assert np.array_equal(g.lens, r.lens) and np.array_equal(g.status, r.status)
+    assert np.array_equal(g.lines.view(np.uint64), r.lines.view(np.uint64))
+    if model == "bequest":
+        import dcegm_jl_b200 as D
+
+        m, c, v = D.minimal_EGM_bequest(ps[1])
+        assert len(m) == ps[1].nT and len(m[0]) == 101 and len(m[-1]) == 100 and np.isfinite(v[0]).all()

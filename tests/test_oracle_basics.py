@@ -95,3 +95,35 @@ def test_linrange_matches_julia_range(oracle):
     for i in (1, 2, 249, 333, 498):
         assert g[i] == float(Fraction(50 * i, 499))
     assert g[0] == 0.0 and g[-1] == 50.0
+
+
+def test_minimal_variants_oracle():
+    """minimal_EGM_borrow / minimal_EGM_bequest (minimal_EGM.jl:49-159), unpinned by reference tests:
+    structural checks of the restatement."""
+    from dcegm_jl_b200 import Param, _abi
+    from oracle import oracle
+
+    p = Param(par=dict(na=40))
+    a = oracle.solve_minimal([p])
+    b = oracle.solve_minimal_borrow([p])            # a_low = 0: identical to minimal_EGM
+    assert np.array_equal(a.lines[0, :, 0, 0, 0], b.lines[0, :, 0, 0, 0])
+    pb = Param(par=dict(na=40, a_low=-2.0))
+    b2 = oracle.solve_minimal_borrow([pb])
+    x, y = b2.line(0, _abi.KIND_C, 0, 3)
+    assert x[0] == -2.0 and y[0] == 0.0 and len(x) == 41 and np.all(np.diff(x) > 0)
+    q = Param(par=dict(na=40, nu=0.0))
+    c = oracle.solve_minimal_bequest([q])
+    xc, yc = c.line(0, _abi.KIND_C, 0, q.nT - 1)
+    xv, yv = c.line(0, _abi.KIND_V, 0, q.nT - 1)
+    assert len(xc) == 40 and np.array_equal(xc, yc) and np.all(yv == 0.0)   # minimal_EGM.jl:102-104
+    xc, yc = c.line(0, _abi.KIND_C, 0, 0)
+    xv, yv = c.line(0, _abi.KIND_V, 0, 0)
+    assert np.array_equal(xc, xv) and xc[0] == 0.0 and yc[0] == 0.0 and np.all(np.diff(xc) > 0)
+    q2 = Param(par=dict(na=40, nu=2.0))
+    d = oracle.solve_minimal_bequest([q2])
+    # with a bequest motive the rich save for it in the penultimate period (minimal_EGM.jl:124-133); the
+    # luxury shifter bbar makes the poor consume more than without
+    c_no = c.line(0, _abi.KIND_C, 0, q.nT - 2)[1]
+    c_beq = d.line(0, _abi.KIND_C, 0, q.nT - 2)[1]
+    assert np.all(c_beq[-5:] < c_no[-5:]) and c_beq[1] > c_no[1]
+    assert d.status[0] == 0
