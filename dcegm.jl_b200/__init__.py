@@ -10,8 +10,9 @@ from . import _abi
 from .param import Param, DEFAULTS
 from .solution import Solution
 from .api import (Point, MLine, Envelope, FModel, GModel, runf, runfdemo, rung, minimal_EGM, bm, getx, gety, gets,
-                  getr, bound, DCEGMError, Simulation, sim, rs, rsg, minimal_EGM_borrow, minimal_EGM_bequest)
+                  getr, bound, DCEGMError, Simulation, sim, rs, rsg, minimal_EGM_borrow, minimal_EGM_bequest, v_analytic)
+from . import io
 
 __all__ = ["Param", "DEFAULTS", "Solution", "_abi", "Point", "MLine", "Envelope", "FModel", "GModel", "runf",
            "runfdemo", "rung", "minimal_EGM", "bm", "getx", "gety", "gets", "getr", "bound", "DCEGMError",
-           "Simulation", "sim", "rs", "rsg", "minimal_EGM_borrow", "minimal_EGM_bequest"]
+           "Simulation", "sim", "rs", "rsg", "minimal_EGM_borrow", "minimal_EGM_bequest", "v_analytic", "io"]

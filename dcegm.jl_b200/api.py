@@ -28,7 +28,7 @@ from .solver import Solver
 
 __all__ = ["Point", "MLine", "Envelope", "FModel", "GModel", "runf", "runfdemo", "rung", "minimal_EGM", "bm",
            "getx", "gety", "gets", "getr", "bound", "DCEGMError", "dc_EGM", "Simulation", "sim", "rs", "rsg",
-           "minimal_EGM_borrow", "minimal_EGM_bequest"]
+           "minimal_EGM_borrow", "minimal_EGM_bequest", "v_analytic"]
 
 
 class DCEGMError(RuntimeError):
@@ -299,3 +299,44 @@ def rs(par=None, **kw):  # simulate.jl:271-274
 def rsg(par=None, **kw):  # simulate.jl:279-282
     m, p = rung(par=par, **kw)
     return sim(m, p)
+
+
+def _u(x, working, p):  # utils.jl:40-46 (host-side, plotting helper only)
+    x = np.asarray(x, float)
+    with np.errstate(divide="ignore"):  # u(0) = -Inf, as in the reference
+        if p.gamma == 1.0:
+            return np.log(x) - p.alpha * working
+        return (1.0 / (1.0 - p.gamma)) * (x ** (1.0 - p.gamma) - 1.0) - p.alpha * working
+
+
+def v_analytic(m, p, id, it, iy=None):
+    """v_analytic(m,p,id,it[,iy]) (plotting.jl:3-42): the value function of choice `id` with the
+    credit-constrained region filled in analytically (u(c) + beta*vbound on a log-spaced grid of p.k points
+    below the second knot), joined to the stored envelope at its second point.  Returns an (n, 2) array of
+    (cash-on-hand, value).  Host-side post-processing of a fetched solution, like the reference's plotting code."""
+    from .io import scale_grid
+
+    g = isinstance(m, GModel)
+    vf = m.v[(id, iy, it)] if g else m.v[(id, it)]
+    c = m.c[(id, iy, it)] if g else m.c[(id, it)]
+    vx, vy = getx(vf), gety(vf)
+    if it == p.nT and not g:  # plotting.jl:6-9
+        cash = np.linspace(p.a_low, p.a_high, p.na)
+        if p.nu > 0:
+            vals = p.nu * _u_plain(cash + p.bbar, p)
+        else:
+            vals = _u(cash, id == 1, p) + p.beta * bound(vf)
+        return np.column_stack([cash, vals])
+    cons = scale_grid(p.cfloor_plot, gety(c)[1], p.k, 1)   # plotting.jl:10, 34
+    cash = scale_grid(p.a_low, vx[1], p.k, 1)              # plotting.jl:11, 35
+    if it == p.nT and p.nu > 0:
+        vals = p.nu * _u_plain(cons + p.bbar, p)
+    else:
+        mask = (cash < vx[1]) | (it == p.nT)               # vfun, dc_algo.jl:238-250
+        vals = np.where(mask, _u(cons, id == 1, p) + p.beta * bound(vf), np.interp(cash, vx, vy))
+    return np.vstack([np.column_stack([cash, vals]), np.column_stack([vx[1:], vy[1:]])])
+
+
+def _u_plain(x, p):  # utils.jl:23-29
+    x = np.asarray(x, float)
+    return np.log(x) if p.gamma == 1.0 else (1.0 / (1.0 - p.gamma)) * x ** (1.0 - p.gamma)
