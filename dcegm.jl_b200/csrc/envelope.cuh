@@ -293,6 +293,18 @@ __device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, do
             double best = -CUDART_INF, bestx = xk;
             bool knot = false;
             for (int s = 0; s < nseg; s++) {
+                // sections entirely to one side of xk need no search: left of xk they contribute all their
+                // own points to the rank (the boundary shared with the previous section is not theirs),
+                // right of xk nothing; neither contains xk
+                {
+                    const int e0 = S.segb()[s], e1 = S.segb()[s + 1];
+                    const double xa = X[e0], xb = X[e1];
+                    if (xk > (xa > xb ? xa : xb)) {
+                        rank += e1 - e0 + (s == 0 ? 1 : 0);
+                        continue;
+                    }
+                    if (xk < (xa < xb ? xa : xb)) continue;
+                }
                 SegView v = seg_view(S, X, V, s);
                 // #knots < xk
                 int lo = 0, len = v.len;
