@@ -40,6 +40,7 @@ MODEL_MINIMAL_BORROW, MODEL_MINIMAL_BEQUEST = 4, 5
 KIND_C, KIND_V, KIND_CDIRTY, KIND_VDIRTY = 0, 1, 2, 3
 KEEP_DIRTY = 1 << 0
 SUMMARY_ONLY = 1 << 1
+FORCE_FINE_GRID = 1 << 2
 SUMMARY_NPROBE = 8
 SIM_PANEL = 1 << 0
 SIM_NMOM = 8

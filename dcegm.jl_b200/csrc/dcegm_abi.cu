@@ -15,6 +15,9 @@
 
 namespace dcegm {
 cudaError_t launch_solve_f(const DeviceBatch& B, int first, int count, cudaStream_t stream);
+cudaError_t launch_solve_f_big(const DeviceBatch& B, int first, int count, unsigned char* scratch, cudaStream_t stream,
+                               int* nlaunch);
+size_t solver_f_big_scratch_bytes(int cap, int isec_cap);
 cudaError_t launch_solve_g(const DeviceBatch& B, int first, int count, cudaStream_t stream);
 cudaError_t launch_solve_minimal(const DeviceBatch& B, int first, int count, cudaStream_t stream);
 cudaError_t launch_pack_lines(const DeviceBatch& B, int first, int count, const long long* d_offsets, double2* d_dst,
@@ -42,6 +45,9 @@ struct dcegm_ctx {
     long long* pin_off = nullptr;
     size_t pin_slots = 0;
     DevBuf pack_xy2;
+    DevBuf big_scratch;   // fine-grid retirement solver (solver_f_big.cu): per-model working lines + envelope scratch
+    bool big = false;     // the uploaded batch runs on the fine-grid solver
+    int launches_last = 0;
     DevBuf simm, yvec, mom, rhist, sstat, pan_d, pan_i, pan_ret, sh_w, sh_d, sh_r, sh_w0, sh_y0;
     bool simulated = false;
     int sim_nsims = 0;      // panel geometry of the last simulation (0 = no panel kept)
@@ -97,11 +103,15 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
     dcegm_layout lay;
     make_layout(model, nmodels, na, ny, nT, (flags & DCEGM_KEEP_DIRTY) ? 1 : 0, (flags & DCEGM_SUMMARY_ONLY) ? 0 : 1, &lay);
     if (model == DCEGM_MODEL_F && ny > kMaxNy) return fail(h, DCEGM_E_INVALID, "ny > 64 is not supported by the retirement-model solver");
-    if (lay.cap >= 2 * kSearchTop) return fail(h, DCEGM_E_INVALID, "na too large for the shared-memory resident solver");
     size_t smem = model == DCEGM_MODEL_F   ? solver_f_smem_bytes(lay.cap, lay.isec_cap)
                   : model == DCEGM_MODEL_G ? solver_g_smem_bytes(lay.cap, lay.isec_cap, na, ny)
                                            : (size_t)(6 * (na + 1) * 8 + 1024);
-    if ((long long)smem > (long long)h->max_smem_optin) {
+    // retirement model on a grid too fine for one SM's shared memory: the fine-grid solver (lines in global memory)
+    h->big = model == DCEGM_MODEL_F &&
+             ((flags & DCEGM_FORCE_FINE_GRID) || lay.cap >= 2 * kSearchTop || (long long)smem > (long long)h->max_smem_optin);
+    if (h->big && lay.cap >= 65536) return fail(h, DCEGM_E_INVALID, "na too large: polylines are indexed with 16 bits (na < ~52000)");
+    if (!h->big && lay.cap >= 2 * kSearchTop) return fail(h, DCEGM_E_INVALID, "na too large for the shared-memory resident solver");
+    if (!h->big && (long long)smem > (long long)h->max_smem_optin) {
         char msg[256];
         snprintf(msg, sizeof msg,
                  "na=%d needs %zu B of shared memory per CTA (device limit %d B): grid too fine for the "
@@ -128,6 +138,8 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
         if ((rc = ensure(h, h->dirty, sizeof(double2) * nslots * na, true))) return rc;
     if ((rc = ensure(h, h->status, sizeof(int32_t) * nmodels, true))) return rc;
     if ((rc = ensure(h, h->summaries, sizeof(dcegm_summary) * nmodels, true))) return rc;
+    if (h->big)
+        if ((rc = ensure(h, h->big_scratch, solver_f_big_scratch_bytes(lay.cap, lay.isec_cap) * nmodels, false))) return rc;
 
     CK(cudaEventRecord(h->ev[0], h->stream));
     CK(cudaMemcpyAsync(h->models.p, h->tab.models.data(), sizeof(DevModel) * nmodels, cudaMemcpyHostToDevice, h->stream));
@@ -163,7 +175,9 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
     return DCEGM_OK;
 }
 
-cudaError_t launch_range(const DeviceBatch& B, int first, int count, cudaStream_t stream) {
+cudaError_t launch_range(dcegm_ctx* h, const DeviceBatch& B, int first, int count, cudaStream_t stream) {
+    h->launches_last = 1;
+    if (h->big) return launch_solve_f_big(B, first, count, (unsigned char*)h->big_scratch.p, stream, &h->launches_last);
     if (B.lay.model == DCEGM_MODEL_F) return launch_solve_f(B, first, count, stream);
     if (B.lay.model == DCEGM_MODEL_G) return launch_solve_g(B, first, count, stream);
     return launch_solve_minimal(B, first, count, stream);
@@ -182,12 +196,12 @@ int run(dcegm_ctx* h) {
     CK(cudaMemsetAsync(B.lens, 0, sizeof(int32_t) * nstates * 4, h->stream));
     CK(cudaMemsetAsync(B.meta, 0, sizeof(dcegm_env_meta) * nstates, h->stream));
     CK(cudaMemsetAsync(B.vbound, 0, sizeof(double) * nstates * 2, h->stream));
-    cudaError_t e = launch_range(B, 0, B.lay.nmodels, h->stream);
+    cudaError_t e = launch_range(h, B, 0, B.lay.nmodels, h->stream);
     if (e != cudaSuccess) return cuda_fail(h, e, "kernel launch");
     CK(cudaEventRecord(h->ev[3], h->stream));
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaEventElapsedTime(&h->timing.kernel_ms, h->ev[2], h->ev[3]));
-    h->timing.n_launches = 1;
+    h->timing.n_launches = h->launches_last;
     h->solved = true;
     return DCEGM_OK;
 }
@@ -247,7 +261,7 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     CK(cudaMemsetAsync(B.vbound, 0, sizeof(double) * nstates * 2, h->stream));
     for (int c = 0; c < nchunks; c++) {
         const int c0 = c * chunk, cnt = (nmodels - c0 < chunk) ? nmodels - c0 : chunk;
-        cudaError_t e = launch_range(B, c0, cnt, h->stream);
+        cudaError_t e = launch_range(h, B, c0, cnt, h->stream);
         if (e != cudaSuccess) return cuda_fail(h, e, "kernel launch");
         CK(cudaEventRecord(h->ev_pool[3 * c], h->stream));
     }
@@ -290,7 +304,7 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     CK(cudaStreamSynchronize(h->s_pack));
     CK(cudaStreamSynchronize(h->s_copy));
     CK(cudaEventElapsedTime(&h->timing.kernel_ms, h->ev[2], h->ev[3]));
-    h->timing.n_launches = 2 * nchunks;
+    h->timing.n_launches = (h->launches_last + 1) * nchunks;
     h->solved = true;
     *npoints = base;
     return err;
@@ -389,7 +403,7 @@ int dcegm_destroy(dcegm_handle h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     DevBuf* bufs[] = {&h->models, &h->grids, &h->off, &h->wgt, &h->lines, &h->lens, &h->vbound, &h->meta, &h->isects,
-                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2,
+                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2, &h->big_scratch,
                       &h->simm, &h->yvec, &h->mom, &h->rhist, &h->sstat, &h->pan_d, &h->pan_i, &h->pan_ret,
                       &h->sh_w, &h->sh_d, &h->sh_r, &h->sh_w0, &h->sh_y0};
     for (DevBuf* b : bufs)

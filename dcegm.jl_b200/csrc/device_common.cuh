@@ -91,6 +91,21 @@ __device__ __forceinline__ size_t state_slot(const dcegm_layout& l, int m, int i
 // memory made the compiler fall back to generic LD/ST).
 extern __shared__ __align__(16) unsigned char dc_smem[];
 
+// Where the scratch of a solver lives.  The persistent per-model kernels keep everything in shared
+// memory (MemShared: offsets from dc_smem, every access an LDS/STS); the fine-grid solver
+// (solver_f_big.cu: lines too long for one SM's shared memory) runs the same code on a per-model
+// region of global memory (MemGlobal).  kTop = largest step of the fixed-trip knot search: lines hold
+// fewer than 2*kTop points.
+struct MemShared {
+    static constexpr int kTop = 1024;
+    __device__ __forceinline__ unsigned char* mem() const { return dc_smem; }
+};
+struct MemGlobal {
+    static constexpr int kTop = 32768;
+    unsigned char* g;
+    __device__ __forceinline__ unsigned char* mem() const { return g; }
+};
+
 // Phase clocks (profiling builds only, -DDCEGM_PHASE_CLOCKS; see tools/phase_clocks.py): block-wide
 // barrier, then thread 0 adds the cycles since the previous mark to slot i.  Compiles to nothing in
 // the product build.
@@ -118,19 +133,21 @@ __device__ __forceinline__ long long* dc_clk() {
 // ---------------------------------------------------------------------------------------------
 // number of knots <= q (searchsortedlast): fixed-trip, branch-free power-of-two descent.  kSearchTop
 // is the largest step; lines hold fewer than 2*kSearchTop points (checked at upload).
-constexpr int kSearchTop = 1024;
+constexpr int kSearchTop = MemShared::kTop;
+template <int Top = kSearchTop>
 __device__ __forceinline__ int count_le(const double* __restrict__ x, int n, double q) {
     int lo = 0;
 #pragma unroll
-    for (int step = kSearchTop; step >= 1; step >>= 1) {
+    for (int step = Top; step >= 1; step >>= 1) {
         const int idx = lo + step - 1;
         const bool ok = idx < n && x[idx < n ? idx : 0] <= q;
         lo = ok ? lo + step : lo;
     }
     return lo;
 }
+template <int Top = kSearchTop>
 __device__ __forceinline__ int left_knot(const double* __restrict__ x, int n, double q) {
-    int i = count_le(x, n, q) - 1;
+    int i = count_le<Top>(x, n, q) - 1;
     i = i < 0 ? 0 : i;
     i = i > n - 2 ? n - 2 : i;
     return i;
@@ -149,8 +166,9 @@ __device__ __forceinline__ double interp_at(const double* __restrict__ x, const 
     double f = (q - x[i]) / (x[i + 1] - x[i]);
     return (1.0 - f) * y[i] + f * y[i + 1];
 }
+template <int Top = kSearchTop>
 __device__ __forceinline__ double interp_y(const double* __restrict__ x, const double* __restrict__ y, int n, double q) {
-    return interp_at(x, y, n, left_knot(x, n, q), q);
+    return interp_at(x, y, n, left_knot<Top>(x, n, q), q);
 }
 // ---------------------------------------------------------------------------------------------
 // Bucket index over the knots of one line: T[b] = number of knots whose bucket is < b, for the
@@ -194,21 +212,28 @@ __device__ __forceinline__ bool knot_index_covers(const KnotIndex& K, double qmi
 // one knot's share of the table build (x strictly increasing, n >= 2): the buckets between the
 // previous knot's and this knot's get this knot's index.  Block-level: every k in [0, n) once; the
 // caller syncs afterwards.
-__device__ __forceinline__ void knot_index_build_step(const KnotIndex& K, const double* __restrict__ x, int n, int nb, int k) {
-    unsigned short* T = reinterpret_cast<unsigned short*>(dc_smem + K.tab);
+__device__ __forceinline__ void knot_index_build_step_at(unsigned short* T, const KnotIndex& K, const double* __restrict__ x,
+                                                          int n, int nb, int k) {
     const int bk = knot_bucket(K, x[k]);
     const int bp = k == 0 ? -1 : knot_bucket(K, x[k - 1]);
     for (int b = bp + 1; b <= bk; b++) T[b] = (unsigned short)k;
     if (k == n - 1)
         for (int b = bk + 1; b <= nb; b++) T[b] = (unsigned short)n;
 }
+__device__ __forceinline__ void knot_index_build_step(const KnotIndex& K, const double* __restrict__ x, int n, int nb, int k) {
+    knot_index_build_step_at(reinterpret_cast<unsigned short*>(dc_smem + K.tab), K, x, n, nb, k);
+}
 // number of knots <= q: all knots in lower buckets are <= q, so the scan starts at the first knot of
 // q's own bucket.  (A variant with three independent probes instead of the dependent scan measured
 // 4 % slower on the C3 batch: most buckets hold one knot.)
-__device__ __forceinline__ int count_le_indexed(const KnotIndex& K, const double* __restrict__ x, int n, double q) {
-    int i = reinterpret_cast<const unsigned short*>(dc_smem + K.tab)[knot_bucket(K, q)];
+__device__ __forceinline__ int count_le_indexed_at(const unsigned short* __restrict__ T, const KnotIndex& K,
+                                                    const double* __restrict__ x, int n, double q) {
+    int i = T[knot_bucket(K, q)];
     while (i < n && x[i] <= q) i++;
     return i;
+}
+__device__ __forceinline__ int count_le_indexed(const KnotIndex& K, const double* __restrict__ x, int n, double q) {
+    return count_le_indexed_at(reinterpret_cast<const unsigned short*>(dc_smem + K.tab), K, x, n, q);
 }
 
 // whole-Point interpolation on a 2-point line (dc_algo.jl:446-478)

@@ -22,8 +22,9 @@ namespace dcegm {
 // All scratch of the envelope lives in the kernel's dynamic shared memory (dc_smem, declared in
 // device_common.cuh) and is addressed as integer offsets from that one symbol.
 
-struct EnvScratch {
-    int off;  // byte offset of the region inside dc_smem
+template <class Mem>
+struct EnvScratchT : Mem {
+    int off;  // byte offset of the region inside the scratch memory (dc_smem, or the model's global region)
     int cap, isec_cap;
     // region layout: 5 double[cap] | 12 double[isec_cap] | redd[kWarps] | scan int[cap] | segb int[kSegCap+1]
     //                | 2 int[isec_cap] | red int[kWarps+1] | cnt int[8] | 5 u16[cap] | 4 u8[cap] | segrise u8[kSegCap]
@@ -43,7 +44,7 @@ struct EnvScratch {
     __host__ __device__ int o_ok(int j) const { return o_segrise() + align16(kSegCap) + j * align16(isec_cap); }
     __host__ __device__ int bytes() const { return o_ok(2) - off; }
 #define DC_ARR(T, name, expr) \
-    __device__ __forceinline__ T* name() const { return reinterpret_cast<T*>(dc_smem + (expr)); }
+    __device__ __forceinline__ T* name() const { return reinterpret_cast<T*>(this->mem() + (expr)); }
     // extended dirty worker line (EGM order): x, value, policy.  The EGM step writes the na points at
     // offset `koff` = max(na/10-1,0); bend-back points are prepended in front.
     DC_ARR(double, Dx, o_d(0)) DC_ARR(double, Dv, o_d(1)) DC_ARR(double, Dc, o_d(2))
@@ -61,13 +62,16 @@ struct EnvScratch {
     DC_ARR(unsigned char, cntI, o_u8(3)) DC_ARR(unsigned char, segrise, o_segrise())
     DC_ARR(unsigned char, insLok, o_ok(0)) DC_ARR(unsigned char, insRok, o_ok(1))
 };
+using EnvScratch = EnvScratchT<MemShared>;
+using EnvScratchG = EnvScratchT<MemGlobal>;
 
 struct SegView {
     const double* X;
     const double* Y;
     int base, st, len;
 };
-__device__ __forceinline__ SegView seg_view(const EnvScratch& S, const double* X, const double* Y, int s) {
+template <class ES>
+__device__ __forceinline__ SegView seg_view(const ES& S, const double* X, const double* Y, int s) {
     SegView v;
     int b0 = S.segb()[s], b1 = S.segb()[s + 1];
     bool rise = S.segrise()[s];
@@ -115,7 +119,8 @@ __device__ __forceinline__ double seg_interp_y(const SegView& v, double q) {
 // One change of winner between union-grid cells j-1 and j (envelope.jl:174-243), resolved by one
 // warp: all lanes follow the same control flow, the scan over all sections is split across lanes.
 // Returns the number of intersections found; points go to px/py (at most kSwitchMaxIsect are stored).
-__device__ inline int resolve_switch(const EnvScratch& S, const double* X, const double* V, int nseg, int k0, int k1,
+template <class ES>
+__device__ inline int resolve_switch(const ES& S, const double* X, const double* V, int nseg, int k0, int k1,
                                      double xl, double xr, double* px, double* py, unsigned* status) {
     const int lane = threadIdx.x & 31;
     int ln1 = k0, ln2 = k1;
@@ -204,7 +209,8 @@ __device__ inline int resolve_switch(const EnvScratch& S, const double* X, const
 // S.Dx()/S.Dv()/S.Dc()[koff .. koff+na).  On exit (Vx,Vy,*nV) holds m.v[1,it].env and (Cx,Cy,*nC)
 // m.c[1,it].env, both with the prepended credit-constraint point; meta / isects / removed are
 // written to global memory.  All threads of the block must call this.
-__device__ inline void worker_envelope(const EnvScratch& S, int koff, int na, double a0, double ev0, const DevModel& p,
+template <class ES>
+__device__ inline void worker_envelope(const ES& S, int koff, int na, double a0, double ev0, const DevModel& p,
                                        double* Vx, double* Vy, int* nV, double* Cx, double* Cy, int* nC,
                                        dcegm_env_meta* meta_out, double2* isects_out, uint32_t* removed_out,
                                        int rem_words) {

@@ -45,18 +45,22 @@ class Solver:
             raise _lib.DcegmError(rc, self.lib.dcegm_last_error(self.h).decode())
 
     # ---- solving -------------------------------------------------------------------------
-    def solve(self, model, params, keep_dirty=False, summary_only=False, fetch=True):
+    def solve(self, model, params, keep_dirty=False, summary_only=False, fetch=True, fine_grid=False):
+        """fine_grid: force the fine-grid retirement solver (automatic when the lines of one model do not fit
+        into shared memory, i.e. na > ~1000)."""
         arr = params if isinstance(params, C.Array) else params_array(params)
-        flags = (_abi.KEEP_DIRTY if keep_dirty else 0) | (_abi.SUMMARY_ONLY if summary_only else 0)
+        flags = ((_abi.KEEP_DIRTY if keep_dirty else 0) | (_abi.SUMMARY_ONLY if summary_only else 0)
+                 | (_abi.FORCE_FINE_GRID if fine_grid else 0))
         fn = {_abi.MODEL_F: self.lib.dcegm_solve_f, _abi.MODEL_G: self.lib.dcegm_solve_g,
               _abi.MODEL_MINIMAL: self.lib.dcegm_solve_minimal, _abi.MODEL_MINIMAL_BORROW: self.lib.dcegm_solve_minimal_borrow,
               _abi.MODEL_MINIMAL_BEQUEST: self.lib.dcegm_solve_minimal_bequest}[model]
         self._ck(fn(self.h, arr, len(arr), flags))
         return self.fetch() if fetch and not summary_only else None
 
-    def upload(self, model, params, keep_dirty=False, summary_only=False):
+    def upload(self, model, params, keep_dirty=False, summary_only=False, fine_grid=False):
         arr = params if isinstance(params, C.Array) else params_array(params)
-        flags = (_abi.KEEP_DIRTY if keep_dirty else 0) | (_abi.SUMMARY_ONLY if summary_only else 0)
+        flags = ((_abi.KEEP_DIRTY if keep_dirty else 0) | (_abi.SUMMARY_ONLY if summary_only else 0)
+                 | (_abi.FORCE_FINE_GRID if fine_grid else 0))
         fn = {_abi.MODEL_F: self.lib.dcegm_upload_f, _abi.MODEL_G: self.lib.dcegm_upload_g,
               _abi.MODEL_MINIMAL: self.lib.dcegm_upload_minimal}[model]
         self._ck(fn(self.h, arr, len(arr), flags))

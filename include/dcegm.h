@@ -118,6 +118,10 @@ void dcegm_param_defaults(dcegm_param* p);
 /* ---- solve flags ------------------------------------------------------------ */
 #define DCEGM_KEEP_DIRTY   (1u << 0)  /* runfdemo: also keep the pre-envelope lines */
 #define DCEGM_SUMMARY_ONLY (1u << 1)  /* do not materialise lines in HBM, only summaries */
+#define DCEGM_FORCE_FINE_GRID (1u << 2)  /* retirement model: run the fine-grid solver (working lines in global
+                                            memory, two launches per period) even when the lines of one model fit into
+                                            shared memory.  It is selected automatically for grids that do not
+                                            (na > ~1000); results are bit-identical either way. */
 
 /* ---- geometry of the resident solution ------------------------------------- *
  * lines  : double [nmodels][nT][nstate][2 id][2 kind(c,v)][cap][2 (x,y)]
