@@ -109,6 +109,7 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
     // retirement model on a grid too fine for one SM's shared memory: the fine-grid solver (lines in global memory)
     h->big = model == DCEGM_MODEL_F &&
              ((flags & DCEGM_FORCE_FINE_GRID) || lay.cap >= 2 * kSearchTop || (long long)smem > (long long)h->max_smem_optin);
+    if (h->big) lay.seg_cap = lay.cap;
     if (h->big && lay.cap >= 65536) return fail(h, DCEGM_E_INVALID, "na too large: polylines are indexed with 16 bits (na < ~52000)");
     if (!h->big && lay.cap >= 2 * kSearchTop) return fail(h, DCEGM_E_INVALID, "na too large for the shared-memory resident solver");
     if (!h->big && (long long)smem > (long long)h->max_smem_optin) {

@@ -23,7 +23,7 @@ constexpr int kCtasPerSm = 2;
 #endif   // threads per CTA of the persistent solver kernels
 constexpr int kWarps = kThreads / 32;
 constexpr int kMaxNy = 64;     // income nodes staged in shared memory by solve_f_kernel
-constexpr int kSegCap = 192;    // max sections of one splitLine
+constexpr int kSegCap = 192;    // max sections of one splitLine (shared-memory resident solvers)
 constexpr int kSwitchMaxIsect = 8;  // max intersections produced by one change of winner
 
 // geometry of the resident solution; must match oracle_layout() (tests compare slot by slot)
@@ -98,10 +98,12 @@ extern __shared__ __align__(16) unsigned char dc_smem[];
 // fewer than 2*kTop points.
 struct MemShared {
     static constexpr int kTop = 1024;
+    static constexpr int kSegCapFixed = 192;  // max sections of one splitLine (more -> DCEGM_ST_SEG_OVERFLOW)
     __device__ __forceinline__ unsigned char* mem() const { return dc_smem; }
 };
 struct MemGlobal {
     static constexpr int kTop = 32768;
+    static constexpr int kSegCapFixed = 0;    // room for one section per point: splitLine cannot overflow
     unsigned char* g;
     __device__ __forceinline__ unsigned char* mem() const { return g; }
 };

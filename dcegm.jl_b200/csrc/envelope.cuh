@@ -30,18 +30,19 @@ struct EnvScratchT : Mem {
     //                | 2 int[isec_cap] | red int[kWarps+1] | cnt int[8] | 5 u16[cap] | 4 u8[cap] | segrise u8[kSegCap]
     //                | 2 u8[isec_cap]
     __host__ __device__ static int align16(int b) { return (b + 15) / 16 * 16; }
+    __host__ __device__ int segcap() const { return Mem::kSegCapFixed > 0 ? Mem::kSegCapFixed : cap; }
     __host__ __device__ int o_d(int j) const { return off + j * align16(cap * 8); }
     __host__ __device__ int o_i(int j) const { return o_d(5) + j * align16(isec_cap * 8); }
     __host__ __device__ int o_redd() const { return o_i(12); }
     __host__ __device__ int o_scan() const { return o_redd() + align16(kWarps * 8); }
     __host__ __device__ int o_segb() const { return o_scan() + align16(cap * 4); }
-    __host__ __device__ int o_key(int j) const { return o_segb() + align16((kSegCap + 1) * 4) + j * align16(isec_cap * 4); }
+    __host__ __device__ int o_key(int j) const { return o_segb() + align16(((Mem::kSegCapFixed > 0 ? Mem::kSegCapFixed : cap) + 1) * 4) + j * align16(isec_cap * 4); }
     __host__ __device__ int o_red() const { return o_key(2); }
     __host__ __device__ int o_cnt() const { return o_red() + align16((kWarps + 1) * 4); }
     __host__ __device__ int o_u16(int j) const { return o_cnt() + 32 + j * align16(cap * 2); }
     __host__ __device__ int o_u8(int j) const { return o_u16(5) + j * align16(cap); }
     __host__ __device__ int o_segrise() const { return o_u8(4); }
-    __host__ __device__ int o_ok(int j) const { return o_segrise() + align16(kSegCap) + j * align16(isec_cap); }
+    __host__ __device__ int o_ok(int j) const { return o_segrise() + align16(Mem::kSegCapFixed > 0 ? Mem::kSegCapFixed : cap) + j * align16(isec_cap); }
     __host__ __device__ int bytes() const { return o_ok(2) - off; }
 #define DC_ARR(T, name, expr) \
     __device__ __forceinline__ T* name() const { return reinterpret_cast<T*>(this->mem() + (expr)); }
@@ -266,7 +267,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             status |= DCEGM_ST_ALL_FALLING;
             nseg = 0;
         }
-    } else if (nseg > kSegCap) {
+    } else if (nseg > (ES::kSegCapFixed > 0 ? ES::kSegCapFixed : S.cap)) {
         status |= DCEGM_ST_SEG_OVERFLOW;
         plain = true;
     }
@@ -293,6 +294,23 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
 
         DC_CLK(5);
         // ---- every point: sorted position, winning section, top Point (envelope.jl:154-164) ----
+        // fine-grid solver: the extent and the size of the first kSegTile sections are staged in shared memory, so
+        // that the test below costs two shared loads instead of four dependent global ones
+        constexpr bool kStage = ES::kSegCapFixed == 0;
+        constexpr int kSegTile = kStage ? 1536 : 1;
+        __shared__ double t_lo[kSegTile], t_hi[kSegTile];
+        __shared__ int t_own[kSegTile];
+        const int ntile = kStage ? (nseg < kSegTile ? nseg : kSegTile) : 0;
+        if (kStage) {
+            for (int s = tid; s < ntile; s += kThreads) {
+                const int e0 = S.segb()[s], e1 = S.segb()[s + 1];
+                const double xa = X[e0], xb = X[e1];
+                t_lo[s] = xa < xb ? xa : xb;
+                t_hi[s] = xa > xb ? xa : xb;
+                t_own[s] = e1 - e0 + (s == 0 ? 1 : 0);
+            }
+            __syncthreads();
+        }
         for (int k = tid; k < n; k += kThreads) {
             const double xk = X[k];
             int rank = 0, ties = 0, w = -1;
@@ -302,7 +320,13 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 // sections entirely to one side of xk need no search: left of xk they contribute all their
                 // own points to the rank (the boundary shared with the previous section is not theirs),
                 // right of xk nothing; neither contains xk
-                {
+                if (kStage && s < ntile) {
+                    if (xk > t_hi[s]) {
+                        rank += t_own[s];
+                        continue;
+                    }
+                    if (xk < t_lo[s]) continue;
+                } else {
                     const int e0 = S.segb()[s], e1 = S.segb()[s + 1];
                     const double xa = X[e0], xb = X[e1];
                     if (xk > (xa > xb ? xa : xb)) {
@@ -611,7 +635,78 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
     int bad = 0;
     for (int k = tid; k + 1 < lenC; k += kThreads) bad |= Cx[k + 1] < Cx[k];
     bad = block_sum(bad, S.red());
-    if (bad) {
+    if (bad && ES::kSegCapFixed == 0) {
+        // long lines (fine-grid solver): stable merge sort of the natural ascending runs, pairwise and
+        // bottom-up; every element finds its place in the merged pair with one binary search in the sibling
+        // run (left-run elements go before equal right-run elements).  Ping-pong with the free D arrays;
+        // run boundaries in segb (room for cap + 1 entries in this variant), scan as temporary.
+        for (int k = tid; k < lenC; k += kThreads) S.scan()[k] = (k == 0) || (Cx[k] < Cx[k - 1]);
+        __syncthreads();
+        for (int k = tid; k < lenC; k += kThreads) S.fuq()[k] = (unsigned char)S.scan()[k];
+        __syncthreads();
+        int nr = block_scan_excl(S.scan(), lenC, S.red());
+        int* rb = S.segb();
+        for (int k = tid; k < lenC; k += kThreads)
+            if (S.fuq()[k]) rb[S.scan()[k]] = k;
+        if (tid == 0) rb[nr] = lenC;
+        __syncthreads();
+        double *sx = Cx, *sy = Cy, *dx = S.Dx(), *dy = S.Dv();
+        while (nr > 1) {
+            for (int k = tid; k < lenC; k += kThreads) {
+                int lo = 0, len = nr;  // run containing k: last boundary <= k
+                while (len > 0) {
+                    const int half = len >> 1;
+                    const bool le = rb[lo + half] <= k;
+                    lo = le ? lo + half + 1 : lo;
+                    len = le ? len - half - 1 : half;
+                }
+                const int j = lo - 1;
+                const double xk = sx[k];
+                int out = k;
+                if ((j & 1) == 0) {
+                    if (j + 1 < nr) {  // count of x < xk in the right sibling
+                        const int b0 = rb[j + 1];
+                        int l2 = 0, n2 = rb[j + 2] - b0;
+                        while (n2 > 0) {
+                            const int half = n2 >> 1;
+                            const bool lt = sx[b0 + l2 + half] < xk;
+                            l2 = lt ? l2 + half + 1 : l2;
+                            n2 = lt ? n2 - half - 1 : half;
+                        }
+                        out = k + l2;
+                    }
+                } else {  // count of x <= xk in the left sibling
+                    const int b0 = rb[j - 1];
+                    int l2 = 0, n2 = rb[j] - b0;
+                    while (n2 > 0) {
+                        const int half = n2 >> 1;
+                        const bool le = sx[b0 + l2 + half] <= xk;
+                        l2 = le ? l2 + half + 1 : l2;
+                        n2 = le ? n2 - half - 1 : half;
+                    }
+                    out = b0 + l2 + (k - rb[j]);
+                }
+                dx[out] = xk;
+                dy[out] = sy[k];
+            }
+            const int nr2 = (nr + 1) >> 1;
+            for (int i = tid; i < nr2; i += kThreads) S.scan()[i] = rb[2 * i];
+            __syncthreads();
+            for (int i = tid; i < nr2; i += kThreads) rb[i] = S.scan()[i];
+            if (tid == 0) rb[nr2] = lenC;
+            __syncthreads();
+            nr = nr2;
+            double* t = sx; sx = dx; dx = t;
+            t = sy; sy = dy; dy = t;
+        }
+        if (sx != Cx) {
+            for (int k = tid; k < lenC; k += kThreads) {
+                Cx[k] = sx[k];
+                Cy[k] = sy[k];
+            }
+            __syncthreads();
+        }
+    } else if (bad) {
         for (int k = tid; k < lenC; k += kThreads) {
             const double xk = Cx[k];
             int r = 0;

@@ -306,10 +306,37 @@ __global__ void __launch_bounds__(kThreads) big_egm_kernel(DeviceBatch B, unsign
     }
 }
 
+#ifdef DCEGM_PHASE_CLOCKS
+__device__ unsigned long long dc_phase_total_big[kPhaseSlots];
+extern "C" int dcegm_debug_phase_clocks_big(unsigned long long* out, int reset) {
+    if (out && cudaMemcpyFromSymbol(out, dc_phase_total_big, sizeof(unsigned long long) * kPhaseSlots) != cudaSuccess) return -2;
+    if (reset) {
+        unsigned long long z[kPhaseSlots] = {0};
+        if (cudaMemcpyToSymbol(dc_phase_total_big, z, sizeof z) != cudaSuccess) return -2;
+    }
+    return 0;
+}
+#define BIG_CLK_BEGIN()                                           \
+    if (threadIdx.x == 0) {                                       \
+        for (int i = 0; i < kPhaseSlots; i++) dc_clk()[i] = 0;    \
+        dc_clk()[kPhaseSlots] = clock64();                        \
+    }
+#define BIG_CLK_END()                                             \
+    do {                                                          \
+        DC_CLK(14);                                               \
+        if (threadIdx.x == 0)                                     \
+            for (int i = 0; i < kPhaseSlots; i++) atomicAdd(&dc_phase_total_big[i], (unsigned long long)dc_clk()[i]); \
+    } while (0)
+#else
+#define BIG_CLK_BEGIN()
+#define BIG_CLK_END() do { } while (0)
+#endif
+
 // ---- envelope, tail and store of period t: one CTA per model ------------------------------------------------
 __global__ void __launch_bounds__(kThreads) big_env_kernel(DeviceBatch B, unsigned char* scratch, size_t stride, int t) {
     const int m = B.first + blockIdx.x;
     const int tid = threadIdx.x;
+    BIG_CLK_BEGIN();
     __shared__ DevModel s_p;
     __shared__ int s_n[2];
     __shared__ int s_status;
@@ -320,7 +347,7 @@ __global__ void __launch_bounds__(kThreads) big_env_kernel(DeviceBatch B, unsign
     if (tid == 0) s_status = st->status;
     __syncthreads();
     const DevModel& p = s_p;
-    const int na = p.na, nT = p.nT;
+    const int na = p.na;
     EnvScratchG S = P.env;
     S.g = g;
     const int w = t & 1;
@@ -350,6 +377,7 @@ __global__ void __launch_bounds__(kThreads) big_env_kernel(DeviceBatch B, unsign
     C.n_wv = s_n[0];
     C.n_wc = s_n[1];
     C.vb_w = ev0w;
+    DC_CLK(12);
 
     // retiree: credit-constraint point and checks (dc_algo.jl:90-101)
     if (tid == 0) {
@@ -393,12 +421,15 @@ __global__ void __launch_bounds__(kThreads) big_env_kernel(DeviceBatch B, unsign
         st->vb_r[w] = C.vb_r;
         st->status = status;
     }
+    DC_CLK(13);
     if (t > 0) {
         big_build_index(P, g, st, C, status);
+        BIG_CLK_END();
         return;
     }
 
     big_summary(B, m, p, C, st, status);
+    BIG_CLK_END();
 }
 
 // Launches the whole backward recursion for models [first, first+count).  `scratch` holds `count` regions of

@@ -99,6 +99,20 @@ def test_c4_geometry_short_horizon(solver, oracle):
     assert g.meta[..., 1].sum() > 0  # the envelope found kinks
 
 
+def test_more_sections_than_the_resident_solver_holds(solver, oracle):
+    """at na = 20000 splitLine returns hundreds of sections (223 in period 5 here; the shared-memory solver stops
+    at 192): the fine-grid solver has room for one section per point"""
+    from dcegm_jl_b200 import Param, _abi
+
+    d = dict(na=20000, ny=32, nT=12, retage=51, beta=0.95, R=1.05, sigma=0.45)
+    d["lambda"] = 5.45e-5
+    ps = [Param(par=d)]
+    g = solver.solve(_abi.MODEL_F, ps)
+    r = oracle.solve_f(ps, portable=True)
+    assert r.meta[..., 0].max() > 192 and r.status[0] == 0
+    assert_bitwise(g, r)
+
+
 def test_packed_transfer_of_fine_grid_solution(solver):
     """dcegm_solve_f_packed routes through the same solver selection"""
     from dcegm_jl_b200 import _abi

@@ -78,4 +78,6 @@ with Solver(0) as s:
         dt = time.perf_counter() - t0
         st = s.status()
         print(json.dumps({"config": f"C4 fine grid: FModel x{n} (na=20000, nT=50, ny=32)", "kernel_ms": s.timing().kernel_ms,
-                          "models_per_s": n / dt, "flagged": int((st != 0).sum())}))
+                          "models_per_s": n / dt, "flagged": int((st != 0).sum()),
+                          "status_bits": {int(b): int(((st >> b) & 1).sum()) for b in range(12) if ((st >> b) & 1).any()},
+                          "launches": s.timing().n_launches}))
