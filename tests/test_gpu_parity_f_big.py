@@ -113,6 +113,42 @@ def test_more_sections_than_the_resident_solver_holds(solver, oracle):
     assert_bitwise(g, r)
 
 
+def test_c4_full_size_model(solver, oracle):
+    """one model of BASELINE configs[3] at its full size (na = 20000, ny = 32, nT = 50, retage = 51; the first
+    (lambda, sigma) draw of the C4 batch of tools/config_runs.py) against the oracle (~30 s of CPU), plus the
+    size-independent properties of a second one: every stored line strictly increasing in x unless the status word
+    says otherwise, lengths within the layout, the summary consistent with the lines"""
+    from dcegm_jl_b200 import Param, _abi
+
+    rng = np.random.default_rng(25032020)
+    lam = 10 ** rng.uniform(np.log10(2e-6), np.log10(0.2), 256)
+    sig = rng.uniform(0, 0.6, 256)
+    ps = []
+    for i in (0, 1):
+        d = dict(na=20000, ny=32, nT=50, retage=51, beta=0.95, R=1.05, sigma=float(sig[i]))
+        d["lambda"] = float(lam[i])
+        ps.append(Param(par=d))
+    g = solver.solve(_abi.MODEL_F, ps)
+    sm = solver.summaries()
+    r = oracle.solve_f(ps[:1], portable=True)
+    assert r.meta[..., 0].max() > 192  # more sections than the shared-memory solver could hold
+    for name in ("lens", "meta", "removed", "vbound", "isects", "status"):
+        assert np.array_equal(getattr(g, name)[:1], getattr(r, name)), name
+    k = np.arange(r.lay.cap)
+    m = np.broadcast_to((k[None, None, None, None, None, :] < r.lens[..., None])[..., None], r.lines.shape)
+    a, b = g.lines[:1][m], r.lines[m]
+    assert ((a == b) | (np.isnan(a) & np.isnan(b))).all()
+    for mi in (0, 1):
+        assert g.lens[mi].max() <= g.lay.cap and sm["max_len"][mi] == g.lens[mi, :49].max()
+        assert sm["tot_segments"][mi] == g.meta[mi, :, 0, 0].sum() and sm["tot_isects"][mi] == g.meta[mi, :, 0, 1].sum()
+        if g.status[mi] == 0:
+            for it in range(49):
+                for idd in (0, 1):
+                    for kind in (0, 1):
+                        x = g.line(mi, kind, idd, it)[0]
+                        assert (np.diff(x) > 0).all()
+
+
 def test_packed_transfer_of_fine_grid_solution(solver):
     """dcegm_solve_f_packed routes through the same solver selection"""
     from dcegm_jl_b200 import _abi
