@@ -18,7 +18,7 @@ EXPORTS = [
     "dcegm_get_layout", "dcegm_fetch_line", "dcegm_fetch_lines", "dcegm_fetch_lens", "dcegm_fetch_vbound",
     "dcegm_fetch_meta", "dcegm_fetch_isects", "dcegm_fetch_removed", "dcegm_fetch_dirty", "dcegm_fetch_packed",
     "dcegm_status", "dcegm_summaries", "dcegm_summaries_to_device", "dcegm_last_timing", "dcegm_upload_f",
-    "dcegm_upload_g", "dcegm_upload_minimal", "dcegm_run", "dcegm_debug_math_check", "dcegm_solve_f_packed", "dcegm_solve_g_packed",
+    "dcegm_upload_g", "dcegm_upload_minimal", "dcegm_run", "dcegm_debug_math_check", "dcegm_debug_dfma_rate", "dcegm_solve_f_packed", "dcegm_solve_g_packed",
     "dcegm_simulate", "dcegm_fetch_sim_moments", "dcegm_fetch_sim_panel", "dcegm_sim_moments_to_device", "dcegm_solve_minimal_borrow", "dcegm_solve_minimal_bequest",
 ]
 
@@ -74,6 +74,7 @@ def load():
     lib.dcegm_summaries.argtypes = [H, C.POINTER(_abi.dcegm_summary)]
     lib.dcegm_summaries_to_device.argtypes = [H, C.c_void_p, C.c_size_t]
     lib.dcegm_last_timing.argtypes = [H, C.POINTER(_abi.dcegm_timing)]
+    lib.dcegm_debug_dfma_rate.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.dcegm_debug_math_check.argtypes = [C.c_ulonglong, C.c_ulonglong, C.c_int, C.c_int, C.POINTER(C.c_ulonglong)]
     for name in EXPORTS:
         fn = getattr(lib, name)  # AttributeError here means the library does not match include/dcegm.h

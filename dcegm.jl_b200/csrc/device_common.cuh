@@ -97,13 +97,18 @@ extern __shared__ __align__(16) unsigned char dc_smem[];
 // region of global memory (MemGlobal).  kTop = largest step of the fixed-trip knot search: lines hold
 // fewer than 2*kTop points.
 struct MemShared {
+    static constexpr int kMaxWarps = 8;       // = kWarps: block-reduction slots in the envelope scratch
     static constexpr int kTop = 1024;
     static constexpr int kSegCapFixed = 192;  // max sections of one splitLine (more -> DCEGM_ST_SEG_OVERFLOW)
+    static constexpr bool kLongLines = false;
     __device__ __forceinline__ unsigned char* mem() const { return dc_smem; }
 };
 struct MemGlobal {
+    static constexpr int kMaxWarps = 32;
     static constexpr int kTop = 32768;
     static constexpr int kSegCapFixed = 0;    // room for one section per point: splitLine cannot overflow
+    static constexpr bool kLongLines = true;  // tens of thousands of points per line: the envelope uses its
+                                              // O(n log n) variants (merge sort, merged insertion, staged sections)
     unsigned char* g;
     __device__ __forceinline__ unsigned char* mem() const { return g; }
 };
@@ -286,10 +291,11 @@ __device__ __forceinline__ double iup(double u, const DevModel& p) {  // utils.j
 // ---------------------------------------------------------------------------------------------
 // block helpers (kThreads threads)
 // ---------------------------------------------------------------------------------------------
-// exclusive prefix sum of data[0..n) in place; returns the total.  red: kWarps+1 ints of scratch.
+// exclusive prefix sum of data[0..n) in place; returns the total.  red: (NT / 32)+1 ints of scratch.
+template <int NT = kThreads>
 __device__ inline int block_scan_excl(int* data, int n, int* red) {
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int per = (n + kThreads - 1) / kThreads;
+    const int per = (n + NT - 1) / NT;
     const int b = tid * per;
     int local = 0;
     for (int i = 0; i < per; i++) {
@@ -305,19 +311,19 @@ __device__ inline int block_scan_excl(int* data, int n, int* red) {
     if (lane == 31) red[wid] = inc;
     __syncthreads();
     if (wid == 0) {
-        int v = lane < kWarps ? red[lane] : 0;
+        int v = lane < (NT / 32) ? red[lane] : 0;
         int vi = v;
 #pragma unroll
-        for (int o = 1; o < kWarps; o <<= 1) {
+        for (int o = 1; o < (NT / 32); o <<= 1) {
             int t = __shfl_up_sync(0xffffffffu, vi, o);
             if (lane >= o) vi += t;
         }
-        if (lane < kWarps) red[lane] = vi - v;
-        if (lane == kWarps - 1) red[kWarps] = vi;
+        if (lane < (NT / 32)) red[lane] = vi - v;
+        if (lane == (NT / 32) - 1) red[(NT / 32)] = vi;
     }
     __syncthreads();
     int run = red[wid] + inc - local;
-    const int total = red[kWarps];
+    const int total = red[(NT / 32)];
     for (int i = 0; i < per; i++) {
         int k = b + i;
         if (k < n) {
@@ -330,6 +336,7 @@ __device__ inline int block_scan_excl(int* data, int n, int* red) {
     return total;
 }
 
+template <int NT = kThreads>
 __device__ inline double block_min(double v, double* red) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 #pragma unroll
@@ -338,10 +345,11 @@ __device__ inline double block_min(double v, double* red) {
     __syncthreads();
     double r = red[0];
 #pragma unroll
-    for (int w = 1; w < kWarps; w++) r = fmin(r, red[w]);
+    for (int w = 1; w < (NT / 32); w++) r = fmin(r, red[w]);
     __syncthreads();
     return r;
 }
+template <int NT = kThreads>
 __device__ inline int block_sum(int v, int* red) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 #pragma unroll
@@ -350,10 +358,11 @@ __device__ inline int block_sum(int v, int* red) {
     __syncthreads();
     int r = 0;
 #pragma unroll
-    for (int w = 0; w < kWarps; w++) r += red[w];
+    for (int w = 0; w < (NT / 32); w++) r += red[w];
     __syncthreads();
     return r;
 }
+template <int NT = kThreads>
 __device__ inline int block_min_int(int v, int* red) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 #pragma unroll
@@ -362,7 +371,7 @@ __device__ inline int block_min_int(int v, int* red) {
     __syncthreads();
     int r = red[0];
 #pragma unroll
-    for (int w = 1; w < kWarps; w++) r = min(r, red[w]);
+    for (int w = 1; w < (NT / 32); w++) r = min(r, red[w]);
     __syncthreads();
     return r;
 }

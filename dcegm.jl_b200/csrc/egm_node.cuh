@@ -30,6 +30,7 @@ using LineSet = LineSetT<MemShared>;
 using LineSetG = LineSetT<MemGlobal>;
 
 // one line -> HBM (interleaved x,y), each point written once
+template <int NT = kThreads>
 __device__ inline void store_line(const DeviceBatch& B, int m, int it, int iy, int id, int kind, const double* x,
                                   const double* y, int n) {
     const size_t slot = line_slot(B.lay, m, it, iy, id, kind);
@@ -37,7 +38,7 @@ __device__ inline void store_line(const DeviceBatch& B, int m, int it, int iy, i
     if (!B.lines) return;
     double2* dst = B.lines + slot * (size_t)B.lay.cap;
     const int nn = n < B.lay.cap ? n : B.lay.cap;
-    for (int k = threadIdx.x; k < nn; k += kThreads) dst[k] = make_double2(x[k], y[k]);
+    for (int k = threadIdx.x; k < nn; k += NT) dst[k] = make_double2(x[k], y[k]);
 }
 
 // vfun (dc_algo.jl:220-251) for the value line (vx, vy, n) with bound vb

@@ -34,11 +34,11 @@ struct EnvScratchT : Mem {
     __host__ __device__ int o_d(int j) const { return off + j * align16(cap * 8); }
     __host__ __device__ int o_i(int j) const { return o_d(5) + j * align16(isec_cap * 8); }
     __host__ __device__ int o_redd() const { return o_i(12); }
-    __host__ __device__ int o_scan() const { return o_redd() + align16(kWarps * 8); }
+    __host__ __device__ int o_scan() const { return o_redd() + align16(Mem::kMaxWarps * 8); }
     __host__ __device__ int o_segb() const { return o_scan() + align16(cap * 4); }
     __host__ __device__ int o_key(int j) const { return o_segb() + align16(((Mem::kSegCapFixed > 0 ? Mem::kSegCapFixed : cap) + 1) * 4) + j * align16(isec_cap * 4); }
     __host__ __device__ int o_red() const { return o_key(2); }
-    __host__ __device__ int o_cnt() const { return o_red() + align16((kWarps + 1) * 4); }
+    __host__ __device__ int o_cnt() const { return o_red() + align16((Mem::kMaxWarps + 1) * 4); }
     __host__ __device__ int o_u16(int j) const { return o_cnt() + 32 + j * align16(cap * 2); }
     __host__ __device__ int o_u8(int j) const { return o_u16(5) + j * align16(cap); }
     __host__ __device__ int o_segrise() const { return o_u8(4); }
@@ -210,7 +210,7 @@ __device__ inline int resolve_switch(const ES& S, const double* X, const double*
 // S.Dx()/S.Dv()/S.Dc()[koff .. koff+na).  On exit (Vx,Vy,*nV) holds m.v[1,it].env and (Cx,Cy,*nC)
 // m.c[1,it].env, both with the prepended credit-constraint point; meta / isects / removed are
 // written to global memory.  All threads of the block must call this.
-template <class ES>
+template <class ES, int NT = kThreads>
 __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0, double ev0, const DevModel& p,
                                        double* Vx, double* Vy, int* nV, double* Cx, double* Cy, int* nC,
                                        dcegm_env_meta* meta_out, double2* isects_out, uint32_t* removed_out,
@@ -220,14 +220,14 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
 
     // ---- bend-back guard (dc_algo.jl:394-418) ------------------------------------------------
     double mn = CUDART_INF;
-    for (int k = tid; k < na; k += kThreads) mn = fmin(mn, S.Dx()[koff + k]);
-    const double minx = block_min(mn, S.redd());
+    for (int k = tid; k < na; k += NT) mn = fmin(mn, S.Dx()[koff + k]);
+    const double minx = block_min<NT>(mn, S.redd());
     const double first = S.Dx()[koff];
     int npre = 0;
     if (!(first <= minx)) {
         npre = koff;  // floor(na/10) - 1 points
         const int klen = na / 10;
-        for (int i = tid; i < npre; i += kThreads) {
+        for (int i = tid; i < npre; i += NT) {
             double x0 = dc_linrange_at(minx, first, klen, i);
             double c0 = x0;
             if (minx < 0) c0 = c0 + fabs(minx) + p.cfloor;
@@ -250,14 +250,14 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
     __syncthreads();
 
     // ---- splitLine: direction changes (envelope.jl:84-110) -----------------------------------
-    for (int k = tid; k < n; k += kThreads) {
+    for (int k = tid; k < n; k += NT) {
         int isb = 0;
         if (k >= 1 && k <= n - 2) isb = (X[k] > X[k - 1]) != (X[k + 1] > X[k]);
         S.scan()[k] = isb;
         S.fknot()[k] = (unsigned char)isb;
     }
     __syncthreads();
-    const int nb = block_scan_excl(S.scan(), n, S.red());
+    const int nb = block_scan_excl<NT>(S.scan(), n, S.red());
     int nseg = nb + 1;
     const bool first_rising = X[1] > X[0];
     bool plain = false;
@@ -274,35 +274,40 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
 
     int ne = 0, nis = 0, nrem = 0;
     if (plain) {
-        for (int k = tid; k < n; k += kThreads) {
+        for (int k = tid; k < n; k += NT) {
             Vx[1 + k] = X[k];
             Vy[1 + k] = V[k];
             S.frem()[k] = 0;
         }
         ne = n;
     } else {
-        for (int k = tid; k < n; k += kThreads)
+        for (int k = tid; k < n; k += NT)
             if (S.fknot()[k]) S.segb()[S.scan()[k] + 1] = k;
         if (tid == 0) {
             S.segb()[0] = 0;
             S.segb()[nseg] = n - 1;
         }
         __syncthreads();
-        for (int s = tid; s < nseg; s += kThreads) S.segrise()[s] = X[S.segb()[s] + 1] > X[S.segb()[s]];
-        for (int k = tid; k < n; k += kThreads) S.order()[k] = 0;
+        for (int s = tid; s < nseg; s += NT) S.segrise()[s] = X[S.segb()[s] + 1] > X[S.segb()[s]];
+        for (int k = tid; k < n; k += NT) S.order()[k] = 0;
         __syncthreads();
 
         DC_CLK(5);
         // ---- every point: sorted position, winning section, top Point (envelope.jl:154-164) ----
         // fine-grid solver: the extent and the size of the first kSegTile sections are staged in shared memory, so
         // that the test below costs two shared loads instead of four dependent global ones
-        constexpr bool kStage = ES::kSegCapFixed == 0;
+        constexpr bool kStage = ES::kLongLines;
         constexpr int kSegTile = kStage ? 1536 : 1;
         __shared__ double t_lo[kSegTile], t_hi[kSegTile];
         __shared__ int t_own[kSegTile];
+        // ... and per group of 32 consecutive sections their common extent and total size: neighbouring sections
+        // are neighbours in x (small wiggles of the value line), so most groups are skipped whole
+        constexpr int kGroups = kSegTile / 32 + 1;
+        __shared__ double g_lo[kGroups], g_hi[kGroups];
+        __shared__ int g_own[kGroups];
         const int ntile = kStage ? (nseg < kSegTile ? nseg : kSegTile) : 0;
         if (kStage) {
-            for (int s = tid; s < ntile; s += kThreads) {
+            for (int s = tid; s < ntile; s += NT) {
                 const int e0 = S.segb()[s], e1 = S.segb()[s + 1];
                 const double xa = X[e0], xb = X[e1];
                 t_lo[s] = xa < xb ? xa : xb;
@@ -310,8 +315,22 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 t_own[s] = e1 - e0 + (s == 0 ? 1 : 0);
             }
             __syncthreads();
+            for (int gi = tid; gi * 32 + 32 <= ntile; gi += NT) {
+                double lo = CUDART_INF, hi = -CUDART_INF;
+                int own = 0;
+                for (int s = gi * 32; s < gi * 32 + 32; s++) {
+                    const double a = t_lo[s], b = t_hi[s];
+                    lo = (a == a) ? (a < lo ? a : lo) : -CUDART_INF;  // a NaN extent is never skipped
+                    hi = (b == b) ? (b > hi ? b : hi) : CUDART_INF;
+                    own += t_own[s];
+                }
+                g_lo[gi] = lo;
+                g_hi[gi] = hi;
+                g_own[gi] = own;
+            }
+            __syncthreads();
         }
-        for (int k = tid; k < n; k += kThreads) {
+        for (int k = tid; k < n; k += NT) {
             const double xk = X[k];
             int rank = 0, ties = 0, w = -1;
             double best = -CUDART_INF, bestx = xk;
@@ -321,6 +340,17 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 // own points to the rank (the boundary shared with the previous section is not theirs),
                 // right of xk nothing; neither contains xk
                 if (kStage && s < ntile) {
+                    if ((s & 31) == 0 && s + 32 <= ntile) {  // a whole group on one side of xk
+                        if (xk > g_hi[s >> 5]) {
+                            rank += g_own[s >> 5];
+                            s += 31;
+                            continue;
+                        }
+                        if (xk < g_lo[s >> 5]) {
+                            s += 31;
+                            continue;
+                        }
+                    }
                     if (xk > t_hi[s]) {
                         rank += t_own[s];
                         continue;
@@ -384,19 +414,19 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         }
         __syncthreads();
         DC_CLK(6);
-        for (int k = tid; k < n; k += kThreads) S.order()[S.pos()[k]] = (unsigned short)k;
+        for (int k = tid; k < n; k += NT) S.order()[S.pos()[k]] = (unsigned short)k;
         __syncthreads();
         // unique(xx)
-        for (int q = tid; q < n; q += kThreads) {
+        for (int q = tid; q < n; q += NT) {
             int uq = (q == 0) || (X[S.order()[q]] != X[S.order()[q - 1]]);
             S.fuq()[q] = (unsigned char)uq;
             S.scan()[q] = uq;
         }
         __syncthreads();
-        const int nu = block_scan_excl(S.scan(), n, S.red());
-        for (int q = tid; q < n; q += kThreads)
+        const int nu = block_scan_excl<NT>(S.scan(), n, S.red());
+        for (int q = tid; q < n; q += NT)
             if (S.fuq()[q]) S.ord2()[S.scan()[q]] = S.order()[q];
-        for (int k = tid; k < n; k += kThreads) {
+        for (int k = tid; k < n; k += NT) {
             int q = S.pos()[k];
             S.pos()[k] = (unsigned short)(S.fuq()[q] ? S.scan()[q] : S.scan()[q] - 1);  // index into the unique grid
         }
@@ -404,7 +434,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
 
         DC_CLK(7);
         // ---- changes of winner (envelope.jl:173-243) ---------------------------------------------
-        for (int j = tid; j < nu; j += kThreads) {
+        for (int j = tid; j < nu; j += NT) {
             S.cntI()[j] = 0;
             if (j >= 1 && S.win()[S.ord2()[j]] != S.win()[S.ord2()[j - 1]]) {
                 int slot = atomicAdd(&S.cnt()[0], 1);
@@ -413,7 +443,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         }
         __syncthreads();
         const int nsw = S.cnt()[0];
-        for (int t = tid >> 5; t < nsw; t += kWarps) {  // warp per change of winner
+        for (int t = tid >> 5; t < nsw; t += (NT / 32)) {  // warp per change of winner
             const int j = S.swj()[t];
             double px[kSwitchMaxIsect], py[kSwitchMaxIsect];
             int c = resolve_switch(S, X, V, nseg, S.win()[S.ord2()[j - 1]], S.win()[S.ord2()[j]], X[S.ord2()[j - 1]], X[S.ord2()[j]],
@@ -439,7 +469,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             nis = S.isec_cap;
         }
         // intersections in emission order (ascending cell, then order of discovery)
-        for (int t = tid; t < nis; t += kThreads) {
+        for (int t = tid; t < nis; t += NT) {
             int key = S.islkey()[t], r = 0;
             for (int u = 0; u < nis; u++) r += S.islkey()[u] < key;
             S.isl2x()[r] = S.islx()[t];
@@ -447,16 +477,16 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             S.isl2key()[r] = key;
         }
         // ---- emission (envelope.jl:170, 212, 248-252) ----------------------------------------------
-        for (int j = tid; j < nu; j += kThreads) {
+        for (int j = tid; j < nu; j += NT) {
             int k = S.ord2()[j];
             int reg = (j == 0) || S.fknot()[k] || (j == nu - 1);
             S.scan()[j] = (j == 0 ? 0 : (int)S.cntI()[j]) + reg;
         }
         __syncthreads();
-        ne = block_scan_excl(S.scan(), nu, S.red());
+        ne = block_scan_excl<NT>(S.scan(), nu, S.red());
         const int room = S.cap - 1;
         if (ne > room) status |= DCEGM_ST_LINE_OVERFLOW;
-        for (int j = tid; j < nu; j += kThreads) {
+        for (int j = tid; j < nu; j += NT) {
             int k = S.ord2()[j];
             int reg = (j == 0) || S.fknot()[k] || (j == nu - 1);
             int at = S.scan()[j] + (j == 0 ? 0 : (int)S.cntI()[j]);
@@ -465,7 +495,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 Vy[1 + at] = S.Ty()[k];
             }
         }
-        for (int t = tid; t < nis; t += kThreads) {
+        for (int t = tid; t < nis; t += NT) {
             int key = S.isl2key()[t];
             int at = S.scan()[key / kSwitchMaxIsect] + key % kSwitchMaxIsect;
             if (at < room) {
@@ -475,7 +505,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         }
         if (ne > room) ne = room;
         // ---- removed! (envelope.jl:64-71): points with no exactly equal Point in the envelope ------
-        for (int k = tid; k < n; k += kThreads) {
+        for (int k = tid; k < n; k += NT) {
             int j = S.pos()[k];
             bool reg = (j == 0) || S.fknot()[k] || (j == nu - 1);
             bool kept = reg && S.Tx()[k] == X[k] && S.Ty()[k] == V[k];
@@ -487,17 +517,17 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
     DC_CLK(9);
     {
         int local = 0;
-        for (int k = tid; k < n; k += kThreads) local += S.frem()[k];
-        nrem = block_sum(local, S.red());
+        for (int k = tid; k < n; k += NT) local += S.frem()[k];
+        nrem = block_sum<NT>(local, S.red());
     }
     // removed bitmask -> global
-    for (int base = 0; base < rem_words * 32; base += kThreads) {
+    for (int base = 0; base < rem_words * 32; base += NT) {
         int k = base + tid;
         unsigned bit = (k < n) ? S.frem()[k] : 0;
         unsigned word = __ballot_sync(0xffffffffu, bit);
         if ((tid & 31) == 0 && k / 32 < rem_words) removed_out[k / 32] = word;
     }
-    for (int t = tid; t < S.isec_cap; t += kThreads)
+    for (int t = tid; t < S.isec_cap; t += NT)
         isects_out[t] = t < nis ? make_double2(S.isl2x()[t], S.isl2y()[t]) : make_double2(0.0, 0.0);
 
     DC_CLK(5);
@@ -505,7 +535,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
     int ncur;
     if (nrem > 0) {
         const int lane = tid & 31, wid = tid >> 5;
-        for (int t = wid; t < nis; t += kWarps) {
+        for (int t = wid; t < nis; t += (NT / 32)) {
             const double ix = S.isl2x()[t];
             int jl = -1, jr = 0x7fffffff;
             for (int k = lane; k < n; k += 32) {
@@ -541,7 +571,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             }
         }
         // deleteat!(cout, rmidx)  (dc_algo.jl:482)
-        for (int k = tid; k < n; k += kThreads) S.scan()[k] = S.frem()[k] ? 0 : 1;
+        for (int k = tid; k < n; k += NT) S.scan()[k] = S.frem()[k] ? 0 : 1;
         __syncthreads();
         // compact the two insertion lists (push! order)
         if (tid == 0) {
@@ -561,8 +591,8 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             S.cnt()[0] = nl;
             S.cnt()[1] = nr;
         }
-        ncur = block_scan_excl(S.scan(), n, S.red());
-        for (int k = tid; k < n; k += kThreads)
+        ncur = block_scan_excl<NT>(S.scan(), n, S.red());
+        for (int k = tid; k < n; k += NT)
             if (!S.frem()[k]) {
                 Cx[1 + S.scan()[k]] = X[k];
                 Cy[1 + S.scan()[k]] = Cc[k];
@@ -570,16 +600,71 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         __syncthreads();
         const int nl = S.cnt()[0], nr = S.cnt()[1];
         if (nl != nr) status |= DCEGM_ST_MISALIGNED;
-        // insert!(…) pairs (dc_algo.jl:486-492)
-        for (int i = 0; i < nl; i++) {
+        // insert!(…) pairs (dc_algo.jl:486-492).  The reference inserts one pair after the other, each before
+        // the first x greater than its left point in the line as it stands.  When the surviving policy is
+        // ascending and every pair lies at or right of the pair before it (the regular case: intersections come
+        // in ascending order), that sequence equals one merge: pair i lands in front of base point
+        // q_i = #{x <= left_i}, behind the i pairs before it.  Anything else takes the sequential path below.
+        bool merged = false;
+        constexpr bool kTryMerge = ES::kLongLines;  // at ~500 points the sequential path is as fast (measured)
+        if (kTryMerge && nl > 0 && nl == nr && ncur + 2 * nl <= S.cap - 1) {
+            int irregular = 0;
+            for (int k = tid; k + 1 < ncur; k += NT) irregular |= Cx[1 + k + 1] < Cx[1 + k];
+            for (int i = tid; i < nl; i += NT) {
+                const double lx = S.insLx()[i];
+                int lo = 0, len = ncur;  // #{base x <= lx}
+                while (len > 0) {
+                    const int half = len >> 1;
+                    const bool le = Cx[1 + lo + half] <= lx;
+                    lo = le ? lo + half + 1 : lo;
+                    len = le ? len - half - 1 : half;
+                }
+                S.islkey()[i] = lo;
+                irregular |= lo >= ncur;  // no x greater than the left point: the reference raises here
+                irregular |= !(lx == lx);
+                if (i > 0) {
+                    const double pl = S.insLx()[i - 1], pr = S.insRx()[i - 1];
+                    irregular |= !(pl <= lx && pr <= lx);
+                }
+            }
+            merged = block_sum<NT>(irregular, S.red()) == 0;
+        }
+        if (merged) {
+            for (int k = tid; k < ncur; k += NT) {
+                int lo = 0, len = nl;  // pairs in front of base point k: #{q_i <= k}
+                while (len > 0) {
+                    const int half = len >> 1;
+                    const bool le = S.islkey()[lo + half] <= k;
+                    lo = le ? lo + half + 1 : lo;
+                    len = le ? len - half - 1 : half;
+                }
+                S.Dx()[k + 2 * lo] = Cx[1 + k];
+                S.Dv()[k + 2 * lo] = Cy[1 + k];
+            }
+            for (int i = tid; i < nl; i += NT) {
+                const int at = S.islkey()[i] + 2 * i;
+                S.Dx()[at] = S.insLx()[i];
+                S.Dv()[at] = S.insLy()[i];
+                S.Dx()[at + 1] = S.insRx()[i];
+                S.Dv()[at + 1] = S.insRy()[i];
+            }
+            __syncthreads();
+            ncur += 2 * nl;
+            for (int k = tid; k < ncur; k += NT) {
+                Cx[1 + k] = S.Dx()[k];
+                Cy[1 + k] = S.Dv()[k];
+            }
+            __syncthreads();
+        }
+        for (int i = 0; i < nl && !merged; i++) {
             const double lx = S.insLx()[i];
             int cand = 0x7fffffff;
-            for (int k = tid; k < ncur; k += kThreads)
+            for (int k = tid; k < ncur; k += NT)
                 if (Cx[1 + k] > lx) {
                     cand = k;
                     break;
                 }
-            const int j = block_min_int(cand, S.red());
+            const int j = block_min_int<NT>(cand, S.red());
             if (j == 0x7fffffff || i >= nr) {
                 status |= DCEGM_ST_INSERT_RANGE;
                 break;
@@ -589,7 +674,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 break;
             }
             // shift [j, ncur) right by two, highest chunk first
-            for (int top = ncur - 1; top >= j; top -= kThreads) {
+            for (int top = ncur - 1; top >= j; top -= NT) {
                 int k = top - tid;
                 double vx = 0, vy = 0;
                 if (k >= j) {
@@ -613,7 +698,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             __syncthreads();
         }
     } else {
-        for (int k = tid; k < n; k += kThreads) {
+        for (int k = tid; k < n; k += NT) {
             Cx[1 + k] = X[k];
             Cy[1 + k] = Cc[k];
         }
@@ -633,26 +718,26 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
     // sortx!(c): stable sort on x.  The repaired policy is already ascending except in degenerate
     // cases; detect, and only then rank-sort through the (now free) D arrays.
     int bad = 0;
-    for (int k = tid; k + 1 < lenC; k += kThreads) bad |= Cx[k + 1] < Cx[k];
-    bad = block_sum(bad, S.red());
-    if (bad && ES::kSegCapFixed == 0) {
+    for (int k = tid; k + 1 < lenC; k += NT) bad |= Cx[k + 1] < Cx[k];
+    bad = block_sum<NT>(bad, S.red());
+    if (bad && ES::kLongLines) {
         // long lines (fine-grid solver): stable merge sort of the natural ascending runs, pairwise and
         // bottom-up; every element finds its place in the merged pair with one binary search in the sibling
         // run (left-run elements go before equal right-run elements).  Ping-pong with the free D arrays;
         // run boundaries in segb (room for cap + 1 entries in this variant), scan as temporary.
-        for (int k = tid; k < lenC; k += kThreads) S.scan()[k] = (k == 0) || (Cx[k] < Cx[k - 1]);
+        for (int k = tid; k < lenC; k += NT) S.scan()[k] = (k == 0) || (Cx[k] < Cx[k - 1]);
         __syncthreads();
-        for (int k = tid; k < lenC; k += kThreads) S.fuq()[k] = (unsigned char)S.scan()[k];
+        for (int k = tid; k < lenC; k += NT) S.fuq()[k] = (unsigned char)S.scan()[k];
         __syncthreads();
-        int nr = block_scan_excl(S.scan(), lenC, S.red());
+        int nr = block_scan_excl<NT>(S.scan(), lenC, S.red());
         int* rb = S.segb();
-        for (int k = tid; k < lenC; k += kThreads)
+        for (int k = tid; k < lenC; k += NT)
             if (S.fuq()[k]) rb[S.scan()[k]] = k;
         if (tid == 0) rb[nr] = lenC;
         __syncthreads();
         double *sx = Cx, *sy = Cy, *dx = S.Dx(), *dy = S.Dv();
         while (nr > 1) {
-            for (int k = tid; k < lenC; k += kThreads) {
+            for (int k = tid; k < lenC; k += NT) {
                 int lo = 0, len = nr;  // run containing k: last boundary <= k
                 while (len > 0) {
                     const int half = len >> 1;
@@ -690,9 +775,9 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 dy[out] = sy[k];
             }
             const int nr2 = (nr + 1) >> 1;
-            for (int i = tid; i < nr2; i += kThreads) S.scan()[i] = rb[2 * i];
+            for (int i = tid; i < nr2; i += NT) S.scan()[i] = rb[2 * i];
             __syncthreads();
-            for (int i = tid; i < nr2; i += kThreads) rb[i] = S.scan()[i];
+            for (int i = tid; i < nr2; i += NT) rb[i] = S.scan()[i];
             if (tid == 0) rb[nr2] = lenC;
             __syncthreads();
             nr = nr2;
@@ -700,14 +785,14 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             t = sy; sy = dy; dy = t;
         }
         if (sx != Cx) {
-            for (int k = tid; k < lenC; k += kThreads) {
+            for (int k = tid; k < lenC; k += NT) {
                 Cx[k] = sx[k];
                 Cy[k] = sy[k];
             }
             __syncthreads();
         }
     } else if (bad) {
-        for (int k = tid; k < lenC; k += kThreads) {
+        for (int k = tid; k < lenC; k += NT) {
             const double xk = Cx[k];
             int r = 0;
             for (int i = 0; i < lenC; i++) {
@@ -718,7 +803,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             S.Dv()[r] = Cy[k];
         }
         __syncthreads();
-        for (int k = tid; k < lenC; k += kThreads) {
+        for (int k = tid; k < lenC; k += NT) {
             Cx[k] = S.Dx()[k];
             Cy[k] = S.Dv()[k];
         }
@@ -726,11 +811,11 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
     }
     // status: knot vectors the next period's interpolate() would reject, non-finite entries
     int flag = 0;
-    for (int k = tid; k < lenC; k += kThreads) {
+    for (int k = tid; k < lenC; k += NT) {
         if (k + 1 < lenC && !(Cx[k + 1] > Cx[k])) flag |= DCEGM_ST_NONMONOTONE;
         if (!isfinite(Cx[k]) || !isfinite(Cy[k])) flag |= DCEGM_ST_NONFINITE;
     }
-    for (int k = tid; k < lenV; k += kThreads) {
+    for (int k = tid; k < lenV; k += NT) {
         if (k + 1 < lenV && !(Vx[k + 1] > Vx[k])) flag |= DCEGM_ST_NONMONOTONE;
         if (!isfinite(Vx[k]) || !isfinite(Vy[k])) flag |= DCEGM_ST_NONFINITE;
     }

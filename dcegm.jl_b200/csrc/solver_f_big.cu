@@ -20,6 +20,16 @@
 
 namespace dcegm {
 
+// threads of big_env_kernel: the envelope of one model is one CTA's work, its passes over the ~22 000 points
+// of a C4 line are bound by memory latency, so the CTA is as wide as the register file allows
+#ifndef DCEGM_BIG_ENV_THREADS
+#define DCEGM_BIG_ENV_THREADS 1024
+#endif
+constexpr int kEnvThreads = DCEGM_BIG_ENV_THREADS;
+#ifndef DCEGM_BIG_EGM_MINBLOCKS
+#define DCEGM_BIG_EGM_MINBLOCKS 3
+#endif
+
 // per-model state that survives between the launches of one solve
 struct BigState {
     int n_wc[2], n_wv[2], n_r[2];  // by line set
@@ -75,6 +85,7 @@ __device__ __forceinline__ LineSetG big_set(const BigPlan& P, unsigned char* g, 
 }
 
 // block-level: knot index over the three knot vectors of L (the lines the next EGM launch reads)
+template <int NT>
 __device__ inline void big_build_index(const BigPlan& P, unsigned char* g, BigState* st, const LineSetG& L, int status) {
     const int tid = threadIdx.x;
     const bool ok = !(status & (DCEGM_ST_NONMONOTONE | DCEGM_ST_NONFINITE)) && L.n_wc >= 2 && L.n_wv >= 2 && L.n_r >= 2;
@@ -88,7 +99,7 @@ __device__ inline void big_build_index(const BigPlan& P, unsigned char* g, BigSt
         knot_index_range(Kc, L.wc_x(), L.n_wc, nb);
         knot_index_range(Kv, L.wv_x(), L.n_wv, nb);
         const int nmax = max(L.n_r, max(L.n_wc, L.n_wv));
-        for (int k = tid; k < nmax; k += kThreads) {
+        for (int k = tid; k < nmax; k += NT) {
             if (k < L.n_r) knot_index_build_step_at(P.tab(g, 0), Kr, L.r_x(), L.n_r, nb, k);
             if (k < L.n_wc) knot_index_build_step_at(P.tab(g, 1), Kc, L.wc_x(), L.n_wc, nb, k);
             if (k < L.n_wv) knot_index_build_step_at(P.tab(g, 2), Kv, L.wv_x(), L.n_wv, nb, k);
@@ -109,20 +120,23 @@ __device__ inline void big_summary(const DeviceBatch& B, int m, const DevModel& 
     const int tid = threadIdx.x;
     const int nT = p.nT;
     constexpr int Top = MemGlobal::kTop;
+    // the first kThreads threads sum in the order of solve_f_kernel's 256-thread CTA, whatever this CTA's width
     double cs_c = 0.0, cs_v = 0.0;
-    for (int k = tid; k < L0.n_wc; k += kThreads) cs_c += L0.wc_y()[k];
-    for (int k = tid; k < L0.n_r; k += kThreads) cs_c += L0.rc_y()[k];
-    for (int k = tid; k < L0.n_wv; k += kThreads) cs_v += isfinite(L0.wv_y()[k]) ? L0.wv_y()[k] : 0.0;
-    for (int k = tid; k < L0.n_r; k += kThreads) cs_v += isfinite(L0.rv_y()[k]) ? L0.rv_y()[k] : 0.0;
     __shared__ double s_cs[2][kWarps];
+    if (tid < kThreads) {
+        for (int k = tid; k < L0.n_wc; k += kThreads) cs_c += L0.wc_y()[k];
+        for (int k = tid; k < L0.n_r; k += kThreads) cs_c += L0.rc_y()[k];
+        for (int k = tid; k < L0.n_wv; k += kThreads) cs_v += isfinite(L0.wv_y()[k]) ? L0.wv_y()[k] : 0.0;
+        for (int k = tid; k < L0.n_r; k += kThreads) cs_v += isfinite(L0.rv_y()[k]) ? L0.rv_y()[k] : 0.0;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        cs_c += __shfl_xor_sync(0xffffffffu, cs_c, o);
-        cs_v += __shfl_xor_sync(0xffffffffu, cs_v, o);
-    }
-    if ((tid & 31) == 0) {
-        s_cs[0][tid >> 5] = cs_c;
-        s_cs[1][tid >> 5] = cs_v;
+        for (int o = 16; o > 0; o >>= 1) {
+            cs_c += __shfl_xor_sync(0xffffffffu, cs_c, o);
+            cs_v += __shfl_xor_sync(0xffffffffu, cs_v, o);
+        }
+        if ((tid & 31) == 0) {
+            s_cs[0][tid >> 5] = cs_c;
+            s_cs[1][tid >> 5] = cs_v;
+        }
     }
     __syncthreads();
     if (tid == 0) {
@@ -220,7 +234,7 @@ __global__ void __launch_bounds__(kThreads) big_terminal_kernel(DeviceBatch B, u
         st->sum_envp = st->sum_seg = st->sum_is = st->sum_rm = st->sum_maxlen = 0;
         st->sum_pts = 4 + 2 * nv;
     }
-    big_build_index(P, g, st, C, 0);
+    big_build_index<kThreads>(P, g, st, C, 0);
     if (nT == 1) {
         __syncthreads();
         big_summary(B, m, p, C, st, 0);
@@ -228,7 +242,7 @@ __global__ void __launch_bounds__(kThreads) big_terminal_kernel(DeviceBatch B, u
 }
 
 // ---- EGM step of period t: thread per savings grid point ------------------------------------------------
-__global__ void __launch_bounds__(kThreads) big_egm_kernel(DeviceBatch B, unsigned char* scratch, size_t stride, int t) {
+__global__ void __launch_bounds__(kThreads, DCEGM_BIG_EGM_MINBLOCKS) big_egm_kernel(DeviceBatch B, unsigned char* scratch, size_t stride, int t) {
     const int lm = blockIdx.y;  // model within this launch
     const int m = B.first + lm;
     const int tid = threadIdx.x;
@@ -333,7 +347,7 @@ extern "C" int dcegm_debug_phase_clocks_big(unsigned long long* out, int reset) 
 #endif
 
 // ---- envelope, tail and store of period t: one CTA per model ------------------------------------------------
-__global__ void __launch_bounds__(kThreads) big_env_kernel(DeviceBatch B, unsigned char* scratch, size_t stride, int t) {
+__global__ void __launch_bounds__(kEnvThreads) big_env_kernel(DeviceBatch B, unsigned char* scratch, size_t stride, int t) {
     const int m = B.first + blockIdx.x;
     const int tid = threadIdx.x;
     BIG_CLK_BEGIN();
@@ -362,7 +376,7 @@ __global__ void __launch_bounds__(kThreads) big_env_kernel(DeviceBatch B, unsign
 
     if (B.dirty) {  // runfdemo: vdirty / cdirty (dc_algo.jl:79-82)
         double2* d = B.dirty + line_slot(B.lay, m, t, 0, 0, 0) * (size_t)na;
-        for (int k = tid; k < na; k += kThreads) {
+        for (int k = tid; k < na; k += kEnvThreads) {
             d[k] = make_double2(S.Dx()[koff + k], S.Dc()[koff + k]);
             d[(size_t)na + k] = make_double2(S.Dx()[koff + k], S.Dv()[koff + k]);
             d[(size_t)2 * na + k] = make_double2(C.r_x()[1 + k], C.rc_y()[1 + k]);
@@ -372,7 +386,7 @@ __global__ void __launch_bounds__(kThreads) big_env_kernel(DeviceBatch B, unsign
 
     // worker: secondary envelope + policy repair
     const size_t ss = state_slot(B.lay, m, t, 0);
-    worker_envelope(S, koff, na, a0, ev0w, p, C.wv_x(), C.wv_y(), &s_n[0], C.wc_x(), C.wc_y(), &s_n[1], B.meta + ss,
+    worker_envelope<EnvScratchG, kEnvThreads>(S, koff, na, a0, ev0w, p, C.wv_x(), C.wv_y(), &s_n[0], C.wc_x(), C.wc_y(), &s_n[1], B.meta + ss,
                     B.isects + ss * (size_t)B.lay.isec_cap, B.removed + ss * (size_t)B.lay.rem_words, B.lay.rem_words);
     C.n_wv = s_n[0];
     C.n_wc = s_n[1];
@@ -389,17 +403,17 @@ __global__ void __launch_bounds__(kThreads) big_env_kernel(DeviceBatch B, unsign
     C.vb_r = ev0r;
     __syncthreads();
     int flag = 0;
-    for (int k = tid; k < na + 1; k += kThreads) {
+    for (int k = tid; k < na + 1; k += kEnvThreads) {
         if (k + 1 < na + 1 && !(C.r_x()[k + 1] > C.r_x()[k])) flag |= DCEGM_ST_NONMONOTONE;
         if (!isfinite(C.r_x()[k]) || !isfinite(C.rc_y()[k]) || !isfinite(C.rv_y()[k])) flag |= DCEGM_ST_NONFINITE;
     }
     if (flag) atomicOr(&s_status, flag);
     if (tid == 0 && S.cnt()[2]) atomicOr(&s_status, S.cnt()[2]);
 
-    store_line(B, m, t, 0, 0, DCEGM_KIND_C, C.wc_x(), C.wc_y(), C.n_wc);
-    store_line(B, m, t, 0, 0, DCEGM_KIND_V, C.wv_x(), C.wv_y(), C.n_wv);
-    store_line(B, m, t, 0, 1, DCEGM_KIND_C, C.r_x(), C.rc_y(), C.n_r);
-    store_line(B, m, t, 0, 1, DCEGM_KIND_V, C.r_x(), C.rv_y(), C.n_r);
+    store_line<kEnvThreads>(B, m, t, 0, 0, DCEGM_KIND_C, C.wc_x(), C.wc_y(), C.n_wc);
+    store_line<kEnvThreads>(B, m, t, 0, 0, DCEGM_KIND_V, C.wv_x(), C.wv_y(), C.n_wv);
+    store_line<kEnvThreads>(B, m, t, 0, 1, DCEGM_KIND_C, C.r_x(), C.rc_y(), C.n_r);
+    store_line<kEnvThreads>(B, m, t, 0, 1, DCEGM_KIND_V, C.r_x(), C.rv_y(), C.n_r);
     __syncthreads();
     const int status = s_status;
     if (tid == 0) {
@@ -423,7 +437,7 @@ __global__ void __launch_bounds__(kThreads) big_env_kernel(DeviceBatch B, unsign
     }
     DC_CLK(13);
     if (t > 0) {
-        big_build_index(P, g, st, C, status);
+        big_build_index<kEnvThreads>(P, g, st, C, status);
         BIG_CLK_END();
         return;
     }
@@ -446,7 +460,7 @@ cudaError_t launch_solve_f_big(const DeviceBatch& B0, int first, int count, unsi
     const dim3 ggrid((na + kThreads - 1) / kThreads, count);
     for (int t = nT - 2; t >= 0; t--) {
         big_egm_kernel<<<ggrid, kThreads, 0, stream>>>(B, scratch, stride, t);
-        big_env_kernel<<<count, kThreads, 0, stream>>>(B, scratch, stride, t);
+        big_env_kernel<<<count, kEnvThreads, 0, stream>>>(B, scratch, stride, t);
         nl += 2;
     }
     if (nlaunch) *nlaunch = nl;

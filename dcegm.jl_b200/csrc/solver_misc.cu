@@ -189,7 +189,57 @@ __global__ void math_check_kernel(unsigned long long n, unsigned long long seed,
     if (bad_rcp) atomicAdd(&which[1], bad_rcp);
 }
 
+// ---- diagnostics: FP64 issue rate of this device ------------------------------------------------
+// Eight independent DFMA chains per thread, 1024 resident threads per SM, no memory traffic: the rate at
+// which the FP64 pipe retires warp instructions.  The denominator of the FP64 roofline in bench.py.
+__global__ void __launch_bounds__(256) fp64_peak_kernel(int iters, double seed, double* sink) {
+    double a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    const double m = 0.999999, c = 1e-7;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+            a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+        }
+    }
+    const double r = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+    if (r == 12345.678) sink[0] = r;  // never true: keeps the chains alive
+}
+
 }  // namespace dcegm
+
+extern "C" int dcegm_debug_dfma_rate(int device_ordinal, double* dfma_per_s, double* ms) {
+    if (!dfma_per_s) return DCEGM_E_INVALID;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return DCEGM_E_NODEVICE;
+    if (device_ordinal < 0 || device_ordinal >= ndev || cudaSetDevice(device_ordinal) != cudaSuccess) return DCEGM_E_INVALID;
+    int sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_ordinal);
+    double* d = nullptr;
+    if (cudaMalloc(&d, 8) != cudaSuccess) return DCEGM_E_CUDA;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int iters = 4096, blocks = sms * 4 * 8;
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; rep++) {  // first repetition warms up
+        cudaEventRecord(e0);
+        dcegm::fp64_peak_kernel<<<blocks, 256>>>(iters, 1.0 + rep, d);
+        cudaEventRecord(e1);
+        if (cudaEventSynchronize(e1) != cudaSuccess) break;
+        float t = 0.f;
+        cudaEventElapsedTime(&t, e0, e1);
+        if (rep > 0 && t < best) best = t;
+    }
+    const cudaError_t e = cudaGetLastError();
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    if (e != cudaSuccess || best > 1e29f) return DCEGM_E_CUDA;
+    *dfma_per_s = (double)blocks * 256.0 * iters * 64.0 / (best * 1e-3);
+    if (ms) *ms = best;
+    return DCEGM_OK;
+}
 
 extern "C" int dcegm_debug_math_check(unsigned long long n, unsigned long long seed, int emin, int emax,
                                       unsigned long long* mismatches2) {

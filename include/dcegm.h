@@ -307,6 +307,11 @@ int  dcegm_fetch_sim_panel(dcegm_handle h, int model, double* w0, double* w1, do
 int  dcegm_debug_math_check(unsigned long long n, unsigned long long seed, int emin, int emax,
                             unsigned long long* mismatches2);
 
+/* FP64 issue rate of the device: thread-level DFMA per second retired by a kernel of independent DFMA chains
+ * at full occupancy (no memory traffic); *ms = duration of the best repetition.  The solver kernels are bound by
+ * this pipe, not by HBM ("Roofline"); bench.py reports their FP64 instruction rate against it. */
+int  dcegm_debug_dfma_rate(int device_ordinal, double* dfma_per_s, double* ms);
+
 #ifdef __cplusplus
 }
 #endif
