@@ -5,6 +5,7 @@
 
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -22,6 +23,8 @@ cudaError_t launch_solve_g(const DeviceBatch& B, int first, int count, cudaStrea
 cudaError_t launch_solve_minimal(const DeviceBatch& B, int first, int count, cudaStream_t stream);
 cudaError_t launch_pack_lines(const DeviceBatch& B, int first, int count, const long long* d_offsets, double2* d_dst,
                               cudaStream_t stream);
+cudaError_t launch_chunk_offsets(const int32_t* lens, size_t nsl, int cap, long long* d_off, long long* h_off_mapped,
+                                 cudaStream_t stream);
 cudaError_t launch_sim(const DeviceBatch& B, const SimBatch& Sb, int first, int count, cudaStream_t stream);
 size_t sim_smem_bytes(const dcegm_layout& l);
 size_t solver_f_smem_bytes(int cap, int isec_cap);
@@ -41,7 +44,6 @@ struct dcegm_ctx {
     cudaStream_t s_pack = nullptr, s_copy = nullptr;  // pipelined solve-to-host: packing and D2H streams
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     std::vector<cudaEvent_t> ev_pool;                 // per-chunk events of the pipelined solve
-    int32_t* pin_lens = nullptr;                      // pinned staging: one chunk of lens / offsets
     long long* pin_off = nullptr;
     size_t pin_slots = 0;
     DevBuf pack_xy2;
@@ -216,19 +218,36 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     if (!h) return DCEGM_E_INVALID;
     if (!xy || !offsets || !npoints) return fail(h, DCEGM_E_INVALID, "xy/offsets/npoints is null");
     if (flags & DCEGM_SUMMARY_ONLY) return fail(h, DCEGM_E_INVALID, "DCEGM_SUMMARY_ONLY keeps no lines to pack");
+    const bool trace = getenv("DCEGM_TRACE") != nullptr;  // host timestamps of the pipeline on stderr
+    const auto tr0 = std::chrono::steady_clock::now();
+    auto trace_ms = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tr0).count(); };
     int rc = upload(h, model, params, nmodels, flags);
     if (rc) return rc;
+    if (trace) fprintf(stderr, "[dcegm] %8.3f ms upload done (host setup %.3f, h2d %.3f)\n", trace_ms(), h->timing.setup_host_ms, h->timing.h2d_ms);
     const DeviceBatch& B = h->batch;
     const dcegm_layout& l = B.lay;
     const size_t per = (size_t)l.nT * l.nstate * 4;
     const size_t nstates = (size_t)nmodels * l.nT * l.nstate;
-    // chunks of whole waves (2 CTAs x 148 SMs), at most 16 of them
+    // chunks of whole waves (2 CTAs x 148 SMs): one wave first, so that the first transfer starts early, then
+    // two waves each, at most 16 chunks
     const int wave = 296;
-    int nchunks = (nmodels + 2 * wave - 1) / (2 * wave);
-    nchunks = nchunks > 16 ? 16 : nchunks;
-    int chunk = (nmodels + nchunks - 1) / nchunks;
-    chunk = (chunk + wave - 1) / wave * wave;
-    nchunks = (nmodels + chunk - 1) / chunk;
+    std::vector<int> cstart, ccount;
+    {
+        int per_chunk = 2 * wave;
+        while ((nmodels - wave + per_chunk - 1) / per_chunk + 1 > 16) per_chunk += wave;
+        int c0 = 0;
+        while (c0 < nmodels) {
+            int cnt = cstart.empty() && nmodels > wave ? wave : per_chunk;
+            if (h->big) cnt = 148 * ((nmodels + 148 * 16 - 1) / (148 * 16));  // fine-grid solver: one envelope CTA per SM
+            cnt = cnt < nmodels - c0 ? cnt : nmodels - c0;
+            cstart.push_back(c0);
+            ccount.push_back(cnt);
+            c0 += cnt;
+        }
+    }
+    const int nchunks = (int)cstart.size();
+    int chunk = 0;
+    for (int c : ccount) chunk = c > chunk ? c : chunk;
     if (!h->s_pack) {
         CK(cudaStreamCreateWithFlags(&h->s_pack, cudaStreamNonBlocking));
         CK(cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking));
@@ -240,19 +259,20 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     }
     const size_t cslots = per * chunk;
     if (h->pin_slots < cslots) {
-        if (h->pin_lens) cudaFreeHost(h->pin_lens);
         if (h->pin_off) cudaFreeHost(h->pin_off);
-        h->pin_lens = nullptr;
         h->pin_off = nullptr;
         h->pin_slots = 0;
-        CK(cudaHostAlloc((void**)&h->pin_lens, sizeof(int32_t) * cslots, cudaHostAllocDefault));
-        CK(cudaHostAlloc((void**)&h->pin_off, sizeof(long long) * (cslots + 1), cudaHostAllocDefault));
+        // host-mapped: written by chunk_offsets_kernel, read by the host after an event (no copy-engine transfer)
+        CK(cudaHostAlloc((void**)&h->pin_off, sizeof(long long) * (cslots + 1), cudaHostAllocMapped));
         h->pin_slots = cslots;
     }
+    long long* pin_off_dev = nullptr;
+    CK(cudaHostGetDevicePointer((void**)&pin_off_dev, h->pin_off, 0));
     if ((rc = ensure(h, h->pack_off, sizeof(long long) * (cslots + 1), false))) return rc;
     const size_t pack_bytes = sizeof(double2) * cslots * l.cap;
     if ((rc = ensure(h, h->pack_xy, pack_bytes, false))) return rc;
-    if ((rc = ensure(h, h->pack_xy2, pack_bytes, false))) return rc;
+    if (nchunks > 1)
+        if ((rc = ensure(h, h->pack_xy2, pack_bytes, false))) return rc;
 
     CK(cudaEventRecord(h->ev[2], h->stream));
     CK(cudaMemsetAsync(B.isects, 0, sizeof(double2) * nstates * l.isec_cap, h->stream));
@@ -260,10 +280,11 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     CK(cudaMemsetAsync(B.lens, 0, sizeof(int32_t) * nstates * 4, h->stream));
     CK(cudaMemsetAsync(B.meta, 0, sizeof(dcegm_env_meta) * nstates, h->stream));
     CK(cudaMemsetAsync(B.vbound, 0, sizeof(double) * nstates * 2, h->stream));
+    int launches = 0;
     for (int c = 0; c < nchunks; c++) {
-        const int c0 = c * chunk, cnt = (nmodels - c0 < chunk) ? nmodels - c0 : chunk;
-        cudaError_t e = launch_range(h, B, c0, cnt, h->stream);
+        cudaError_t e = launch_range(h, B, cstart[c], ccount[c], h->stream);
         if (e != cudaSuccess) return cuda_fail(h, e, "kernel launch");
+        launches += h->launches_last;
         CK(cudaEventRecord(h->ev_pool[3 * c], h->stream));
     }
     CK(cudaEventRecord(h->ev[3], h->stream));
@@ -272,28 +293,24 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     offsets[0] = 0;
     int err = DCEGM_OK;
     for (int c = 0; c < nchunks && err == DCEGM_OK; c++) {
-        const int c0 = c * chunk, cnt = (nmodels - c0 < chunk) ? nmodels - c0 : chunk;
+        const int c0 = cstart[c], cnt = ccount[c];
         const size_t nsl = per * cnt;
         CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * c], 0));
-        CK(cudaMemcpyAsync(h->pin_lens, B.lens + per * c0, sizeof(int32_t) * nsl, cudaMemcpyDeviceToHost, h->s_pack));
+        if (c >= 1) CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * (c - 1) + 1], 0));  // pack_off still read by pack c-1
+        cudaError_t e = launch_chunk_offsets(B.lens + per * c0, nsl, l.cap, (long long*)h->pack_off.p, pin_off_dev, h->s_pack);
+        if (e != cudaSuccess) return cuda_fail(h, e, "offsets kernel");
         CK(cudaStreamSynchronize(h->s_pack));
-        long long run_ = 0;
+        if (trace) fprintf(stderr, "[dcegm] %8.3f ms chunk %d solved, offsets on host\n", trace_ms(), c);
+        const long long run_ = h->pin_off[nsl];
         int64_t* go = offsets + per * c0;
-        for (size_t s = 0; s < nsl; s++) {
-            h->pin_off[s] = run_;
-            go[s] = base + run_;
-            run_ += h->pin_lens[s] < l.cap ? h->pin_lens[s] : l.cap;
-        }
-        h->pin_off[nsl] = run_;
-        go[nsl] = base + run_;
+        for (size_t s = 0; s <= nsl; s++) go[s] = base + h->pin_off[s];
         if ((size_t)(base + run_) > cap_points) {
             err = fail(h, DCEGM_E_CAPACITY, "dcegm_solve_*_packed: destination too small");
             break;
         }
         double2* buf = (double2*)((c & 1) ? h->pack_xy2.p : h->pack_xy.p);
-        CK(cudaMemcpyAsync(h->pack_off.p, h->pin_off, sizeof(long long) * (nsl + 1), cudaMemcpyHostToDevice, h->s_pack));
         if (c >= 2) CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * (c - 2) + 2], 0));  // buffer free again
-        cudaError_t e = launch_pack_lines(B, c0, cnt, (const long long*)h->pack_off.p, buf, h->s_pack);
+        e = launch_pack_lines(B, c0, cnt, (const long long*)h->pack_off.p, buf, h->s_pack);
         if (e != cudaSuccess) return cuda_fail(h, e, "pack kernel");
         CK(cudaEventRecord(h->ev_pool[3 * c + 1], h->s_pack));
         CK(cudaStreamWaitEvent(h->s_copy, h->ev_pool[3 * c + 1], 0));
@@ -303,9 +320,11 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     }
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaStreamSynchronize(h->s_pack));
+    if (trace) fprintf(stderr, "[dcegm] %8.3f ms all packed (%d chunks of %d)\n", trace_ms(), nchunks, chunk);
     CK(cudaStreamSynchronize(h->s_copy));
+    if (trace) fprintf(stderr, "[dcegm] %8.3f ms all copied: %.1f MB\n", trace_ms(), base * 16.0 / 1e6);
     CK(cudaEventElapsedTime(&h->timing.kernel_ms, h->ev[2], h->ev[3]));
-    h->timing.n_launches = (h->launches_last + 1) * nchunks;
+    h->timing.n_launches = launches + 2 * nchunks;
     h->solved = true;
     *npoints = base;
     return err;
@@ -412,7 +431,6 @@ int dcegm_destroy(dcegm_handle h) {
     for (auto& ev : h->ev)
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : h->ev_pool) cudaEventDestroy(ev);
-    if (h->pin_lens) cudaFreeHost(h->pin_lens);
     if (h->pin_off) cudaFreeHost(h->pin_off);
     if (h->s_pack) cudaStreamDestroy(h->s_pack);
     if (h->s_copy) cudaStreamDestroy(h->s_copy);

@@ -150,6 +150,63 @@ __global__ void pack_lines_kernel(const double2* __restrict__ lines, const long 
     for (long long k = threadIdx.x; k < o1 - o0; k += blockDim.x) dst[o0 + k] = src[k];
 }
 
+// exclusive prefix sum of min(lens, cap) over the nsl line slots of one chunk -> off[0..nsl] (device, read by
+// pack_lines_kernel) and the same numbers into host-mapped memory: the host learns the chunk's size and the
+// caller's offsets without a transfer that would queue behind the bulk device-to-host copies
+__global__ void __launch_bounds__(1024) chunk_offsets_kernel(const int32_t* __restrict__ lens, int nsl, int cap,
+                                                             long long* __restrict__ off, long long* __restrict__ off_host) {
+    __shared__ long long s_warp[32];
+    __shared__ long long s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (int b0 = 0; b0 < nsl; b0 += 1024) {
+        const int k = b0 + tid;
+        long long v = 0;
+        if (k < nsl) {
+            const int n = lens[k];
+            v = n < cap ? n : cap;
+        }
+        long long inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const long long t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_warp[wid] = inc;
+        __syncthreads();
+        if (wid == 0) {
+            long long w = s_warp[lane], wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const long long t = __shfl_up_sync(0xffffffffu, wi, o);
+                if (lane >= o) wi += t;
+            }
+            s_warp[lane] = wi - w;  // exclusive over warps
+        }
+        __syncthreads();
+        const long long carry = s_carry;
+        const long long excl = carry + s_warp[wid] + inc - v;
+        if (k < nsl) {
+            off[k] = excl;
+            off_host[k] = excl;
+        }
+        __syncthreads();
+        if (tid == 1023) s_carry = excl + v;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        off[nsl] = s_carry;
+        off_host[nsl] = s_carry;
+    }
+}
+
+cudaError_t launch_chunk_offsets(const int32_t* lens, size_t nsl, int cap, long long* d_off, long long* h_off_mapped,
+                                 cudaStream_t stream) {
+    chunk_offsets_kernel<<<1, 1024, 0, stream>>>(lens, (int)nsl, cap, d_off, h_off_mapped);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_pack_lines(const DeviceBatch& B, int first, int count, const long long* d_offsets, double2* d_dst,
                               cudaStream_t stream) {
     const size_t per = (size_t)B.lay.nT * B.lay.nstate * 4;
