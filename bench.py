@@ -31,14 +31,14 @@ NCU_DRAM_BYTES_PER_MODEL = 904.3e6 / 1184
 WORKLOAD = "C3: retirement model (FModel) batch, na=500, nT=25, ny=5, log10(lambda)~U(log10 2e-6, log10 0.2), sigma~U(0,0.6)"
 
 
-def c3_params(n, seed=25032020, offset=0):
+def c3_params(n, seed=25032020, offset=0, na=None):
     from dcegm_jl_b200 import Param
     from dcegm_jl_b200.param import params_array
 
     rng = np.random.default_rng(seed)
     lam = 10 ** rng.uniform(np.log10(2e-6), np.log10(0.2), size=offset + n)
     sig = rng.uniform(0, 0.6, size=offset + n)
-    base = Param(par=dict(na=NA, beta=0.95, R=1.05, nT=NT, ny=NY)).to_c()
+    base = Param(par=dict(na=na or NA, beta=0.95, R=1.05, nT=NT, ny=NY)).to_c()
     arr = params_array([base] * n)
     for i in range(n):
         arr[i].lambda_ = float(lam[offset + i])
@@ -148,6 +148,7 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--batch", type=int, default=BATCH, help="models per GPU")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--na", type=int, default=NA, help="savings grid points (experiments only; the metric is quoted at 500)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -170,7 +171,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     W = max(args.warmup, 3)
     nper = args.batch
-    arr = c3_params(nper, offset=rank * nper)  # contiguous shard of the global draw
+    arr = c3_params(nper, offset=rank * nper, na=args.na)  # contiguous shard of the global draw
     solver = Solver(local)
     lib, h = solver.lib, solver.h
 

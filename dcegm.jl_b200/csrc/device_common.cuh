@@ -17,6 +17,9 @@ namespace dcegm {
 #ifdef DC_T512
 constexpr int kThreads = 512;
 constexpr int kCtasPerSm = 1;
+#elif defined(DC_CTAS3)
+constexpr int kThreads = 256;
+constexpr int kCtasPerSm = 3;
 #else
 constexpr int kThreads = 256;
 constexpr int kCtasPerSm = 2;

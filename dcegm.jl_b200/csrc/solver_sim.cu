@@ -26,15 +26,17 @@ size_t sim_smem_bytes(const dcegm_layout& l) {
 }
 
 // vfun (dc_algo.jl:220-251) on the value line of period `it` (0-based)
+template <int Top>
 __device__ __forceinline__ double sim_vfun(bool worker_line, bool terminal, double c1, double m1, const double* vx,
                                            const double* vy, int n, double vb, const DevModel& p) {
     if (terminal && p.nu > 0) return p.nu * u_plain(c1 + p.bbar, p) - 0.0;  // bequest(c1,false,p)
     const bool mask = terminal || (m1 < vx[1]);
     if (mask) return u_work(c1, worker_line, p) + p.beta * vb;
-    return interp_y(vx, vy, n, m1);
+    return interp_y<Top>(vx, vy, n, m1);
 }
 
-template <int MODEL>
+// Top = largest step of the fixed-trip knot search: lines hold fewer than 2*Top points (chosen at launch from cap)
+template <int MODEL, int Top>
 __global__ void __launch_bounds__(kThreads) sim_kernel(DeviceBatch B, SimBatch Sb) {
     const int m = B.first + blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -111,16 +113,20 @@ __global__ void __launch_bounds__(kThreads) sim_kernel(DeviceBatch B, SimBatch S
                 lens[s] = n < cap ? n : cap;
             }
             for (int s = tid; s < nstate * 2; s += kThreads) vb[s] = B.vbound[((size_t)m * nT + it) * nstate * 2 + s];
-            for (int s = 0; s < nstate * 4; s++) {
-                const size_t slot = ((size_t)m * nT + it) * nstate * 4 + s;
-                const int n = min(B.lens[slot], cap);
-                const double2* src = B.lines + slot * (size_t)cap;
-                double* dx = ln + ((size_t)s * 2) * cap;
-                double* dy = dx + cap;
-                for (int k = tid; k < n; k += kThreads) {
-                    const double2 v = src[k];
-                    dx[k] = v.x;
-                    dy[k] = v.y;
+            {   // all (slot, point) pairs of the period in one flat loop: independent loads, no per-slot chain
+                const size_t slot0 = ((size_t)m * nT + it) * nstate * 4;
+                const double2* src0 = B.lines + slot0 * (size_t)cap;
+                const int32_t* len0 = B.lens + slot0;
+                const int total = nstate * 4 * cap;
+#pragma unroll 4
+                for (int idx = tid; idx < total; idx += kThreads) {
+                    const int s = idx / cap, k = idx - s * cap;
+                    if (k < len0[s]) {
+                        const double2 v = src0[idx];
+                        double* dx = ln + ((size_t)s * 2) * cap;
+                        dx[k] = v.x;
+                        dx[cap + k] = v.y;
+                    }
                 }
             }
             __syncthreads();
@@ -181,7 +187,7 @@ __global__ void __launch_bounds__(kThreads) sim_kernel(DeviceBatch B, SimBatch S
                 // ---- consumption, utility, end-of-period wealth (simulate.jl:106-110) ----
                 const int st = MODEL == DCEGM_MODEL_G ? ys[a] : 0;
                 const int id = wk ? 0 : 1;
-                const double cons = interp_y(line(st, id, 0, 0), line(st, id, 0, 1), lens[(st * 2 + id) * 2 + 0], w0);
+                const double cons = interp_y<Top>(line(st, id, 0, 0), line(st, id, 0, 1), lens[(st * 2 + id) * 2 + 0], w0);
                 const double util = u_work(cons, wk, p);
                 double w1n = w0 - cons;
                 if (MODEL == DCEGM_MODEL_F) w1n = w1n > a_hi ? a_hi : (w1n < a_lo ? a_lo : w1n);  // clamp!, simulate.jl:109
@@ -189,13 +195,16 @@ __global__ void __launch_bounds__(kThreads) sim_kernel(DeviceBatch B, SimBatch S
                 if (negc && MODEL == DCEGM_MODEL_F) flags |= DCEGM_ST_NEG_CONS;
                 // ---- probability to remain worker (simulate.jl:119-121) ----
                 const bool term = it == nT - 1;
-                const double v1 = sim_vfun(true, term, cons, w0, line(st, 0, 1, 0), line(st, 0, 1, 1), lens[(st * 2 + 0) * 2 + 1],
-                                           vb[st * 2 + 0], p);
-                const double v2 = sim_vfun(false, term, cons, w0, line(st, 1, 1, 0), line(st, 1, 1, 1), lens[(st * 2 + 1) * 2 + 1],
-                                           vb[st * 2 + 1], p);
-                const double mx = v1 > v2 ? v1 : v2;
-                const double e1 = dc_exp((v1 - mx) / p.lambda), e2 = dc_exp((v2 - mx) / p.lambda);
-                const double pw = wk ? e1 / (e1 + e2) : 0.0;
+                double pw = 0.0;  // retirees: simulate.jl:121 sets 0 whatever the values are
+                if (wk) {
+                    const double v1 = sim_vfun<Top>(true, term, cons, w0, line(st, 0, 1, 0), line(st, 0, 1, 1),
+                                                    lens[(st * 2 + 0) * 2 + 1], vb[st * 2 + 0], p);
+                    const double v2 = sim_vfun<Top>(false, term, cons, w0, line(st, 1, 1, 0), line(st, 1, 1, 1),
+                                                    lens[(st * 2 + 1) * 2 + 1], vb[st * 2 + 1], p);
+                    const double mx = v1 > v2 ? v1 : v2;
+                    const double e1 = dc_exp((v1 - mx) / p.lambda), e2 = dc_exp((v2 - mx) / p.lambda);
+                    pw = e1 / (e1 + e2);
+                }
                 // ---- next period's state (simulate.jl:124-127, 201) ----
                 const double ud = Sb.given ? Sb.dsh[at] : dc_sim_uniform(sp.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_D);
                 bool next = pw > ud;
@@ -261,16 +270,20 @@ cudaError_t launch_sim(const DeviceBatch& B0, const SimBatch& Sb, int first, int
     DeviceBatch B = B0;
     B.first = first;
     const size_t smem = sim_smem_bytes(B.lay);
-    cudaError_t e;
+    cudaError_t e = cudaSuccess;
+#define DC_SIM_LAUNCH(MODEL, TOP)                                                                                  \
+    do {                                                                                                           \
+        e = cudaFuncSetAttribute(sim_kernel<MODEL, TOP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        if (e != cudaSuccess) return e;                                                                            \
+        sim_kernel<MODEL, TOP><<<count, kThreads, smem, stream>>>(B, Sb);                                          \
+    } while (0)
+    const bool small = B.lay.cap < 256;  // na <= ~170: eight search steps instead of eleven
     if (B.lay.model == DCEGM_MODEL_F) {
-        e = cudaFuncSetAttribute(sim_kernel<DCEGM_MODEL_F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        sim_kernel<DCEGM_MODEL_F><<<count, kThreads, smem, stream>>>(B, Sb);
+        if (small) DC_SIM_LAUNCH(DCEGM_MODEL_F, 128); else DC_SIM_LAUNCH(DCEGM_MODEL_F, kSearchTop);
     } else {
-        e = cudaFuncSetAttribute(sim_kernel<DCEGM_MODEL_G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        sim_kernel<DCEGM_MODEL_G><<<count, kThreads, smem, stream>>>(B, Sb);
+        if (small) DC_SIM_LAUNCH(DCEGM_MODEL_G, 128); else DC_SIM_LAUNCH(DCEGM_MODEL_G, kSearchTop);
     }
+#undef DC_SIM_LAUNCH
     return cudaGetLastError();
 }
 
