@@ -28,6 +28,9 @@ ALGO_BYTES_PER_MODEL = 2 * 2 * 24 * 501 * 16 + 128 + 248
 # dram__bytes_read.sum + dram__bytes_write.sum of solve_f_kernel per model, from the `ncu --set full` capture
 # summarised in profiles/r1d_solve_f_ncu_summary.md (904.3 MB for 1184 models)
 NCU_DRAM_BYTES_PER_MODEL = 904.3e6 / 1184
+# sm__inst_executed_pipe_fp64.sum of solve_f_kernel per model (warp instructions), same capture series
+# (profiles/r1e_solve_f_metrics.csv: 977 324 011 for 1184 models)
+NCU_FP64_WARP_INST_PER_MODEL = 977324011 / 1184
 WORKLOAD = "C3: retirement model (FModel) batch, na=500, nT=25, ny=5, log10(lambda)~U(log10 2e-6, log10 0.2), sigma~U(0,0.6)"
 
 
@@ -60,7 +63,7 @@ class ClockSampler:
              "clocks_event_reasons.sw_power_cap")
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -213,7 +216,6 @@ def main():
     torch.cuda.synchronize()
     if dist:
         dist.barrier()
-    clocks = sampler.stop() if rank == 0 else None
     t = torch.tensor([tot_ms], dtype=torch.float64, device="cuda")
     if dist:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -256,18 +258,29 @@ def main():
         dist.barrier()
     t0 = time.perf_counter()
     d2h = 0
+    step_ms = []
     for _ in range(args.steps):
+        t1 = time.perf_counter()
         d2h = e2e_step()
+        step_ms.append((time.perf_counter() - t1) * 1e3)
     e2e_s = time.perf_counter() - t0
+    if os.environ.get("DCEGM_TRACE"):
+        print("e2e step wall ms:", [round(x, 2) for x in step_ms], file=sys.stderr)
     t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     if dist:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = solved * args.steps / float(t.item())
+    clocks = sampler.stop() if rank == 0 else None  # sampled over both timed regions (device-resident and e2e)
     lib.dcegm_host_free(pinned)
 
     if rank == 0:
         peak, peak_src = measured_peak()
         ms_kernel = kern_ms / args.steps
+        # FP64 issue rate of this GPU, measured now (independent DFMA chains at full occupancy)
+        dfma, dfma_ms = C.c_double(), C.c_double()
+        lib.dcegm_debug_dfma_rate(local, C.byref(dfma), C.byref(dfma_ms))
+        fp64_achieved = NCU_FP64_WARP_INST_PER_MODEL * nper / (ms_kernel * 1e-3) / 1e9
+        fp64_peak = dfma.value / 32 / 1e9
         achieved = ALGO_BYTES_PER_MODEL * nper / (ms_kernel * 1e-3) / 1e9  # bytes of one launch (rank 0) / its duration
         out = {
             "metric": "models solved/sec (500pts x 25T retirement model)", "value": value, "unit": "models/s",
@@ -280,11 +293,18 @@ def main():
                        "flagged_models_rank0": n_flagged, "models_counted": int(solved),
                        "flagged_note": "status != 0 (non-monotone line: Interpolations.jl would throw) -> not counted; the oracle flags the same models"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_DRAM_BYTES_PER_MODEL * nper, "traffic_source": "ncu --set full, profiles/r1d_solve_f_ncu_summary.md, bytes per launch scaled to this batch",
+                         "traffic": NCU_DRAM_BYTES_PER_MODEL * nper, "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum (profiles/r1d_solve_f_ncu_summary.md, r1e_solve_f_metrics.csv), bytes per launch scaled to this batch",
                          "peak_source": peak_src,
                          "note": "dominant kernel solve_f_kernel is FP64-pipe bound by construction (SURVEY.md §8d): "
                                  "~70 FP64 instr per algorithmic byte; HBM fraction reported as the metric asks"},
-            "e2e": {"value": e2e_value, "unit": "models/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+            "roofline_fp64": {"bound": "fp64 pipe", "achieved": fp64_achieved, "peak": fp64_peak, "unit": "G warp-inst/s",
+                              "frac": fp64_achieved / fp64_peak if fp64_peak > 0 else None,
+                              "peak_tflops": 2 * dfma.value / 1e12,
+                              "source": "achieved = FP64-pipe warp instructions per model (ncu sm__inst_executed_pipe_fp64.sum, "
+                                        "profiles/r1e_solve_f_metrics.csv) x models / kernel time; peak = dcegm_debug_dfma_rate measured in this run"},
+            "e2e": {"value": e2e_value, "unit": "models/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "d2h_gbs": d2h * args.steps / e2e_s / 1e9,
+                    "note": "bound by the device-to-host transfer of every stored polyline (pinned D2H measures ~57 GB/s on these boxes)"},
             "gpu_launches": args.steps * 1,
             "clocks": clocks,
         }
