@@ -29,8 +29,9 @@ for l in lines[start:]:
 print("sass rows", len(sass), "tagged", len(tags))
 REASONS = ["stall_wait", "stall_no_inst", "stall_barrier", "stall_short_sb", "stall_long_sb", "stall_math",
            "stall_branch_resolving", "stall_not_selected", "stall_selected"]
-agg = collections.defaultdict(lambda: [0] * (3 + len(REASONS)))
-tot = [0] * (3 + len(REASONS))
+NCOL = 3 + len(REASONS) + 2  # ... + thread instructions, predicated-on thread instructions
+agg = collections.defaultdict(lambda: [0] * NCOL)
+tot = [0] * NCOL
 
 
 def num(r, name):
@@ -39,13 +40,16 @@ def num(r, name):
 
 
 for r, t in zip(sass, tags):
-    vals = [num(r, "Instructions Executed"), num(r, "# Samples"), 1] + [num(r, k) for k in REASONS]
+    vals = ([num(r, "Instructions Executed"), num(r, "# Samples"), 1] + [num(r, k) for k in REASONS]
+            + [num(r, "Thread Instructions Executed"), num(r, "Predicated-On Thread Instructions Executed")])
     for i, v in enumerate(vals):
         agg[t][i] += v
         tot[i] += v
 print("total inst", tot[0], "samples", tot[1])
 print("stall mix: " + "  ".join(f"{k[6:]} {100 * tot[3 + i] / tot[1]:.1f}%" for i, k in enumerate(REASONS)))
-byfile = collections.defaultdict(lambda: [0] * (3 + len(REASONS)))
+print(f"warp divergence: {tot[-2] / max(tot[0], 1):.2f} active threads per warp instruction, "
+      f"{tot[-1] / max(tot[0], 1):.2f} predicated-on")
+byfile = collections.defaultdict(lambda: [0] * NCOL)
 for (f, ln), v in agg.items():
     for i in range(len(v)):
         byfile[f][i] += v[i]
@@ -55,6 +59,7 @@ def fmt(v):
     s = f"inst {100 * v[0] / tot[0]:5.2f}%  samples {100 * v[1] / tot[1]:5.2f}%  sass {v[2]:5d} |"
     for i, k in enumerate(REASONS[:6]):
         s += f" {k[6:]} {100 * v[3 + i] / max(v[1], 1):4.0f}%"
+    s += f" | thr/inst {v[-2] / max(v[0], 1):4.1f} on {v[-1] / max(v[0], 1):4.1f}"
     return s
 
 
