@@ -353,12 +353,15 @@ __global__ void __launch_bounds__(kEnvThreads) big_env_kernel(DeviceBatch B, uns
     BIG_CLK_BEGIN();
     __shared__ DevModel s_p;
     __shared__ int s_n[2];
-    __shared__ int s_status;
+    __shared__ int s_status, s_now;  // status word of the model so far; bits raised by this period's lines
     if (tid == 0) s_p = B.models[m];
     const BigPlan P(B.lay.cap, B.lay.isec_cap);
     unsigned char* g = scratch + (size_t)blockIdx.x * stride;
     BigState* st = P.state(g);
-    if (tid == 0) s_status = st->status;
+    if (tid == 0) {
+        s_status = st->status;
+        s_now = 0;
+    }
     __syncthreads();
     const DevModel& p = s_p;
     const int na = p.na;
@@ -407,8 +410,14 @@ __global__ void __launch_bounds__(kEnvThreads) big_env_kernel(DeviceBatch B, uns
         if (k + 1 < na + 1 && !(C.r_x()[k + 1] > C.r_x()[k])) flag |= DCEGM_ST_NONMONOTONE;
         if (!isfinite(C.r_x()[k]) || !isfinite(C.rc_y()[k]) || !isfinite(C.rv_y()[k])) flag |= DCEGM_ST_NONFINITE;
     }
-    if (flag) atomicOr(&s_status, flag);
-    if (tid == 0 && S.cnt()[2]) atomicOr(&s_status, S.cnt()[2]);
+    if (flag) {
+        atomicOr(&s_status, flag);
+        atomicOr(&s_now, flag);
+    }
+    if (tid == 0 && S.cnt()[2]) {
+        atomicOr(&s_status, S.cnt()[2]);
+        atomicOr(&s_now, S.cnt()[2]);
+    }
 
     store_line<kEnvThreads>(B, m, t, 0, 0, DCEGM_KIND_C, C.wc_x(), C.wc_y(), C.n_wc);
     store_line<kEnvThreads>(B, m, t, 0, 0, DCEGM_KIND_V, C.wv_x(), C.wv_y(), C.n_wv);
@@ -437,7 +446,10 @@ __global__ void __launch_bounds__(kEnvThreads) big_env_kernel(DeviceBatch B, uns
     }
     DC_CLK(13);
     if (t > 0) {
-        big_build_index<kEnvThreads>(P, g, st, C, status);
+        // The bucket index (and with it the straight-line EGM node) needs THIS period's lines strictly increasing and
+        // finite; a model flagged in an earlier period uses it again as soon as its lines are regular (both node
+        // paths give the same bits on regular lines).
+        big_build_index<kEnvThreads>(P, g, st, C, s_now);
         BIG_CLK_END();
         return;
     }
