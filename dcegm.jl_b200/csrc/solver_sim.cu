@@ -201,12 +201,16 @@ __global__ void __launch_bounds__(kThreads) sim_kernel(DeviceBatch B, SimBatch S
                                                     lens[(st * 2 + 0) * 2 + 1], vb[st * 2 + 0], p);
                     const double v2 = sim_vfun<Top>(false, term, cons, w0, line(st, 1, 1, 0), line(st, 1, 1, 1),
                                                     lens[(st * 2 + 1) * 2 + 1], vb[st * 2 + 1], p);
-                    const double mx = v1 > v2 ? v1 : v2;
-                    const double e1 = dc_exp((v1 - mx) / p.lambda), e2 = dc_exp((v2 - mx) / p.lambda);
+                    // the larger value's exponential is exp(0) = 1 exactly: one dc_exp instead of two
+                    const bool w_hi = v1 > v2;
+                    const double mx = w_hi ? v1 : v2;
+                    const double e = dc_exp(((w_hi ? v2 : v1) - mx) / p.lambda);
+                    const double e1 = w_hi ? 1.0 : e, e2 = w_hi ? e : 1.0;
                     pw = e1 / (e1 + e2);
                 }
                 // ---- next period's state (simulate.jl:124-127, 201) ----
-                const double ud = Sb.given ? Sb.dsh[at] : dc_sim_uniform(sp.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_D);
+                // a retiree's draw cannot matter (pw = 0 is never above a uniform in [0,1)): no Philox call for it
+                const double ud = Sb.given ? Sb.dsh[at] : (wk ? dc_sim_uniform(sp.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_D) : 1.0);
                 bool next = pw > ud;
                 if (MODEL == DCEGM_MODEL_F && !wk) {
                     const double ur = Sb.given ? (Sb.rsh ? Sb.rsh[at] : 1.0) : dc_sim_uniform(sp.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_R);
