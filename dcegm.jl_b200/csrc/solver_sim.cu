@@ -19,7 +19,8 @@ constexpr int kSimTile = kThreads * kSimAgents;  // agents per tile
 
 size_t sim_smem_bytes(const dcegm_layout& l) {
     const size_t lines = (size_t)l.nstate * 8 * l.cap * sizeof(double);
-    const size_t tabs = ((size_t)l.ny * l.ny + (size_t)l.nT * l.ny + (size_t)l.nT * DCEGM_SIM_NMOM + kWarps * DCEGM_SIM_NMOM +
+    const size_t tabs = ((size_t)l.ny * l.ny + (size_t)l.nT * l.ny + (size_t)l.nT * DCEGM_SIM_NMOM +
+                         (size_t)l.nT * kWarps * DCEGM_SIM_NMOM +
                          (size_t)l.nstate * 2) * sizeof(double);
     const size_t ints = ((size_t)l.nT + 1 + (size_t)l.nstate * 4 + 4) * sizeof(int);
     return lines + tabs + ints + 64;
@@ -60,8 +61,8 @@ __global__ void __launch_bounds__(kThreads) sim_kernel(DeviceBatch B, SimBatch S
     double* gg = ln + (size_t)nstate * 8 * cap;                      // [ny][ny] cumulative transition rows
     double* inctab = gg + ny * ny;                                   // [nT][ny] income(it+1, yvec)
     double* mom = inctab + nT * ny;                                  // [nT][NMOM]
-    double* red = mom + nT * DCEGM_SIM_NMOM;                         // [kWarps][NMOM]
-    double* vb = red + kWarps * DCEGM_SIM_NMOM;                      // [nstate][2]
+    double* red = mom + nT * DCEGM_SIM_NMOM;                         // [nT][kWarps][NMOM] warp sums of the current tile
+    double* vb = red + nT * kWarps * DCEGM_SIM_NMOM;                 // [nstate][2]
     int* hist = reinterpret_cast<int*>(vb + nstate * 2);             // [nT+1]
     int* lens = hist + nT + 1;                                       // [nstate][id][kind]
     auto line = [&](int st, int id, int kind, int xy) { return ln + ((((size_t)st * 2 + id) * 2 + kind) * 2 + xy) * cap; };
@@ -239,20 +240,21 @@ __global__ void __launch_bounds__(kThreads) sim_kernel(DeviceBatch B, SimBatch S
                 }
             }
             if (flags) atomicOr(&s_status, flags);
-            // ---- tile sums: shuffle tree, warps ascending, added to the running per-period sums ----
+            // ---- tile sums: shuffle tree per warp now; the warps are added up (ascending) once per tile ----
 #pragma unroll
             for (int k = 0; k < DCEGM_SIM_NMOM; k++) {
                 double v = sum[k];
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-                if (lane == 0) red[wid * DCEGM_SIM_NMOM + k] = v;
+                if (lane == 0) red[(it * kWarps + wid) * DCEGM_SIM_NMOM + k] = v;
             }
-            __syncthreads();
-            if (tid < DCEGM_SIM_NMOM) {
-                double t = red[tid];
-                for (int w = 1; w < kWarps; w++) t += red[w * DCEGM_SIM_NMOM + tid];
-                mom[it * DCEGM_SIM_NMOM + tid] = tile0 == 0 ? t : mom[it * DCEGM_SIM_NMOM + tid] + t;
-            }
+        }
+        __syncthreads();
+        for (int q = tid; q < nT * DCEGM_SIM_NMOM; q += kThreads) {
+            const int it = q / DCEGM_SIM_NMOM, k = q - it * DCEGM_SIM_NMOM;
+            double t = red[(it * kWarps) * DCEGM_SIM_NMOM + k];
+            for (int w = 1; w < kWarps; w++) t += red[(it * kWarps + w) * DCEGM_SIM_NMOM + k];
+            mom[q] = tile0 == 0 ? t : mom[q] + t;
         }
 #pragma unroll
         for (int a = 0; a < kSimAgents; a++) {
