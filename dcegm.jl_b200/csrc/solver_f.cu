@@ -12,6 +12,8 @@
 //   3. credit-constraint point, checks, store.
 #include <math_constants.h>
 
+#define DC_OUTLINE_MATH  // dc_math.h: out-of-line log/exp cores (instruction-cache footprint of the hot loop)
+
 #include "device_common.cuh"
 #include "egm_node.cuh"
 #include "envelope.cuh"

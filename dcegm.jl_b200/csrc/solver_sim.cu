@@ -8,6 +8,8 @@
 // Per-period sums are reduced tile by tile in a fixed order (the CPU oracle reproduces it).
 #include <math_constants.h>
 
+#define DC_OUTLINE_MATH  // dc_math.h: out-of-line log/exp cores (instruction-cache footprint of the hot loop)
+
 #include "dc_rng.h"
 #include "device_common.cuh"
 
@@ -38,7 +40,7 @@ __device__ __forceinline__ double sim_vfun(bool worker_line, bool terminal, doub
 
 // Top = largest step of the fixed-trip knot search: lines hold fewer than 2*Top points (chosen at launch from cap)
 template <int MODEL, int Top>
-__global__ void __launch_bounds__(kThreads) sim_kernel(DeviceBatch B, SimBatch Sb) {
+__global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatch Sb) {
     const int m = B.first + blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     __shared__ DevModel s_p;
