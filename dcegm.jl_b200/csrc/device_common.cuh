@@ -226,9 +226,12 @@ __device__ __forceinline__ void knot_index_build_step_at(unsigned short* T, cons
                                                           int n, int nb, int k) {
     const int bk = knot_bucket(K, x[k]);
     const int bp = k == 0 ? -1 : knot_bucket(K, x[k - 1]);
+#pragma unroll 1
     for (int b = bp + 1; b <= bk; b++) T[b] = (unsigned short)k;
-    if (k == n - 1)
+    if (k == n - 1) {
+#pragma unroll 1
         for (int b = bk + 1; b <= nb; b++) T[b] = (unsigned short)n;
+    }
 }
 __device__ __forceinline__ void knot_index_build_step(const KnotIndex& K, const double* __restrict__ x, int n, int nb, int k) {
     knot_index_build_step_at(reinterpret_cast<unsigned short*>(dc_smem + K.tab), K, x, n, nb, k);
@@ -301,6 +304,7 @@ __device__ inline int block_scan_excl(int* data, int n, int* red) {
     const int per = (n + NT - 1) / NT;
     const int b = tid * per;
     int local = 0;
+#pragma unroll (NT > 256 ? 4 : 1)
     for (int i = 0; i < per; i++) {
         int k = b + i;
         if (k < n) local += data[k];
@@ -327,6 +331,7 @@ __device__ inline int block_scan_excl(int* data, int n, int* red) {
     __syncthreads();
     int run = red[wid] + inc - local;
     const int total = red[(NT / 32)];
+#pragma unroll (NT > 256 ? 4 : 1)
     for (int i = 0; i < per; i++) {
         int k = b + i;
         if (k < n) {

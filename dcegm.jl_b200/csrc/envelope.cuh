@@ -19,6 +19,23 @@
 
 namespace dcegm {
 
+// Block-strided loops of worker_envelope: kept rolled where the scratch is shared memory (the unrolled copies of ~40
+// loops made the envelope 69 KB of code that every CTA streams through the instruction cache once per period),
+// unrolled by four on long lines in global memory (independent loads in flight).
+#ifndef DC_ENV_ROLLED
+#define DC_ENV_ROLLED 1
+#endif
+#if DC_ENV_ROLLED
+#define DC_ENV_UNROLL _Pragma("unroll (ES::kLongLines ? 4 : 1)")
+#else
+#define DC_ENV_UNROLL
+#endif
+// seg_interp_y: inline by default; solve_g_kernel (five envelopes per period, code footprint matters more than the
+// call) compiles it out of line.  Measured: F 218.5 k vs 212.0 k models/s inline vs not, G 101.2 vs 98.1 ms.
+#ifndef DC_SEG_INTERP_ATTR
+#define DC_SEG_INTERP_ATTR __device__ __forceinline__
+#endif
+
 // All scratch of the envelope lives in the kernel's dynamic shared memory (dc_smem, declared in
 // device_common.cuh) and is addressed as integer offsets from that one symbol.
 
@@ -100,7 +117,7 @@ __device__ __forceinline__ int seg_count_le(const SegView& v, double q) {
     return lo;
 }
 // interp(L[s],[q]) with extrap=true (line.jl:220-254), y only
-__device__ __forceinline__ double seg_interp_y(const SegView& v, double q) {
+DC_SEG_INTERP_ATTR double seg_interp_y(const SegView& v, double q) {
     const int n = v.len;
     if (q < seg_x(v, 0)) {
         double d = seg_x(v, 1) - seg_x(v, 0);
@@ -220,6 +237,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
 
     // ---- bend-back guard (dc_algo.jl:394-418) ------------------------------------------------
     double mn = CUDART_INF;
+    DC_ENV_UNROLL
     for (int k = tid; k < na; k += NT) mn = fmin(mn, S.Dx()[koff + k]);
     const double minx = block_min<NT>(mn, S.redd());
     const double first = S.Dx()[koff];
@@ -227,6 +245,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
     if (!(first <= minx)) {
         npre = koff;  // floor(na/10) - 1 points
         const int klen = na / 10;
+        DC_ENV_UNROLL
         for (int i = tid; i < npre; i += NT) {
             double x0 = dc_linrange_at(minx, first, klen, i);
             double c0 = x0;
@@ -250,6 +269,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
     __syncthreads();
 
     // ---- splitLine: direction changes (envelope.jl:84-110) -----------------------------------
+    DC_ENV_UNROLL
     for (int k = tid; k < n; k += NT) {
         int isb = 0;
         if (k >= 1 && k <= n - 2) isb = (X[k] > X[k - 1]) != (X[k + 1] > X[k]);
@@ -274,6 +294,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
 
     int ne = 0, nis = 0, nrem = 0;
     if (plain) {
+        DC_ENV_UNROLL
         for (int k = tid; k < n; k += NT) {
             Vx[1 + k] = X[k];
             Vy[1 + k] = V[k];
@@ -281,6 +302,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         }
         ne = n;
     } else {
+        DC_ENV_UNROLL
         for (int k = tid; k < n; k += NT)
             if (S.fknot()[k]) S.segb()[S.scan()[k] + 1] = k;
         if (tid == 0) {
@@ -288,7 +310,9 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             S.segb()[nseg] = n - 1;
         }
         __syncthreads();
+        DC_ENV_UNROLL
         for (int s = tid; s < nseg; s += NT) S.segrise()[s] = X[S.segb()[s] + 1] > X[S.segb()[s]];
+        DC_ENV_UNROLL
         for (int k = tid; k < n; k += NT) S.order()[k] = 0;
         __syncthreads();
 
@@ -307,6 +331,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         __shared__ int g_own[kGroups];
         const int ntile = kStage ? (nseg < kSegTile ? nseg : kSegTile) : 0;
         if (kStage) {
+            DC_ENV_UNROLL
             for (int s = tid; s < ntile; s += NT) {
                 const int e0 = S.segb()[s], e1 = S.segb()[s + 1];
                 const double xa = X[e0], xb = X[e1];
@@ -330,6 +355,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             }
             __syncthreads();
         }
+        DC_ENV_UNROLL
         for (int k = tid; k < n; k += NT) {
             const double xk = X[k];
             int rank = 0, ties = 0, w = -1;
@@ -414,9 +440,11 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         }
         __syncthreads();
         DC_CLK(6);
+        DC_ENV_UNROLL
         for (int k = tid; k < n; k += NT) S.order()[S.pos()[k]] = (unsigned short)k;
         __syncthreads();
         // unique(xx)
+        DC_ENV_UNROLL
         for (int q = tid; q < n; q += NT) {
             int uq = (q == 0) || (X[S.order()[q]] != X[S.order()[q - 1]]);
             S.fuq()[q] = (unsigned char)uq;
@@ -424,8 +452,10 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         }
         __syncthreads();
         const int nu = block_scan_excl<NT>(S.scan(), n, S.red());
+        DC_ENV_UNROLL
         for (int q = tid; q < n; q += NT)
             if (S.fuq()[q]) S.ord2()[S.scan()[q]] = S.order()[q];
+        DC_ENV_UNROLL
         for (int k = tid; k < n; k += NT) {
             int q = S.pos()[k];
             S.pos()[k] = (unsigned short)(S.fuq()[q] ? S.scan()[q] : S.scan()[q] - 1);  // index into the unique grid
@@ -434,6 +464,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
 
         DC_CLK(7);
         // ---- changes of winner (envelope.jl:173-243) ---------------------------------------------
+        DC_ENV_UNROLL
         for (int j = tid; j < nu; j += NT) {
             S.cntI()[j] = 0;
             if (j >= 1 && S.win()[S.ord2()[j]] != S.win()[S.ord2()[j - 1]]) {
@@ -469,6 +500,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             nis = S.isec_cap;
         }
         // intersections in emission order (ascending cell, then order of discovery)
+        DC_ENV_UNROLL
         for (int t = tid; t < nis; t += NT) {
             int key = S.islkey()[t], r = 0;
             for (int u = 0; u < nis; u++) r += S.islkey()[u] < key;
@@ -477,6 +509,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             S.isl2key()[r] = key;
         }
         // ---- emission (envelope.jl:170, 212, 248-252) ----------------------------------------------
+        DC_ENV_UNROLL
         for (int j = tid; j < nu; j += NT) {
             int k = S.ord2()[j];
             int reg = (j == 0) || S.fknot()[k] || (j == nu - 1);
@@ -486,6 +519,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         ne = block_scan_excl<NT>(S.scan(), nu, S.red());
         const int room = S.cap - 1;
         if (ne > room) status |= DCEGM_ST_LINE_OVERFLOW;
+        DC_ENV_UNROLL
         for (int j = tid; j < nu; j += NT) {
             int k = S.ord2()[j];
             int reg = (j == 0) || S.fknot()[k] || (j == nu - 1);
@@ -495,6 +529,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 Vy[1 + at] = S.Ty()[k];
             }
         }
+        DC_ENV_UNROLL
         for (int t = tid; t < nis; t += NT) {
             int key = S.isl2key()[t];
             int at = S.scan()[key / kSwitchMaxIsect] + key % kSwitchMaxIsect;
@@ -505,6 +540,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         }
         if (ne > room) ne = room;
         // ---- removed! (envelope.jl:64-71): points with no exactly equal Point in the envelope ------
+        DC_ENV_UNROLL
         for (int k = tid; k < n; k += NT) {
             int j = S.pos()[k];
             bool reg = (j == 0) || S.fknot()[k] || (j == nu - 1);
@@ -517,6 +553,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
     DC_CLK(9);
     {
         int local = 0;
+        DC_ENV_UNROLL
         for (int k = tid; k < n; k += NT) local += S.frem()[k];
         nrem = block_sum<NT>(local, S.red());
     }
@@ -527,6 +564,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         unsigned word = __ballot_sync(0xffffffffu, bit);
         if ((tid & 31) == 0 && k / 32 < rem_words) removed_out[k / 32] = word;
     }
+    DC_ENV_UNROLL
     for (int t = tid; t < S.isec_cap; t += NT)
         isects_out[t] = t < nis ? make_double2(S.isl2x()[t], S.isl2y()[t]) : make_double2(0.0, 0.0);
 
@@ -571,6 +609,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             }
         }
         // deleteat!(cout, rmidx)  (dc_algo.jl:482)
+        DC_ENV_UNROLL
         for (int k = tid; k < n; k += NT) S.scan()[k] = S.frem()[k] ? 0 : 1;
         __syncthreads();
         // compact the two insertion lists (push! order)
@@ -592,6 +631,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             S.cnt()[1] = nr;
         }
         ncur = block_scan_excl<NT>(S.scan(), n, S.red());
+        DC_ENV_UNROLL
         for (int k = tid; k < n; k += NT)
             if (!S.frem()[k]) {
                 Cx[1 + S.scan()[k]] = X[k];
@@ -609,7 +649,9 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         constexpr bool kTryMerge = ES::kLongLines;  // at ~500 points the sequential path is as fast (measured)
         if (kTryMerge && nl > 0 && nl == nr && ncur + 2 * nl <= S.cap - 1) {
             int irregular = 0;
+            DC_ENV_UNROLL
             for (int k = tid; k + 1 < ncur; k += NT) irregular |= Cx[1 + k + 1] < Cx[1 + k];
+            DC_ENV_UNROLL
             for (int i = tid; i < nl; i += NT) {
                 const double lx = S.insLx()[i];
                 int lo = 0, len = ncur;  // #{base x <= lx}
@@ -630,6 +672,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             merged = block_sum<NT>(irregular, S.red()) == 0;
         }
         if (merged) {
+            DC_ENV_UNROLL
             for (int k = tid; k < ncur; k += NT) {
                 int lo = 0, len = nl;  // pairs in front of base point k: #{q_i <= k}
                 while (len > 0) {
@@ -641,6 +684,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 S.Dx()[k + 2 * lo] = Cx[1 + k];
                 S.Dv()[k + 2 * lo] = Cy[1 + k];
             }
+            DC_ENV_UNROLL
             for (int i = tid; i < nl; i += NT) {
                 const int at = S.islkey()[i] + 2 * i;
                 S.Dx()[at] = S.insLx()[i];
@@ -650,6 +694,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             }
             __syncthreads();
             ncur += 2 * nl;
+            DC_ENV_UNROLL
             for (int k = tid; k < ncur; k += NT) {
                 Cx[1 + k] = S.Dx()[k];
                 Cy[1 + k] = S.Dv()[k];
@@ -659,6 +704,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         for (int i = 0; i < nl && !merged; i++) {
             const double lx = S.insLx()[i];
             int cand = 0x7fffffff;
+            DC_ENV_UNROLL
             for (int k = tid; k < ncur; k += NT)
                 if (Cx[1 + k] > lx) {
                     cand = k;
@@ -698,6 +744,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             __syncthreads();
         }
     } else {
+        DC_ENV_UNROLL
         for (int k = tid; k < n; k += NT) {
             Cx[1 + k] = X[k];
             Cy[1 + k] = Cc[k];
@@ -718,6 +765,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
     // sortx!(c): stable sort on x.  The repaired policy is already ascending except in degenerate
     // cases; detect, and only then rank-sort through the (now free) D arrays.
     int bad = 0;
+    DC_ENV_UNROLL
     for (int k = tid; k + 1 < lenC; k += NT) bad |= Cx[k + 1] < Cx[k];
     bad = block_sum<NT>(bad, S.red());
     if (bad && ES::kLongLines) {
@@ -725,18 +773,22 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         // bottom-up; every element finds its place in the merged pair with one binary search in the sibling
         // run (left-run elements go before equal right-run elements).  Ping-pong with the free D arrays;
         // run boundaries in segb (room for cap + 1 entries in this variant), scan as temporary.
+        DC_ENV_UNROLL
         for (int k = tid; k < lenC; k += NT) S.scan()[k] = (k == 0) || (Cx[k] < Cx[k - 1]);
         __syncthreads();
+        DC_ENV_UNROLL
         for (int k = tid; k < lenC; k += NT) S.fuq()[k] = (unsigned char)S.scan()[k];
         __syncthreads();
         int nr = block_scan_excl<NT>(S.scan(), lenC, S.red());
         int* rb = S.segb();
+        DC_ENV_UNROLL
         for (int k = tid; k < lenC; k += NT)
             if (S.fuq()[k]) rb[S.scan()[k]] = k;
         if (tid == 0) rb[nr] = lenC;
         __syncthreads();
         double *sx = Cx, *sy = Cy, *dx = S.Dx(), *dy = S.Dv();
         while (nr > 1) {
+            DC_ENV_UNROLL
             for (int k = tid; k < lenC; k += NT) {
                 int lo = 0, len = nr;  // run containing k: last boundary <= k
                 while (len > 0) {
@@ -775,8 +827,10 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 dy[out] = sy[k];
             }
             const int nr2 = (nr + 1) >> 1;
+            DC_ENV_UNROLL
             for (int i = tid; i < nr2; i += NT) S.scan()[i] = rb[2 * i];
             __syncthreads();
+            DC_ENV_UNROLL
             for (int i = tid; i < nr2; i += NT) rb[i] = S.scan()[i];
             if (tid == 0) rb[nr2] = lenC;
             __syncthreads();
@@ -785,6 +839,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             t = sy; sy = dy; dy = t;
         }
         if (sx != Cx) {
+            DC_ENV_UNROLL
             for (int k = tid; k < lenC; k += NT) {
                 Cx[k] = sx[k];
                 Cy[k] = sy[k];
@@ -792,6 +847,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             __syncthreads();
         }
     } else if (bad) {
+        DC_ENV_UNROLL
         for (int k = tid; k < lenC; k += NT) {
             const double xk = Cx[k];
             int r = 0;
@@ -803,6 +859,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             S.Dv()[r] = Cy[k];
         }
         __syncthreads();
+        DC_ENV_UNROLL
         for (int k = tid; k < lenC; k += NT) {
             Cx[k] = S.Dx()[k];
             Cy[k] = S.Dv()[k];
@@ -811,10 +868,12 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
     }
     // status: knot vectors the next period's interpolate() would reject, non-finite entries
     int flag = 0;
+    DC_ENV_UNROLL
     for (int k = tid; k < lenC; k += NT) {
         if (k + 1 < lenC && !(Cx[k + 1] > Cx[k])) flag |= DCEGM_ST_NONMONOTONE;
         if (!isfinite(Cx[k]) || !isfinite(Cy[k])) flag |= DCEGM_ST_NONFINITE;
     }
+    DC_ENV_UNROLL
     for (int k = tid; k < lenV; k += NT) {
         if (k + 1 < lenV && !(Vx[k + 1] > Vx[k])) flag |= DCEGM_ST_NONMONOTONE;
         if (!isfinite(Vx[k]) || !isfinite(Vy[k])) flag |= DCEGM_ST_NONFINITE;

@@ -12,6 +12,7 @@
 //   C. per iy: worker envelope + policy repair (envelope.cuh), credit-constraint point, store.
 #include <math_constants.h>
 
+#define DC_SEG_INTERP_ATTR static __device__ __noinline__  // envelope.cuh
 #include "device_common.cuh"
 #include "envelope.cuh"
 
