@@ -68,6 +68,8 @@ __device__ inline void store_line_g(const DeviceBatch& B, int m, int it, int iy,
     for (int k = threadIdx.x; k < nn; k += kThreads) dst[k] = make_double2(x[k], y[k]);
 }
 
+// Top = largest step of the fixed-trip knot search (lines hold fewer than 2*Top points; chosen at launch from cap)
+template <int Top>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBatch B) {
     const int m = B.first + blockIdx.x;
     const int tid = threadIdx.x;
@@ -160,18 +162,18 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBat
                 if (iid == 0) {
                     const double* cx = P.line(jy, 0); const double* cy = P.line(jy, 1);
                     const int ncw = P.len(jy)[0];
-                    c1 = interp_y(cx, cy, ncw, m1);
+                    c1 = interp_y<Top>(cx, cy, ncw, m1);
                     c1 = c1 < p.cfloor ? p.cfloor : c1;
                     if (next_terminal && p.nu > 0)
                         v1 = p.nu * u_plain(c1 + p.bbar, p) - 0.0;
                     else if (next_terminal || m1 < P.line(jy, 2)[1])
                         v1 = u_work(c1, true, p) + p.beta * P.vb(jy)[0];
                     else
-                        v1 = interp_y(P.line(jy, 2), P.line(jy, 3), P.len(jy)[1], m1);
+                        v1 = interp_y<Top>(P.line(jy, 2), P.line(jy, 3), P.len(jy)[1], m1);
                 } else {
                     const double* rx = P.line(jy, 4);
                     const int nr = P.len(jy)[2];
-                    const int ir = left_knot(rx, nr, m1);
+                    const int ir = left_knot<Top>(rx, nr, m1);
                     c1 = interp_at(rx, P.line(jy, 5), nr, ir, m1);
                     c1 = c1 < p.cfloor ? p.cfloor : c1;
                     if (next_terminal && p.nu > 0)
@@ -331,13 +333,14 @@ cudaError_t launch_solve_g(const DeviceBatch& B0, int first, int count, cudaStre
     DeviceBatch B = B0;
     B.first = first;
     const size_t smem = GPlan(B.lay.cap, B.lay.isec_cap, B.lay.na, B.lay.ny).bytes();
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(solve_g_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
-    }
-    solve_g_kernel<<<count, kThreads, smem, stream>>>(B);
+    const bool small = B.lay.cap < 256;  // na <= ~170: eight search steps instead of eleven
+    cudaError_t e = small ? cudaFuncSetAttribute(solve_g_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                          : cudaFuncSetAttribute(solve_g_kernel<kSearchTop>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    if (small)
+        solve_g_kernel<128><<<count, kThreads, smem, stream>>>(B);
+    else
+        solve_g_kernel<kSearchTop><<<count, kThreads, smem, stream>>>(B);
     return cudaGetLastError();
 }
 
