@@ -236,6 +236,85 @@ __device__ __forceinline__ void knot_index_build_step_at(unsigned short* T, cons
 __device__ __forceinline__ void knot_index_build_step(const KnotIndex& K, const double* __restrict__ x, int n, int nb, int k) {
     knot_index_build_step_at(reinterpret_cast<unsigned short*>(dc_smem + K.tab), K, x, n, nb, k);
 }
+// Block-level build of the tables of three lines at once, balanced whatever the spacing of the knots (the
+// per-knot scheme above lets the thread that owns a knot behind a wide gap fill all the gap's buckets alone —
+// 8 % of solve_f_kernel's time was spent waiting for it at the next barrier):
+//   1. T[b] = n;  2. the first knot of every non-empty bucket writes its index;  3. suffix-minimum over the
+// buckets (thread-local pass, warp shuffles, one exchange across warps) fills the empty ones.
+// Gives T[b] = first knot whose bucket is >= b, the same table as knot_index_build_step.  All NT threads call it;
+// the tables are valid after it returns.
+template <int NT>
+__device__ inline void knot_index_build3(unsigned short* T0, unsigned short* T1, unsigned short* T2, const KnotIndex& K0,
+                                         const KnotIndex& K1, const KnotIndex& K2, const double* __restrict__ x0, int n0,
+                                         const double* __restrict__ x1, int n1, const double* __restrict__ x2, int n2,
+                                         int nb) {
+    constexpr int NW = NT / 32;
+    __shared__ int s_kmin[3][NW];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    for (int b = tid; b <= nb; b += NT) {
+        T0[b] = (unsigned short)n0;
+        T1[b] = (unsigned short)n1;
+        T2[b] = (unsigned short)n2;
+    }
+    __syncthreads();
+    const int nmax = max(n0, max(n1, n2));
+    for (int k = tid; k < nmax; k += NT) {
+        if (k < n0) {
+            const int bk = knot_bucket(K0, x0[k]);
+            if (k == 0 || knot_bucket(K0, x0[k - 1]) != bk) T0[bk] = (unsigned short)k;
+        }
+        if (k < n1) {
+            const int bk = knot_bucket(K1, x1[k]);
+            if (k == 0 || knot_bucket(K1, x1[k - 1]) != bk) T1[bk] = (unsigned short)k;
+        }
+        if (k < n2) {
+            const int bk = knot_bucket(K2, x2[k]);
+            if (k == 0 || knot_bucket(K2, x2[k - 1]) != bk) T2[bk] = (unsigned short)k;
+        }
+    }
+    __syncthreads();
+    const int per = (nb + NT) / NT;  // entries 0..nb, `per` consecutive ones per thread
+    const int b0 = tid * per;
+    int mine[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff};
+    for (int i = 0; i < per; i++) {
+        const int b = b0 + i;
+        if (b <= nb) {
+            mine[0] = min(mine[0], (int)T0[b]);
+            mine[1] = min(mine[1], (int)T1[b]);
+            mine[2] = min(mine[2], (int)T2[b]);
+        }
+    }
+    int carry[3];
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+        int v = mine[j];  // inclusive suffix minimum over the lanes of the warp
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_down_sync(0xffffffffu, v, o);
+            if (lane + o < 32) v = min(v, t);
+        }
+        if (lane == 0) s_kmin[j][wid] = v;
+        const int nxt = __shfl_down_sync(0xffffffffu, v, 1);
+        carry[j] = lane < 31 ? nxt : 0x7fffffff;  // minimum over the later lanes
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 3; j++)
+        for (int w = wid + 1; w < NW; w++) carry[j] = min(carry[j], s_kmin[j][w]);
+    for (int i = per - 1; i >= 0; i--) {
+        const int b = b0 + i;
+        if (b <= nb) {
+            carry[0] = min(carry[0], (int)T0[b]);
+            carry[1] = min(carry[1], (int)T1[b]);
+            carry[2] = min(carry[2], (int)T2[b]);
+            T0[b] = (unsigned short)carry[0];
+            T1[b] = (unsigned short)carry[1];
+            T2[b] = (unsigned short)carry[2];
+        }
+    }
+    __syncthreads();
+}
+
 // number of knots <= q: all knots in lower buckets are <= q, so the scan starts at the first knot of
 // q's own bucket.  (A variant with three independent probes instead of the dependent scan measured
 // 4 % slower on the C3 batch: most buckets hold one knot.)

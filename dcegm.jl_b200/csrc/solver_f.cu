@@ -165,12 +165,19 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_f_kernel(DeviceBat
             knot_index_range(Kr, N.r_x(), N.n_r, nbuck);
             knot_index_range(Kc, N.wc_x(), N.n_wc, nbuck);
             knot_index_range(Kv, N.wv_x(), N.n_wv, nbuck);
+#ifdef DC_KNOT_BUILD_PER_KNOT  // A/B builds only
             const int nmax = max(N.n_r, max(N.n_wc, N.n_wv));
             for (int k = tid; k < nmax; k += kThreads) {  // the three tables in one pass
                 if (k < N.n_r) knot_index_build_step(Kr, N.r_x(), N.n_r, nbuck, k);
                 if (k < N.n_wc) knot_index_build_step(Kc, N.wc_x(), N.n_wc, nbuck, k);
                 if (k < N.n_wv) knot_index_build_step(Kv, N.wv_x(), N.n_wv, nbuck, k);
             }
+#else
+            knot_index_build3<kThreads>(reinterpret_cast<unsigned short*>(dc_smem + Kr.tab),
+                                        reinterpret_cast<unsigned short*>(dc_smem + Kc.tab),
+                                        reinterpret_cast<unsigned short*>(dc_smem + Kv.tab), Kr, Kc, Kv, N.r_x(), N.n_r,
+                                        N.wc_x(), N.n_wc, N.wv_x(), N.n_wv, nbuck);
+#endif
         }
         __syncthreads();
         DC_CLK(1);

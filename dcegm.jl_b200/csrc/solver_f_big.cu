@@ -98,12 +98,8 @@ __device__ inline void big_build_index(const BigPlan& P, unsigned char* g, BigSt
         knot_index_range(Kr, L.r_x(), L.n_r, nb);
         knot_index_range(Kc, L.wc_x(), L.n_wc, nb);
         knot_index_range(Kv, L.wv_x(), L.n_wv, nb);
-        const int nmax = max(L.n_r, max(L.n_wc, L.n_wv));
-        for (int k = tid; k < nmax; k += NT) {
-            if (k < L.n_r) knot_index_build_step_at(P.tab(g, 0), Kr, L.r_x(), L.n_r, nb, k);
-            if (k < L.n_wc) knot_index_build_step_at(P.tab(g, 1), Kc, L.wc_x(), L.n_wc, nb, k);
-            if (k < L.n_wv) knot_index_build_step_at(P.tab(g, 2), Kv, L.wv_x(), L.n_wv, nb, k);
-        }
+        knot_index_build3<NT>(P.tab(g, 0), P.tab(g, 1), P.tab(g, 2), Kr, Kc, Kv, L.r_x(), L.n_r, L.wc_x(), L.n_wc, L.wv_x(),
+                              L.n_wv, nb);
     }
     if (tid == 0) {
         st->Kr = Kr;
