@@ -126,10 +126,8 @@ __device__ __forceinline__ double pow_hot(double x, double y) {
 __device__ __forceinline__ void pow_hot2(double x1, double x2, double y, double* r1, double* r2) {
     const bool ok = dc_is_norm_pos(x1) && dc_is_norm_pos(x2);
     double h1, l1, h2, l2;
-    dc_log_parts_pos(ok ? x1 : 1.0, &h1, &l1);
-    dc_log_parts_pos(ok ? x2 : 1.0, &h2, &l2);
-    *r1 = dc_pow_from_log(h1, l1, y);
-    *r2 = dc_pow_from_log(h2, l2, y);
+    dc_log_parts_pos2(ok ? x1 : 1.0, ok ? x2 : 1.0, &h1, &l1, &h2, &l2);
+    dc_pow_from_log2(h1, l1, h2, l2, y, r1, r2);
     if (!ok) {
         *r1 = dc_pow_cold(x1, y);
         *r2 = dc_pow_cold(x2, y);
@@ -140,6 +138,19 @@ __device__ __forceinline__ double u_from_log(double lh, double ll, bool working,
     const double dis = working ? p.alpha : 0.0;
     if (p.gamma_is_one) return (lh + ll) - dis;
     return p.oneover_oneminusgamma * (dc_pow_from_log(lh, ll, p.oneminusgamma) - 1.0) - dis;
+}
+// u(c1, working) and u(c2, not working) together
+__device__ __forceinline__ void u_from_log2(double l1h, double l1l, double l2h, double l2l, const DevModel& p, double* u1,
+                                            double* u2) {
+    if (p.gamma_is_one) {
+        *u1 = (l1h + l1l) - p.alpha;
+        *u2 = (l2h + l2l) - 0.0;
+        return;
+    }
+    double p1, p2;
+    dc_pow_from_log2(l1h, l1l, l2h, l2l, p.oneminusgamma, &p1, &p2);
+    *u1 = p.oneover_oneminusgamma * (p1 - 1.0) - p.alpha;
+    *u2 = p.oneover_oneminusgamma * (p2 - 1.0) - 0.0;
 }
 __device__ __forceinline__ double up_from_log(double lh, double ll, double c, const DevModel& p) {
     if (p.gamma_is_one) return 1.0 / c;
