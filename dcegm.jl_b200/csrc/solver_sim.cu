@@ -23,13 +23,18 @@ namespace dcegm {
 #endif
 constexpr int kSimUnroll = DC_SIM_UNROLL;
 constexpr int kSimAgents = 4;                    // agents per thread and tile
-constexpr int kSimTile = kThreads * kSimAgents;  // agents per tile
+constexpr int kSimTile = kThreads * kSimAgents;  // agents per tile: the unit of the fixed summation order
+// tiles that share one staging of a period's lines (their sums are still formed and added tile by tile)
+// (measured, G agent-periods/s: 16.5 / 17.2 / 18.5 / 19.5 for 1 / 2 / 4 / 8 tiles with five income states staged per
+// period; with the single state of the retirement model staging is cheap and one tile is fastest: 19.0 vs 16.7)
+constexpr int kSimSubMax = 8;
+__host__ __device__ constexpr int sim_sub(int model) { return model == DCEGM_MODEL_G ? 8 : 1; }
 
 
 size_t sim_smem_bytes(const dcegm_layout& l) {
     const size_t lines = (size_t)l.nstate * 8 * l.cap * sizeof(double);
     const size_t tabs = ((size_t)l.ny * l.ny + (size_t)l.nT * l.ny + (size_t)l.nT * DCEGM_SIM_NMOM +
-                         (size_t)l.nT * kWarps * DCEGM_SIM_NMOM +
+                         (size_t)kSimSubMax * kWarps * DCEGM_SIM_NMOM +
                          (size_t)l.nstate * 2) * sizeof(double);
     const size_t ints = ((size_t)l.nT + 1 + (size_t)l.nstate * 4 + 4) * sizeof(int);
     return lines + tabs + ints + 64;
@@ -50,6 +55,8 @@ template <int MODEL, int Top>
 __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatch Sb) {
     const int m = B.first + blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    constexpr int kSimSub = sim_sub(MODEL);
+    constexpr int kSimState = kSimSub * kSimAgents;  // agents per thread between two stagings
     __shared__ DevModel s_p;
     __shared__ SimModel s_sp;
     __shared__ int s_status;
@@ -70,8 +77,8 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
     double* gg = ln + (size_t)nstate * 8 * cap;                      // [ny][ny] cumulative transition rows
     double* inctab = gg + ny * ny;                                   // [nT][ny] income(it+1, yvec)
     double* mom = inctab + nT * ny;                                  // [nT][NMOM]
-    double* red = mom + nT * DCEGM_SIM_NMOM;                         // [nT][kWarps][NMOM] warp sums of the current tile
-    double* vb = red + nT * kWarps * DCEGM_SIM_NMOM;                 // [nstate][2]
+    double* red = mom + nT * DCEGM_SIM_NMOM;                         // [kSimSub][kWarps][NMOM] warp sums of one period
+    double* vb = red + kSimSubMax * kWarps * DCEGM_SIM_NMOM;         // [nstate][2]
     int* hist = reinterpret_cast<int*>(vb + nstate * 2);             // [nT+1]
     int* lens = hist + nT + 1;                                       // [nstate][id][kind]
     auto line = [&](int st, int id, int kind, int xy) { return ln + ((((size_t)st * 2 + id) * 2 + kind) * 2 + xy) * cap; };
@@ -102,12 +109,24 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
     double* pd = Sb.pan_d ? Sb.pan_d + (size_t)m * 6 * npan : nullptr;
     int32_t* pi = Sb.pan_i ? Sb.pan_i + (size_t)m * 2 * npan : nullptr;
 
-    for (int tile0 = 0; tile0 < nsims; tile0 += kSimTile) {
-        double w1[kSimAgents];
-        int ys[kSimAgents], ret[kSimAgents];
-        bool working[kSimAgents], prev_worker[kSimAgents];
-#pragma unroll
-        for (int a = 0; a < kSimAgents; a++) {
+    // warp sums of period `itf` (in red) -> running per-period sums, tile by tile in ascending order, warps ascending
+    auto fold = [&](int itf, int group0) {
+        if (tid < DCEGM_SIM_NMOM) {
+            for (int lt = 0; lt < kSimSub; lt++) {
+                const int t0 = group0 + lt * kSimTile;
+                if (t0 >= nsims) break;
+                double t = red[(lt * kWarps) * DCEGM_SIM_NMOM + tid];
+                for (int w = 1; w < kWarps; w++) t += red[(lt * kWarps + w) * DCEGM_SIM_NMOM + tid];
+                mom[itf * DCEGM_SIM_NMOM + tid] = t0 == 0 ? t : mom[itf * DCEGM_SIM_NMOM + tid] + t;
+            }
+        }
+    };
+    for (int group0 = 0; group0 < nsims; group0 += kSimTile * kSimSub) {
+        double w1[kSimState];
+        int ys[kSimState], ret[kSimState];
+        bool working[kSimState], prev_worker[kSimState];
+#pragma unroll 1
+        for (int a = 0; a < kSimState; a++) {
             w1[a] = 0.0;
             ys[a] = 0;
             ret[a] = 0;
@@ -116,6 +135,7 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
         }
         for (int it = 0; it < nT; it++) {
             __syncthreads();
+            if (it > 0) fold(it - 1, group0);  // eight threads; the others go on staging
             // ---- stage the lines of period `it` (AoS in HBM -> SoA in shared memory) ----
             for (int s = tid; s < nstate * 4; s += kThreads) {
                 const size_t slot = ((size_t)m * nT + it) * nstate * 4 + s;
@@ -140,13 +160,18 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
                 }
             }
             __syncthreads();
+            int flags = 0;
+#pragma unroll 1
+            for (int lt = 0; lt < kSimSub; lt++) {
+            const int tile0 = group0 + lt * kSimTile;
+            if (tile0 >= nsims) break;  // block-uniform
             double sum[DCEGM_SIM_NMOM];
 #pragma unroll
             for (int k = 0; k < DCEGM_SIM_NMOM; k++) sum[k] = 0.0;
-            int flags = 0;
 #pragma unroll kSimUnroll
-            for (int a = 0; a < kSimAgents; a++) {
-                const int i = tile0 + a * kThreads + tid;
+            for (int a0 = 0; a0 < kSimAgents; a0++) {
+                const int a = lt * kSimAgents + a0;  // slot of the agent's state
+                const int i = tile0 + a0 * kThreads + tid;
                 if (i >= nsims) continue;
                 const size_t at = (size_t)i + (size_t)nsims * it;
                 // ---- state at the start of the period (simulate.jl:82-101, 160-178) ----
@@ -248,26 +273,22 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
                     pi[1 * npan + at] = worker;
                 }
             }
-            if (flags) atomicOr(&s_status, flags);
-            // ---- tile sums: shuffle tree per warp now; the warps are added up (ascending) once per tile ----
+            // ---- tile sums: shuffle tree per warp; the warps are added up (ascending) by fold() ----
 #pragma unroll
             for (int k = 0; k < DCEGM_SIM_NMOM; k++) {
                 double v = sum[k];
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-                if (lane == 0) red[(it * kWarps + wid) * DCEGM_SIM_NMOM + k] = v;
+                if (lane == 0) red[(lt * kWarps + wid) * DCEGM_SIM_NMOM + k] = v;
             }
+            }  // lt
+            if (flags) atomicOr(&s_status, flags);
         }
         __syncthreads();
-        for (int q = tid; q < nT * DCEGM_SIM_NMOM; q += kThreads) {
-            const int it = q / DCEGM_SIM_NMOM, k = q - it * DCEGM_SIM_NMOM;
-            double t = red[(it * kWarps) * DCEGM_SIM_NMOM + k];
-            for (int w = 1; w < kWarps; w++) t += red[(it * kWarps + w) * DCEGM_SIM_NMOM + k];
-            mom[q] = tile0 == 0 ? t : mom[q] + t;
-        }
-#pragma unroll
-        for (int a = 0; a < kSimAgents; a++) {
-            const int i = tile0 + a * kThreads + tid;
+        fold(nT - 1, group0);
+#pragma unroll 1
+        for (int a = 0; a < kSimState; a++) {
+            const int i = group0 + (a / kSimAgents) * kSimTile + (a % kSimAgents) * kThreads + tid;
             if (i < nsims) {
                 atomicAdd(&hist[ret[a]], 1);
                 if (Sb.pan_ret) Sb.pan_ret[(size_t)m * nsims + i] = ret[a];
