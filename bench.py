@@ -26,11 +26,11 @@ BATCH = 4096
 # 2 lines x 2 choices x 24 periods x 501 points x 16 B + terminal 128 B + param 248 B
 ALGO_BYTES_PER_MODEL = 2 * 2 * 24 * 501 * 16 + 128 + 248
 # dram__bytes_read.sum + dram__bytes_write.sum of solve_f_kernel per model, from the `ncu --set full` capture
-# summarised in profiles/r1d_solve_f_ncu_summary.md (904.3 MB for 1184 models)
-NCU_DRAM_BYTES_PER_MODEL = 904.3e6 / 1184
+# summarised in profiles/r1g_ncu_summary.md (11.53 MB + 885.39 MB for 1184 models)
+NCU_DRAM_BYTES_PER_MODEL = (11.529984e6 + 885.387008e6) / 1184
 # sm__inst_executed_pipe_fp64.sum of solve_f_kernel per model (warp instructions), same capture series
-# (profiles/r1e_solve_f_metrics.csv: 977 324 011 for 1184 models)
-NCU_FP64_WARP_INST_PER_MODEL = 977324011 / 1184
+# (profiles/r1g_solve_f_metrics.csv: 978 056 424 for 1184 models)
+NCU_FP64_WARP_INST_PER_MODEL = 978056424 / 1184
 WORKLOAD = "C3: retirement model (FModel) batch, na=500, nT=25, ny=5, log10(lambda)~U(log10 2e-6, log10 0.2), sigma~U(0,0.6)"
 
 
@@ -293,7 +293,7 @@ def main():
                        "flagged_models_rank0": n_flagged, "models_counted": int(solved),
                        "flagged_note": "status != 0 (non-monotone line: Interpolations.jl would throw) -> not counted; the oracle flags the same models"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_DRAM_BYTES_PER_MODEL * nper, "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum (profiles/r1d_solve_f_ncu_summary.md, r1e_solve_f_metrics.csv), bytes per launch scaled to this batch",
+                         "traffic": NCU_DRAM_BYTES_PER_MODEL * nper, "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum (profiles/r1g_ncu_summary.md, r1g_solve_f_metrics.csv), bytes per launch scaled to this batch",
                          "peak_source": peak_src,
                          "note": "dominant kernel solve_f_kernel is FP64-pipe bound by construction (SURVEY.md §8d): "
                                  "~70 FP64 instr per algorithmic byte; HBM fraction reported as the metric asks"},
@@ -301,7 +301,7 @@ def main():
                               "frac": fp64_achieved / fp64_peak if fp64_peak > 0 else None,
                               "peak_tflops": 2 * dfma.value / 1e12,
                               "source": "achieved = FP64-pipe warp instructions per model (ncu sm__inst_executed_pipe_fp64.sum, "
-                                        "profiles/r1e_solve_f_metrics.csv) x models / kernel time; peak = dcegm_debug_dfma_rate measured in this run"},
+                                        "profiles/r1g_solve_f_metrics.csv) x models / kernel time; peak = dcegm_debug_dfma_rate measured in this run"},
             "e2e": {"value": e2e_value, "unit": "models/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "d2h_gbs": d2h * args.steps / e2e_s / 1e9,
                     "note": "bound by the device-to-host transfer of every stored polyline (pinned D2H measures ~57 GB/s on these boxes)"},
