@@ -127,3 +127,23 @@ def test_minimal_variants_oracle():
     c_beq = d.line(0, _abi.KIND_C, 0, q.nT - 2)[1]
     assert np.all(c_beq[-5:] < c_no[-5:]) and c_beq[1] > c_no[1]
     assert d.status[0] == 0
+
+
+def test_oracle_on_a_fine_grid_keeps_its_invariants(oracle):
+    """BASELINE configs[3] geometry on a short horizon (the GPU side is tests/test_gpu_parity_f_big.py): the layout grows
+    with na, sections are not capped, every stored line is strictly increasing in x while the status word is clean."""
+    from dcegm_jl_b200 import Param
+
+    d = dict(na=4000, ny=8, nT=8, retage=9, beta=0.95, R=1.05, sigma=0.45)
+    d["lambda"] = 5.45e-5
+    r = oracle.solve_f([Param(par=d)], portable=True)
+    lay = r.lay
+    assert lay.na == 4000 and lay.cap == (4000 + 400 + 2 * 250 + 2 + 7) // 8 * 8 and lay.isec_cap == 250
+    assert r.status[0] == 0 and r.lens.max() <= lay.cap
+    assert r.meta[0, :, 0, 1].sum() > 0  # kinks were found
+    for it in range(7):
+        for idd in (0, 1):
+            for kind in (0, 1):
+                n = r.lens[0, it, 0, idd, kind]
+                x = r.lines[0, it, 0, idd, kind, :n, 0]
+                assert (np.diff(x) > 0).all()
