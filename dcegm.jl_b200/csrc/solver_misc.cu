@@ -10,6 +10,7 @@ namespace dcegm {
 // recursion runs out of shared memory.  Output: kind C lines (m[it], c[it]) for id 0; the bequest
 // variant also keeps the value function as kind V lines (m[it], v[it]).
 __global__ void __launch_bounds__(kThreads) solve_minimal_kernel(DeviceBatch B) {
+    const int nthr = blockDim.x;  // one thread per grid point, at most kThreads (coarse grids get a narrower CTA)
     extern __shared__ __align__(16) unsigned char smem[];
     const int m = B.first + blockIdx.x, tid = threadIdx.x;
     __shared__ DevModel s_p;
@@ -33,7 +34,7 @@ __global__ void __launch_bounds__(kThreads) solve_minimal_kernel(DeviceBatch B) 
     int cur = 0, nnext = 2;
     if (beq) {  // minimal_EGM.jl:102-104: terminal lines on the whole savings grid
         nnext = na;
-        for (int k = tid; k < na; k += kThreads) {
+        for (int k = tid; k < na; k += nthr) {
             buf[0][0][k] = avec[k];
             buf[0][1][k] = avec[k];
             buf[0][2][k] = p.nu > 0 ? p.nu * u_plain(avec[k] + p.bbar, p) : 0.0;
@@ -47,12 +48,12 @@ __global__ void __launch_bounds__(kThreads) solve_minimal_kernel(DeviceBatch B) 
         const size_t slot = line_slot(B.lay, m, nT - 1, 0, 0, DCEGM_KIND_C);
         if (tid == 0) B.lens[slot] = nnext;
         if (B.lines)
-            for (int k = tid; k < nnext; k += kThreads) B.lines[slot * (size_t)B.lay.cap + k] = make_double2(buf[0][0][k], buf[0][1][k]);
+            for (int k = tid; k < nnext; k += nthr) B.lines[slot * (size_t)B.lay.cap + k] = make_double2(buf[0][0][k], buf[0][1][k]);
         if (beq) {
             const size_t sv = line_slot(B.lay, m, nT - 1, 0, 0, DCEGM_KIND_V);
             if (tid == 0) B.lens[sv] = nnext;
             if (B.lines)
-                for (int k = tid; k < nnext; k += kThreads) B.lines[sv * (size_t)B.lay.cap + k] = make_double2(buf[0][0][k], buf[0][2][k]);
+                for (int k = tid; k < nnext; k += nthr) B.lines[sv * (size_t)B.lay.cap + k] = make_double2(buf[0][0][k], buf[0][2][k]);
         }
     }
     for (int t = nT - 2; t >= 0; t--) {
@@ -63,7 +64,7 @@ __global__ void __launch_bounds__(kThreads) solve_minimal_kernel(DeviceBatch B) 
         double* cy = buf[cur ^ 1][1];
         double* cv = buf[cur ^ 1][2];
         const bool beq_period = beq && t == nT - 2 && p.nu > 0;  // minimal_EGM.jl:124-133
-        for (int ia = tid; ia < na; ia += kThreads) {
+        for (int ia = tid; ia < na; ia += nthr) {
             const double Ra = p.R * avec[ia];
             double acc = 0.0, accv = 0.0;
             for (int iy = 0; iy < ny; iy++) {
@@ -94,18 +95,18 @@ __global__ void __launch_bounds__(kThreads) solve_minimal_kernel(DeviceBatch B) 
         }
         __syncthreads();
         int flag = 0;
-        for (int k = tid; k < na; k += kThreads)
+        for (int k = tid; k < na; k += nthr)
             if (!(cx[k + 1] > cx[k])) flag = DCEGM_ST_NONMONOTONE;
         if (flag) atomicOr(&s_status, flag);
         const size_t slot = line_slot(B.lay, m, t, 0, 0, DCEGM_KIND_C);
         if (tid == 0) B.lens[slot] = na + 1;
         if (B.lines)
-            for (int k = tid; k < na + 1; k += kThreads) B.lines[slot * (size_t)B.lay.cap + k] = make_double2(cx[k], cy[k]);
+            for (int k = tid; k < na + 1; k += nthr) B.lines[slot * (size_t)B.lay.cap + k] = make_double2(cx[k], cy[k]);
         if (beq) {
             const size_t sv = line_slot(B.lay, m, t, 0, 0, DCEGM_KIND_V);
             if (tid == 0) B.lens[sv] = na + 1;
             if (B.lines)
-                for (int k = tid; k < na + 1; k += kThreads) B.lines[sv * (size_t)B.lay.cap + k] = make_double2(cx[k], cv[k]);
+                for (int k = tid; k < na + 1; k += nthr) B.lines[sv * (size_t)B.lay.cap + k] = make_double2(cx[k], cv[k]);
         }
         nnext = na + 1;
         cur ^= 1;
@@ -137,7 +138,9 @@ cudaError_t launch_solve_minimal(const DeviceBatch& B0, int first, int count, cu
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    solve_minimal_kernel<<<count, kThreads, smem, stream>>>(B);
+    int nthr = (B.lay.na + 1 + 31) / 32 * 32;  // a thread per grid point
+    nthr = nthr > kThreads ? kThreads : nthr;
+    solve_minimal_kernel<<<count, nthr, smem, stream>>>(B);
     return cudaGetLastError();
 }
 
