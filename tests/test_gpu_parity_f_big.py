@@ -161,3 +161,16 @@ def test_packed_transfer_of_fine_grid_solution(solver):
     flat = g.lines.reshape(-1, g.lay.cap, 2)
     for s in (0, 5, len(lens) - 1):
         assert np.array_equal(xy[off[s]:off[s + 1]], flat[s, : lens[s]], equal_nan=True)
+
+
+def test_irregular_models_on_the_fine_grid(solver, oracle):
+    """a wider draw at na = 3000: models whose lines stop being strictly increasing (status NONMONOTONE / MISALIGNED, the
+    reference would throw there) take the sequential insertion path, the merge sort of the policy and the generic EGM node;
+    they must still match the oracle bit for bit, status words included"""
+    from dcegm_jl_b200 import _abi
+
+    ps = draws(32, seed=11, na=3000, ny=8, nT=14, retage=15)
+    g = solver.solve(_abi.MODEL_F, ps)
+    r = oracle.solve_f(ps, portable=True, nthreads=8)
+    assert_bitwise(g, r)
+    assert (r.status != 0).any(), "the draw should contain irregular models"
