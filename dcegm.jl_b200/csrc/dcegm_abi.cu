@@ -610,6 +610,7 @@ int dcegm_simulate(dcegm_handle h, unsigned flags, const dcegm_sim_shocks* sh) {
     if (l.model != DCEGM_MODEL_F && l.model != DCEGM_MODEL_G) return fail(h, DCEGM_E_INVALID, "dcegm_simulate: the resident solution is not an FModel / GModel");
     if (!B.lines) return fail(h, DCEGM_E_NOSOLUTION, "dcegm_simulate needs the stored lines (solve without DCEGM_SUMMARY_ONLY)");
     if ((long long)sim_smem_bytes(l) > (long long)h->max_smem_optin) return fail(h, DCEGM_E_INVALID, "dcegm_simulate: lines of one period do not fit into shared memory");
+    if (l.ny > 256 || l.nT > 65533) return fail(h, DCEGM_E_INVALID, "dcegm_simulate: ny <= 256 and nT <= 65533 (packed agent state)");
     const int n = l.nmodels, nT = l.nT;
     const bool panel = flags & DCEGM_SIM_PANEL;
     int nsims = sh ? sh->nsims : h->tab.sim[0].nsims;

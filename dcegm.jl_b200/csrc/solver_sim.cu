@@ -122,16 +122,14 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
         }
     };
     for (int group0 = 0; group0 < nsims; group0 += kSimTile * kSimSub) {
+        // the agents' state between periods lives in local memory (the per-agent body is rolled): wealth, and one
+        // word holding the income state (bits 0-7), "works this period" (bit 8) and the retirement period (bits 16-31)
         double w1[kSimState];
-        int ys[kSimState], ret[kSimState];
-        bool working[kSimState], prev_worker[kSimState];
+        unsigned stw[kSimState];
 #pragma unroll 1
         for (int a = 0; a < kSimState; a++) {
             w1[a] = 0.0;
-            ys[a] = 0;
-            ret[a] = 0;
-            working[a] = true;
-            prev_worker[a] = true;
+            stw[a] = 1u << 8;
         }
         for (int it = 0; it < nT; it++) {
             __syncthreads();
@@ -176,7 +174,9 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
                 const size_t at = (size_t)i + (size_t)nsims * it;
                 // ---- state at the start of the period (simulate.jl:82-101, 160-178) ----
                 double w0, inc;
-                const bool wk = working[a];
+                const unsigned sw = stw[a];
+                const bool wk = (sw >> 8) & 1u;
+                int ysa = (int)(sw & 0xffu), reta = (int)(sw >> 16);
                 const int worker = wk ? 1 : 2;
                 if (MODEL == DCEGM_MODEL_G) {
                     if (it == 0) {
@@ -186,30 +186,29 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
                         else
                             y0 = (int)(dc_sim_uniform(sp.rseed, (uint32_t)i, 0u, DC_STREAM_Y0) * (double)ny);
                         y0 = y0 < 0 ? 0 : (y0 > ny - 1 ? ny - 1 : y0);
-                        ys[a] = y0;
+                        ysa = y0;
                     } else {
                         // searchsortedfirst(GG[ystate[i,it-1],:], wshocks[i,it]) (simulate.jl:148)
                         const double uw = Sb.given ? Sb.wsh[at] : dc_sim_uniform(sp.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_W);
-                        const double* row = gg + ys[a] * ny;
+                        const double* row = gg + ysa * ny;
                         int j = 0;
                         while (j < ny && !(row[j] >= uw)) j++;
                         if (j >= ny) {
                             flags |= DCEGM_ST_YSTATE_RANGE;
                             j = ny - 1;
                         }
-                        ys[a] = j;
+                        ysa = j;
                     }
                 }
                 if (it == 0) {
                     const double u0 = Sb.given ? Sb.w0sh[i] : dc_sim_uniform(sp.rseed, (uint32_t)i, 0u, DC_STREAM_W0);
                     w0 = sp.initw0 + u0 * (sp.initw1 - sp.initw0);
-                    inc = MODEL == DCEGM_MODEL_G ? inctab[ys[a]] : __longlong_as_double(0x7ff8000000000000LL);  // stays NaN, simulate.jl:18
+                    inc = MODEL == DCEGM_MODEL_G ? inctab[ysa] : __longlong_as_double(0x7ff8000000000000LL);  // stays NaN, simulate.jl:18
                 } else {
-                    if (prev_worker[a] && !wk) ret[a] = it + 1;  // simulate.jl:95
                     if (!wk) {
                         inc = p.pension;
                     } else if (MODEL == DCEGM_MODEL_G) {
-                        inc = inctab[it * ny + ys[a]];
+                        inc = inctab[it * ny + ysa];
                     } else {
                         const double uw = Sb.given ? Sb.wsh[at] : dc_sim_uniform(sp.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_W);
                         const double shock = dc_norm_quantile(uw) * sp.sigma;  // simulate.jl:73
@@ -220,7 +219,7 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
                     w0 = w1[a] * p.R + inc;  // simulate.jl:103
                 }
                 // ---- consumption, utility, end-of-period wealth (simulate.jl:106-110) ----
-                const int st = MODEL == DCEGM_MODEL_G ? ys[a] : 0;
+                const int st = MODEL == DCEGM_MODEL_G ? ysa : 0;
                 const int id = wk ? 0 : 1;
                 const double cons = interp_y<Top>(line(st, id, 0, 0), line(st, id, 0, 1), lens[(st * 2 + id) * 2 + 0], w0);
                 const double util = u_work(cons, wk, p);
@@ -251,8 +250,9 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
                     const double ur = Sb.given ? (Sb.rsh ? Sb.rsh[at] : 1.0) : dc_sim_uniform(sp.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_R);
                     next = p.delta > ur;
                 }
-                prev_worker[a] = wk;
-                working[a] = next;
+                // retirement period (simulate.jl:95 sets it at the start of the first period not worked, 1-based)
+                if (wk && !next && it + 1 < nT) reta = it + 2;
+                stw[a] = (unsigned)ysa | (next ? 1u << 8 : 0u) | ((unsigned)reta << 16);
                 w1[a] = w1n;
                 sum[0] += w0;
                 sum[1] += w1n;
@@ -269,7 +269,7 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
                     pd[3 * npan + at] = util;
                     pd[4 * npan + at] = inc;
                     pd[5 * npan + at] = pw;
-                    pi[0 * npan + at] = MODEL == DCEGM_MODEL_G ? ys[a] + 1 : 0;
+                    pi[0 * npan + at] = MODEL == DCEGM_MODEL_G ? ysa + 1 : 0;
                     pi[1 * npan + at] = worker;
                 }
             }
@@ -290,8 +290,9 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
         for (int a = 0; a < kSimState; a++) {
             const int i = group0 + (a / kSimAgents) * kSimTile + (a % kSimAgents) * kThreads + tid;
             if (i < nsims) {
-                atomicAdd(&hist[ret[a]], 1);
-                if (Sb.pan_ret) Sb.pan_ret[(size_t)m * nsims + i] = ret[a];
+                const int reta = (int)(stw[a] >> 16);
+                atomicAdd(&hist[reta], 1);
+                if (Sb.pan_ret) Sb.pan_ret[(size_t)m * nsims + i] = reta;
             }
         }
     }
