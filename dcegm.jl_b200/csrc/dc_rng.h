@@ -3,7 +3,7 @@
  * The reference seeds Julia's global RNG (Random.seed!(p.rseed), src/simulate.jl:72,137) and draws
  * whole matrices; its stream cannot be reproduced outside Julia.  Here every draw is a pure function
  * of (seed, agent, period, stream): Philox4x32-10 (Salmon et al., SC'11) keyed by the 64-bit seed,
- * counter = (agent, period, stream, 0).  Like the reference, the model index does not enter — two
+ * counter = (agent, period, stream >> 1, 0), words 0-1 for even streams and 2-3 for odd ones.  Like the reference, the model index does not enter — two
  * parameterisations simulated with one seed see the same shocks (common random numbers).
  *
  * Integer arithmetic only for the bits; the uniform -> normal map is Wichura's AS241 (PPND16, relative
@@ -50,12 +50,23 @@ DC_HD void dc_philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, 
     out[3] = c3;
 }
 
-/* uniform on [0,1) with 53 random bits, like Julia's rand(Float64) */
-DC_HD double dc_sim_uniform(int64_t seed, uint32_t agent, uint32_t period, uint32_t stream) {
-    uint32_t o[4];
-    dc_philox4x32_10(agent, period, stream, 0u, (uint32_t)((uint64_t)seed & 0xffffffffu), (uint32_t)((uint64_t)seed >> 32), o);
-    const uint64_t bits = ((uint64_t)(o[0] >> 5) << 26) | (uint64_t)(o[1] >> 6);
+/* Uniforms on [0,1) with 53 random bits, like Julia's rand(Float64).  One Philox block (four words) serves two
+ * streams: block = stream >> 1, the even stream takes words 0-1 and the odd one words 2-3 — so the simulator gets an
+ * agent's income shock (W) and choice shock (D) of a period from one call. */
+DC_HD double dc_bits53(uint32_t a, uint32_t b) {
+    const uint64_t bits = ((uint64_t)(a >> 5) << 26) | (uint64_t)(b >> 6);
     return (double)(int64_t)bits * 1.1102230246251565e-16; /* 2^-53, exact */
+}
+DC_HD void dc_sim_uniform_pair(int64_t seed, uint32_t agent, uint32_t period, uint32_t block, double* even, double* odd) {
+    uint32_t o[4];
+    dc_philox4x32_10(agent, period, block, 0u, (uint32_t)((uint64_t)seed & 0xffffffffu), (uint32_t)((uint64_t)seed >> 32), o);
+    *even = dc_bits53(o[0], o[1]);
+    *odd = dc_bits53(o[2], o[3]);
+}
+DC_HD double dc_sim_uniform(int64_t seed, uint32_t agent, uint32_t period, uint32_t stream) {
+    double e, o;
+    dc_sim_uniform_pair(seed, agent, period, stream >> 1, &e, &o);
+    return (stream & 1u) ? o : e;
 }
 
 DC_HD double dc_horner8(const double* k, double r) {

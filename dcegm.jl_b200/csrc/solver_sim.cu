@@ -178,6 +178,12 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
                 const bool wk = (sw >> 8) & 1u;
                 int ysa = (int)(sw & 0xffu), reta = (int)(sw >> 16);
                 const int worker = wk ? 1 : 2;
+                // income shock and choice shock of this agent-period: one Philox block (dc_rng.h); nobody needs
+                // either for a retiree of the retirement model
+                double u_w = 0.0, u_d = 1.0;
+                static_assert(DC_STREAM_W == 0 && DC_STREAM_D == 1, "W and D share block 0");
+                if (!Sb.given && (wk || (MODEL == DCEGM_MODEL_G && it > 0)))
+                    dc_sim_uniform_pair(sp.rseed, (uint32_t)i, (uint32_t)it, 0u, &u_w, &u_d);
                 if (MODEL == DCEGM_MODEL_G) {
                     if (it == 0) {
                         int y0;
@@ -189,7 +195,7 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
                         ysa = y0;
                     } else {
                         // searchsortedfirst(GG[ystate[i,it-1],:], wshocks[i,it]) (simulate.jl:148)
-                        const double uw = Sb.given ? Sb.wsh[at] : dc_sim_uniform(sp.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_W);
+                        const double uw = Sb.given ? Sb.wsh[at] : u_w;
                         const double* row = gg + ysa * ny;
                         int j = 0;
                         while (j < ny && !(row[j] >= uw)) j++;
@@ -210,7 +216,7 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
                     } else if (MODEL == DCEGM_MODEL_G) {
                         inc = inctab[it * ny + ysa];
                     } else {
-                        const double uw = Sb.given ? Sb.wsh[at] : dc_sim_uniform(sp.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_W);
+                        const double uw = Sb.given ? Sb.wsh[at] : u_w;
                         const double shock = dc_norm_quantile(uw) * sp.sigma;  // simulate.jl:73
                         const int it1 = it + 1, age = it1 + 19;
                         inc = it1 > sp.retage ? p.pension
@@ -244,7 +250,7 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
                 }
                 // ---- next period's state (simulate.jl:124-127, 201) ----
                 // a retiree's draw cannot matter (pw = 0 is never above a uniform in [0,1)): no Philox call for it
-                const double ud = Sb.given ? Sb.dsh[at] : (wk ? dc_sim_uniform(sp.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_D) : 1.0);
+                const double ud = Sb.given ? Sb.dsh[at] : (wk ? u_d : 1.0);
                 bool next = pw > ud;
                 if (MODEL == DCEGM_MODEL_F && !wk) {
                     const double ur = Sb.given ? (Sb.rsh ? Sb.rsh[at] : 1.0) : dc_sim_uniform(sp.rseed, (uint32_t)i, (uint32_t)it, DC_STREAM_R);
