@@ -471,7 +471,7 @@ cudaError_t launch_solve_f_big(const DeviceBatch& B0, int first, int count, unsi
         const int v = e ? atoi(e) : 4;
         return v < 1 ? 1 : (v > kMaxParts ? kMaxParts : v);
     }();
-    const int np = count >= 16 * parts_wanted ? parts_wanted : 1;
+    const int np = count / 16 < 1 ? 1 : (count / 16 < parts_wanted ? count / 16 : parts_wanted);  // parts of >= 16 models
     cudaStream_t st[kMaxParts] = {stream};
     cudaEvent_t fork = nullptr, join[kMaxParts] = {};
     if (np > 1) {
