@@ -19,13 +19,19 @@ ST_INSERT_RANGE = 1 << 8
 ST_LOOP_LIMIT = 1 << 9
 ST_NEG_CONS = 1 << 10
 ST_YSTATE_RANGE = 1 << 11
+# informational: the reference returns normally on these (include/dcegm.h)
+ST_EXTRA_RIGHT = 1 << 12
+ST_NONMONO_FIRST = 1 << 13
+ST_DUP_KNOT = 1 << 14
+ST_INFO_MASK = ST_EXTRA_RIGHT | ST_NONMONO_FIRST
+ST_FATAL_MASK = ~ST_INFO_MASK & 0xFFFFFFFF
 
 STATUS_TEXT = {
     ST_ISECT_OVERFLOW: "more intersections than isec_cap",
     ST_LINE_OVERFLOW: "a line outgrew its slot",
     ST_NONMONOTONE: "knot vector not strictly increasing (Interpolations.jl would throw, line.jl:236)",
     ST_NO_BRACKET: "fzero without a sign change (envelope.jl:199)",
-    ST_MISALIGNED: "insert_left/insert_right lengths differ (dc_algo.jl:486-491)",
+    ST_MISALIGNED: "insert_right shorter than insert_left (dc_algo.jl:486-491)",
     ST_ALL_FALLING: "splitLine produced no section (envelope.jl:97-104)",
     ST_NONFINITE: "NaN/Inf in a computed line",
     ST_SEG_OVERFLOW: "more sections than seg_cap",
@@ -33,6 +39,9 @@ STATUS_TEXT = {
     ST_LOOP_LIMIT: "third-line loop did not terminate (envelope.jl:197-240)",
     ST_NEG_CONS: "simulator: negative consumption (simulate.jl:111-116 calls error())",
     ST_YSTATE_RANGE: "simulator: Markov draw beyond the last cumulative weight (simulate.jl:148)",
+    ST_DUP_KNOT: "a stored line repeats an abscissa (intersection at a shared turning point, envelope.jl:199,212,248-252)",
+    ST_EXTRA_RIGHT: "info: insert_right longer than insert_left, surplus dropped (dc_algo.jl:486-492)",
+    ST_NONMONO_FIRST: "info: a period-1 line is not strictly increasing (never interpolated by the solve)",
 }
 
 MODEL_F, MODEL_G, MODEL_MINIMAL = 1, 2, 3

@@ -20,6 +20,7 @@ EXPORTS = [
     "dcegm_status", "dcegm_summaries", "dcegm_summaries_to_device", "dcegm_last_timing", "dcegm_upload_f",
     "dcegm_upload_g", "dcegm_upload_minimal", "dcegm_run", "dcegm_debug_math_check", "dcegm_debug_dfma_rate", "dcegm_solve_f_packed", "dcegm_solve_g_packed",
     "dcegm_simulate", "dcegm_fetch_sim_moments", "dcegm_fetch_sim_panel", "dcegm_sim_moments_to_device", "dcegm_solve_minimal_borrow", "dcegm_solve_minimal_bequest",
+    "dcegm_sweep_record_bytes", "dcegm_sweep_records_to_device",
 ]
 
 
@@ -59,6 +60,8 @@ def load():
     lib.dcegm_fetch_sim_moments.argtypes = [H, C.c_int, C.c_int, dp, ip, ip]
     lib.dcegm_fetch_sim_panel.argtypes = [H, C.c_int, dp, dp, dp, dp, dp, dp, ip, ip, ip]
     lib.dcegm_sim_moments_to_device.argtypes = [H, C.c_void_p, C.c_size_t]
+    lib.dcegm_sweep_record_bytes.argtypes = [C.c_int]
+    lib.dcegm_sweep_records_to_device.argtypes = [H, C.c_void_p, C.c_size_t, C.c_int]
     lib.dcegm_run.argtypes = [H]
     lib.dcegm_get_layout.argtypes = [H, C.POINTER(_abi.dcegm_layout)]
     lib.dcegm_fetch_line.argtypes = [H, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, dp, C.c_int, C.POINTER(C.c_int)]
@@ -78,7 +81,9 @@ def load():
     lib.dcegm_debug_math_check.argtypes = [C.c_ulonglong, C.c_ulonglong, C.c_int, C.c_int, C.POINTER(C.c_ulonglong)]
     for name in EXPORTS:
         fn = getattr(lib, name)  # AttributeError here means the library does not match include/dcegm.h
-        if name not in ("dcegm_last_error", "dcegm_param_defaults"):
+        if name == "dcegm_sweep_record_bytes":
+            fn.restype = C.c_size_t
+        elif name not in ("dcegm_last_error", "dcegm_param_defaults"):
             fn.restype = C.c_int
     if lib.dcegm_abi_version() != _abi.ABI_VERSION:
         raise RuntimeError("libdcegm_cuda.so ABI version mismatch")

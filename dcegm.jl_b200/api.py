@@ -131,6 +131,7 @@ class _Indexed:
 
 _STATUS_ERRORS = {
     _abi.ST_NONMONOTONE: "knot-vectors must be unique and sorted in increasing order",  # Interpolations.jl, line.jl:236
+    _abi.ST_DUP_KNOT: "knot-vectors must be unique and sorted in increasing order",    # duplicate knot (envelope.jl:212,248-252)
     _abi.ST_NO_BRACKET: "ArgumentError: The interval [a,b] is not a bracketing interval",  # Roots.fzero, envelope.jl:199
     _abi.ST_ALL_FALLING: "an upper envelope requires by definition at least 2 lines.",      # envelope.jl:149-151
     _abi.ST_MISALIGNED: "BoundsError: insert_right shorter than insert_left",               # dc_algo.jl:486-491
@@ -144,6 +145,7 @@ _STATUS_ERRORS = {
 
 
 def _raise_for_status(st):
+    st &= _abi.ST_FATAL_MASK  # informational bits: the reference returns normally (include/dcegm.h)
     if st:
         raise DCEGMError("; ".join(t for b, t in _STATUS_ERRORS.items() if st & b) + f" (status 0x{st:x})")
 

@@ -25,6 +25,8 @@ cudaError_t launch_pack_lines(const DeviceBatch& B, int first, int count, const 
                               cudaStream_t stream);
 cudaError_t launch_chunk_offsets(const int32_t* lens, size_t nsl, int cap, long long* d_off, long long* h_off_mapped,
                                  cudaStream_t stream);
+cudaError_t launch_sweep_records(const dcegm_summary* summ, const double* mom, const int32_t* sim_status, int nmodels, int nT,
+                                 int nT_pad, size_t rec_bytes, unsigned char* dst, cudaStream_t stream);
 cudaError_t launch_sim(const DeviceBatch& B, const SimBatch& Sb, int first, int count, cudaStream_t stream);
 size_t sim_smem_bytes(const dcegm_layout& l);
 size_t solver_f_smem_bytes(int cap, int isec_cap);
@@ -598,6 +600,24 @@ int dcegm_summaries_to_device(dcegm_handle h, void* dst_device, size_t bytes) {
     const size_t need = sizeof(dcegm_summary) * (size_t)h->batch.lay.nmodels;
     if (!dst_device || bytes < need) return fail(h, DCEGM_E_CAPACITY, "dcegm_summaries_to_device: destination too small");
     CK(cudaMemcpyAsync(dst_device, h->batch.summaries, need, cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return DCEGM_OK;
+}
+
+size_t dcegm_sweep_record_bytes(int nT_pad) {
+    return sizeof(dcegm_summary) + 8 + sizeof(double) * (size_t)(nT_pad > 0 ? nT_pad : 0) * DCEGM_SIM_NMOM;
+}
+
+int dcegm_sweep_records_to_device(dcegm_handle h, void* dst_device, size_t bytes, int nT_pad) {
+    int rc = need_solution(h);
+    if (rc) return rc;
+    const dcegm_layout& l = h->batch.lay;
+    if (nT_pad < l.nT) return fail(h, DCEGM_E_INVALID, "dcegm_sweep_records_to_device: nT_pad < nT");
+    const size_t rec = dcegm_sweep_record_bytes(nT_pad);
+    if (!dst_device || bytes < rec * (size_t)l.nmodels) return fail(h, DCEGM_E_CAPACITY, "dcegm_sweep_records_to_device: destination too small");
+    cudaError_t e = launch_sweep_records(h->batch.summaries, h->simulated ? (const double*)h->mom.p : nullptr,
+                                         (const int32_t*)h->sstat.p, l.nmodels, l.nT, nT_pad, rec, (unsigned char*)dst_device, h->stream);
+    if (e != cudaSuccess) return cuda_fail(h, e, "sweep record kernel");
     CK(cudaStreamSynchronize(h->stream));
     return DCEGM_OK;
 }

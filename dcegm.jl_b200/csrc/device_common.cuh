@@ -328,6 +328,19 @@ __device__ __forceinline__ int count_le_indexed(const KnotIndex& K, const double
     return count_le_indexed_at(reinterpret_cast<const unsigned short*>(dc_smem + K.tab), K, x, n, q);
 }
 
+// status bit of a knot pair x0, x1 (consecutive abscissae of a stored line) the previous period's interpolate()
+// rejects: DCEGM_ST_DUP_KNOT for equal knots, DCEGM_ST_NONMONOTONE for a decreasing (or unordered, NaN) pair; in the
+// first period — whose lines no step of the solve interpolates (dc_algo.jl:22-37 reads it+1 only) — the
+// informational DCEGM_ST_NONMONO_FIRST for both.  0 when x1 > x0.
+__device__ __forceinline__ int knot_pair_flag(double x0, double x1, bool first_period) {
+    if (x1 > x0) return 0;
+    if (first_period) return (int)DCEGM_ST_NONMONO_FIRST;
+    return x1 == x0 ? (int)DCEGM_ST_DUP_KNOT : (int)DCEGM_ST_NONMONOTONE;
+}
+// status bits after which the knot vectors of a model are not strictly increasing (or not finite): the bucket index
+// is not exact there and the EGM step takes its generic path (binary searches)
+constexpr int kStatusNoIndex = (int)(DCEGM_ST_NONMONOTONE | DCEGM_ST_DUP_KNOT | DCEGM_ST_NONFINITE);
+
 // whole-Point interpolation on a 2-point line (dc_algo.jl:446-478)
 __device__ __forceinline__ double2 interp2pt(double2 a, double2 b, double q) {
     if (b.x < a.x) {  // sortx!(newleft)

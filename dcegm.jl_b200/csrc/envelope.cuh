@@ -231,7 +231,7 @@ template <class ES, int NT = kThreads>
 __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0, double ev0, const DevModel& p,
                                        double* Vx, double* Vy, int* nV, double* Cx, double* Cy, int* nC,
                                        dcegm_env_meta* meta_out, double2* isects_out, uint32_t* removed_out,
-                                       int rem_words) {
+                                       int rem_words, bool first_period = false) {
     const int tid = threadIdx.x;
     unsigned status = 0;
 
@@ -639,7 +639,10 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             }
         __syncthreads();
         const int nl = S.cnt()[0], nr = S.cnt()[1];
-        if (nl != nr) status |= DCEGM_ST_MISALIGNED;
+        // the reference's loop runs over insert_left and indexes insert_right with it (dc_algo.jl:486-492): a shorter
+        // insert_right is a BoundsError, a longer one is silently ignored
+        if (nr < nl) status |= DCEGM_ST_MISALIGNED;
+        if (nr > nl) status |= DCEGM_ST_EXTRA_RIGHT;
         // insert!(…) pairs (dc_algo.jl:486-492).  The reference inserts one pair after the other, each before
         // the first x greater than its left point in the line as it stands.  When the surviving policy is
         // ascending and every pair lies at or right of the pair before it (the regular case: intersections come
@@ -647,7 +650,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         // q_i = #{x <= left_i}, behind the i pairs before it.  Anything else takes the sequential path below.
         bool merged = false;
         constexpr bool kTryMerge = ES::kLongLines;  // at ~500 points the sequential path is as fast (measured)
-        if (kTryMerge && nl > 0 && nl == nr && ncur + 2 * nl <= S.cap - 1) {
+        if (kTryMerge && nl > 0 && nl <= nr && ncur + 2 * nl <= S.cap - 1) {
             int irregular = 0;
             DC_ENV_UNROLL
             for (int k = tid; k + 1 < ncur; k += NT) irregular |= Cx[1 + k + 1] < Cx[1 + k];
@@ -866,16 +869,16 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         }
         __syncthreads();
     }
-    // status: knot vectors the next period's interpolate() would reject, non-finite entries
+    // status: knot vectors the previous period's interpolate() would reject (knot_pair_flag), non-finite entries
     int flag = 0;
     DC_ENV_UNROLL
     for (int k = tid; k < lenC; k += NT) {
-        if (k + 1 < lenC && !(Cx[k + 1] > Cx[k])) flag |= DCEGM_ST_NONMONOTONE;
+        if (k + 1 < lenC) flag |= knot_pair_flag(Cx[k], Cx[k + 1], first_period);
         if (!isfinite(Cx[k]) || !isfinite(Cy[k])) flag |= DCEGM_ST_NONFINITE;
     }
     DC_ENV_UNROLL
     for (int k = tid; k < lenV; k += NT) {
-        if (k + 1 < lenV && !(Vx[k + 1] > Vx[k])) flag |= DCEGM_ST_NONMONOTONE;
+        if (k + 1 < lenV) flag |= knot_pair_flag(Vx[k], Vx[k + 1], first_period);
         if (!isfinite(Vx[k]) || !isfinite(Vy[k])) flag |= DCEGM_ST_NONFINITE;
     }
     if (flag || status) atomicOr(&S.cnt()[2], flag | (int)status);

@@ -218,7 +218,7 @@ static DevModel make_dev(const dcegm_param& p) {
 
 bool build_tables(int model, const dcegm_param* params, int nmodels, HostTables& out, const char** why) {
     static const char* kWhy[] = {"nmodels must be positive", "all models of one call must share na, ny and nT",
-                                 "na >= 2, ny >= 1, nT >= 2, nD == 2 required", "quad_group must be a power of two <= 32",
+                                 "na >= 2, ny >= 1, nT >= 2, nD == 2 required", "quad_group > 1 (lane-group quadrature sums) is not implemented by the kernels: pass 0 or 1",
                                  "unknown model kind"};
     if (nmodels <= 0 || !params) {
         *why = kWhy[0];
@@ -235,8 +235,7 @@ bool build_tables(int model, const dcegm_param* params, int nmodels, HostTables&
             *why = kWhy[2];
             return false;
         }
-        int g = p.quad_group > 0 ? p.quad_group : 1;
-        if (g > 32 || (g & (g - 1))) {
+        if (p.quad_group > 1) {  // the kernels sum the nodes in ascending serial order
             *why = kWhy[3];
             return false;
         }

@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_f_kernel(DeviceBat
         // ---------------- 1. EGM step -----------------------------------------------------------------
         // fast path: straight-line node evaluation (bucket-indexed knot search, pow from shared
         // logarithms); see egm_node_generic for the conditions under which it does not apply
-        bool fast = model_fast && !beq && !(s_status & (DCEGM_ST_NONMONOTONE | DCEGM_ST_NONFINITE)) && N.n_wc >= 2 &&
+        bool fast = model_fast && !beq && !(s_status & kStatusNoIndex) && N.n_wc >= 2 &&
                           N.n_wv >= 2 && N.n_r >= 2;
         KnotIndex Kr, Kc, Kv;
         Kr.tab = tab0;
@@ -234,9 +234,11 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_f_kernel(DeviceBat
 
         // ---------------- 2. worker: secondary envelope + policy repair -----------------------------
         const size_t ss = state_slot(B.lay, m, t, 0);
+        // lines of the first period are never interpolated by the solve (dc_algo.jl:22-37 reads it+1 only)
+        const bool first_period = t == 0;
         worker_envelope(S, koff, na, a0, ev0w, p, C.wv_x(), C.wv_y(), &s_n[0], C.wc_x(), C.wc_y(), &s_n[1], B.meta + ss,
                         B.isects + ss * (size_t)B.lay.isec_cap, B.removed + ss * (size_t)B.lay.rem_words,
-                        B.lay.rem_words);
+                        B.lay.rem_words, first_period);
         C.n_wv = s_n[0];
         C.n_wc = s_n[1];
         C.vb_w = ev0w;
@@ -253,7 +255,7 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_f_kernel(DeviceBat
         __syncthreads();
         int flag = 0;
         for (int k = tid; k < na + 1; k += kThreads) {
-            if (k + 1 < na + 1 && !(C.r_x()[k + 1] > C.r_x()[k])) flag |= DCEGM_ST_NONMONOTONE;
+            if (k + 1 < na + 1) flag |= knot_pair_flag(C.r_x()[k], C.r_x()[k + 1], first_period);
             if (!isfinite(C.r_x()[k]) || !isfinite(C.rc_y()[k]) || !isfinite(C.rv_y()[k])) flag |= DCEGM_ST_NONFINITE;
         }
         if (flag) atomicOr(&s_status, flag);
@@ -354,12 +356,9 @@ cudaError_t launch_solve_f(const DeviceBatch& B0, int first, int count, cudaStre
     DeviceBatch B = B0;
     B.first = first;
     const size_t smem = FPlan(B.lay.cap, B.lay.isec_cap).bytes();
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(solve_f_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
-    }
+    // the attribute is per device and the call is cheap: set on every launch (several handles / GPUs per process)
+    cudaError_t e = cudaFuncSetAttribute(solve_f_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
     solve_f_kernel<<<count, kThreads, smem, stream>>>(B);
     return cudaGetLastError();
 }

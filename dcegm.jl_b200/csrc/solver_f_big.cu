@@ -89,7 +89,7 @@ __device__ __forceinline__ LineSetG big_set(const BigPlan& P, unsigned char* g, 
 template <int NT>
 __device__ inline void big_build_index(const BigPlan& P, unsigned char* g, BigState* st, const LineSetG& L, int status) {
     const int tid = threadIdx.x;
-    const bool ok = !(status & (DCEGM_ST_NONMONOTONE | DCEGM_ST_NONFINITE)) && L.n_wc >= 2 && L.n_wv >= 2 && L.n_r >= 2;
+    const bool ok = !(status & kStatusNoIndex) && L.n_wc >= 2 && L.n_wv >= 2 && L.n_r >= 2;
     KnotIndex Kr, Kc, Kv;
     Kr.tab = Kc.tab = Kv.tab = 0;
     Kr.lo = Kc.lo = Kv.lo = Kr.inv = Kc.inv = Kv.inv = 0.0;
@@ -386,8 +386,9 @@ __global__ void __launch_bounds__(kEnvThreads) big_env_kernel(DeviceBatch B, uns
 
     // worker: secondary envelope + policy repair
     const size_t ss = state_slot(B.lay, m, t, 0);
+    const bool first_period = t == 0;  // see solve_f_kernel
     worker_envelope<EnvScratchG, kEnvThreads>(S, koff, na, a0, ev0w, p, C.wv_x(), C.wv_y(), &s_n[0], C.wc_x(), C.wc_y(), &s_n[1], B.meta + ss,
-                    B.isects + ss * (size_t)B.lay.isec_cap, B.removed + ss * (size_t)B.lay.rem_words, B.lay.rem_words);
+                    B.isects + ss * (size_t)B.lay.isec_cap, B.removed + ss * (size_t)B.lay.rem_words, B.lay.rem_words, first_period);
     C.n_wv = s_n[0];
     C.n_wc = s_n[1];
     C.vb_w = ev0w;
@@ -404,7 +405,7 @@ __global__ void __launch_bounds__(kEnvThreads) big_env_kernel(DeviceBatch B, uns
     __syncthreads();
     int flag = 0;
     for (int k = tid; k < na + 1; k += kEnvThreads) {
-        if (k + 1 < na + 1 && !(C.r_x()[k + 1] > C.r_x()[k])) flag |= DCEGM_ST_NONMONOTONE;
+        if (k + 1 < na + 1) flag |= knot_pair_flag(C.r_x()[k], C.r_x()[k + 1], first_period);
         if (!isfinite(C.r_x()[k]) || !isfinite(C.rc_y()[k]) || !isfinite(C.rv_y()[k])) flag |= DCEGM_ST_NONFINITE;
     }
     if (flag) {

@@ -232,6 +232,7 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBat
         // ---- C. per state: envelope, credit-constraint point, checks, store ---------------------------
         for (int iy = 0; iy < ny; iy++) {
             const size_t ss = state_slot(B.lay, m, t, iy);
+            const bool first_period = t == 0;  // see solve_f_kernel
             const double ev0w = P.vb(iy)[2], ev0r = P.vb(iy)[3];
             if (B.dirty) {
                 double2* d = B.dirty + line_slot(B.lay, m, t, iy, 0, 0) * (size_t)na;
@@ -251,7 +252,7 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBat
             __syncthreads();
             worker_envelope(S, koff, na, a0, ev0w, p, P.line(iy, 2), P.line(iy, 3), &s_n[0], P.line(iy, 0),
                             P.line(iy, 1), &s_n[1], B.meta + ss, B.isects + ss * (size_t)B.lay.isec_cap,
-                            B.removed + ss * (size_t)B.lay.rem_words, B.lay.rem_words);
+                            B.removed + ss * (size_t)B.lay.rem_words, B.lay.rem_words, first_period);
             const int n_wv = s_n[0], n_wc = s_n[1], n_r = na + 1;
             if (tid == 0) {
                 P.line(iy, 4)[0] = a0;
@@ -268,7 +269,7 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBat
             {
                 const double* rx = P.line(iy, 4);
                 for (int k = tid; k < n_r; k += kThreads) {
-                    if (k + 1 < n_r && !(rx[k + 1] > rx[k])) flag |= DCEGM_ST_NONMONOTONE;
+                    if (k + 1 < n_r) flag |= knot_pair_flag(rx[k], rx[k + 1], first_period);
                     if (!isfinite(rx[k]) || !isfinite(P.line(iy, 5)[k]) || !isfinite(P.line(iy, 6)[k])) flag |= DCEGM_ST_NONFINITE;
                 }
             }

@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(kThreads) solve_minimal_kernel(DeviceBatch B) 
         __syncthreads();
         int flag = 0;
         for (int k = tid; k < na; k += nthr)
-            if (!(cx[k + 1] > cx[k])) flag = DCEGM_ST_NONMONOTONE;
+            flag |= knot_pair_flag(cx[k], cx[k + 1], t == 0);
         if (flag) atomicOr(&s_status, flag);
         const size_t slot = line_slot(B.lay, m, t, 0, 0, DCEGM_KIND_C);
         if (tid == 0) B.lens[slot] = na + 1;
@@ -132,11 +132,9 @@ cudaError_t launch_solve_minimal(const DeviceBatch& B0, int first, int count, cu
     DeviceBatch B = B0;
     B.first = first;
     const size_t smem = (size_t)6 * (B.lay.na + 1) * sizeof(double);
-    static size_t configured = 48 * 1024;
-    if (smem > configured) {
+    if (smem > 48 * 1024) {  // per device, set on every launch (several handles / GPUs per process)
         cudaError_t e = cudaFuncSetAttribute(solve_minimal_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        configured = smem;
     }
     int nthr = (B.lay.na + 1 + 31) / 32 * 32;  // a thread per grid point
     nthr = nthr > kThreads ? kThreads : nthr;
@@ -216,6 +214,34 @@ cudaError_t launch_pack_lines(const DeviceBatch& B, int first, int count, const 
     const size_t nsl = per * count;
     if (nsl == 0) return cudaSuccess;
     pack_lines_kernel<<<(unsigned)nsl, 128, 0, stream>>>(B.lines, d_offsets, B.lay.cap, per * first, d_dst);
+    return cudaGetLastError();
+}
+
+// One fixed-size record per model for the single all-gather of a multi-GPU sweep (include/dcegm.h:
+// dcegm_sweep_record_bytes): [dcegm_summary | int32 sim_status | int32 nT | double moments[nT_pad][DCEGM_SIM_NMOM]].
+// Moments are NaN when no simulation ran, beyond nT, and for models whose solution the simulator must not be
+// trusted on: any fatal status bit, or a first-period line that is not strictly increasing (sim interpolates period 1).
+__global__ void sweep_records_kernel(const dcegm_summary* __restrict__ summ, const double* __restrict__ mom,
+                                     const int32_t* __restrict__ sim_status, int nT, int nT_pad, size_t rec_bytes,
+                                     unsigned char* __restrict__ dst) {
+    const int m = blockIdx.x;
+    unsigned char* r = dst + (size_t)m * rec_bytes;
+    const dcegm_summary sm = summ[m];
+    if (threadIdx.x == 0) {
+        *reinterpret_cast<dcegm_summary*>(r) = sm;
+        int32_t* tail = reinterpret_cast<int32_t*>(r + sizeof(dcegm_summary));
+        tail[0] = mom ? sim_status[m] : -1;
+        tail[1] = nT;
+    }
+    double* out = reinterpret_cast<double*>(r + sizeof(dcegm_summary) + 8);
+    const bool masked = !mom || ((unsigned)sm.status & (DCEGM_ST_FATAL_MASK | DCEGM_ST_NONMONO_FIRST)) != 0;
+    const double nan = __longlong_as_double(0x7ff8000000000000LL);
+    for (int k = threadIdx.x; k < nT_pad * DCEGM_SIM_NMOM; k += blockDim.x)
+        out[k] = (masked || k >= nT * DCEGM_SIM_NMOM) ? nan : mom[(size_t)m * nT * DCEGM_SIM_NMOM + k];
+}
+cudaError_t launch_sweep_records(const dcegm_summary* summ, const double* mom, const int32_t* sim_status, int nmodels, int nT,
+                                 int nT_pad, size_t rec_bytes, unsigned char* dst, cudaStream_t stream) {
+    sweep_records_kernel<<<nmodels, 128, 0, stream>>>(summ, mom, sim_status, nT, nT_pad, rec_bytes, dst);
     return cudaGetLastError();
 }
 

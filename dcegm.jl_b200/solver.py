@@ -186,6 +186,11 @@ class Solver:
         self._ck(self.lib.dcegm_summaries(self.h, arr))
         return np.frombuffer(arr, dtype=SUMMARY_DTYPE).copy()
 
+    def sweep_records_to_device(self, ptr, nbytes, nT_pad):
+        """one fixed-size record per model (summary + simulation status + moments padded to nT_pad periods) into
+        device memory: the send buffer of the one all-gather of a sweep (dcegm_sweep_records_to_device)"""
+        self._ck(self.lib.dcegm_sweep_records_to_device(self.h, C.c_void_p(ptr), nbytes, int(nT_pad)))
+
     def summaries_to_device(self, ptr, nbytes):
         self._ck(self.lib.dcegm_summaries_to_device(self.h, C.c_void_p(ptr), nbytes))
 

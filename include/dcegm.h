@@ -48,10 +48,12 @@ extern "C" {
 #define DCEGM_ST_OK              0u
 #define DCEGM_ST_ISECT_OVERFLOW  (1u << 0) /* more intersections than isec_cap */
 #define DCEGM_ST_LINE_OVERFLOW   (1u << 1) /* a line outgrew `cap` points */
-#define DCEGM_ST_NONMONOTONE     (1u << 2) /* a stored line is not strictly increasing in x: the next
-                                              period's interpolate() throws (line.jl:236) */
+#define DCEGM_ST_NONMONOTONE     (1u << 2) /* a stored line of a period > 1 has DECREASING (or unordered) abscissae: the
+                                              previous period's interpolate() throws in every Interpolations.jl
+                                              version ("knot-vectors must be sorted", line.jl:236) */
 #define DCEGM_ST_NO_BRACKET      (1u << 3) /* fzero without sign change (envelope.jl:199,225-228) */
-#define DCEGM_ST_MISALIGNED      (1u << 4) /* insert_left / insert_right lengths differ (dc_algo.jl:486-491) */
+#define DCEGM_ST_MISALIGNED      (1u << 4) /* insert_right shorter than insert_left: insert_right[ileft] is a BoundsError
+                                              (dc_algo.jl:486-491) */
 #define DCEGM_ST_ALL_FALLING     (1u << 5) /* splitLine returned no section (envelope.jl:97-104) */
 #define DCEGM_ST_NONFINITE       (1u << 6) /* NaN/Inf in a computed line */
 #define DCEGM_ST_SEG_OVERFLOW    (1u << 7) /* more sections than seg_cap */
@@ -59,6 +61,22 @@ extern "C" {
 #define DCEGM_ST_LOOP_LIMIT      (1u << 9) /* third-line loop did not terminate (envelope.jl:197-240) */
 #define DCEGM_ST_NEG_CONS        (1u << 10) /* simulator: negative consumption, the reference calls error() (simulate.jl:111-116) */
 #define DCEGM_ST_YSTATE_RANGE    (1u << 11) /* simulator: Markov draw beyond the last cumulative weight (simulate.jl:148 would index out of bounds) */
+#define DCEGM_ST_DUP_KNOT        (1u << 14) /* a stored line of a period > 1 repeats an abscissa (non-decreasing, not strictly
+                                               increasing).  The reference's own upper_env produces this whenever an
+                                               intersection is found AT a turning point shared by two sections
+                                               (envelope.jl:199 f(pt1) == 0, :212 and :248-252 push the point twice).
+                                               interpolate() then throws in Interpolations.jl versions that require
+                                               unique knots; the lines stored here are what a version without that
+                                               check computes (searchsortedlast never selects the empty cell). */
+/* Informational bits: the reference returns normally from runf/rung on these models; they neither raise in
+ * the host mirror nor remove a model from throughput counts (DCEGM_ST_FATAL_MASK excludes them). */
+#define DCEGM_ST_EXTRA_RIGHT     (1u << 12) /* insert_right LONGER than insert_left: the loop of dc_algo.jl:486-492 runs over
+                                               insert_left only, the surplus right points are silently dropped */
+#define DCEGM_ST_NONMONO_FIRST   (1u << 13) /* a line of the FIRST period is not strictly increasing in x.  The solve never
+                                               interpolates period 1 (dc_algo.jl:22-37 reads it+1 only), so runf returns
+                                               normally; sim() / plots that interpolate period 1 would throw (line.jl:236) */
+#define DCEGM_ST_INFO_MASK       (DCEGM_ST_EXTRA_RIGHT | DCEGM_ST_NONMONO_FIRST)
+#define DCEGM_ST_FATAL_MASK      (~DCEGM_ST_INFO_MASK)
 
 /* ---- model parameters: POD mirror of `mutable struct Param` ----------------
  * reference: src/param.jl:33-70, defaults src/param.json, SURVEY.md App. C.
@@ -295,6 +313,14 @@ int  dcegm_fetch_sim_moments(dcegm_handle h, int first, int count, double* momen
 /* device-to-device copy of the moments (nmodels*nT*DCEGM_SIM_NMOM doubles) into caller-provided device
  * memory: the second part of the allgather payload of a multi-GPU sweep */
 int  dcegm_sim_moments_to_device(dcegm_handle h, void* dst_device, size_t bytes);
+/* The payload of the ONE all-gather of a multi-GPU sweep: one fixed-size record per model of the
+ * resident batch, written to caller-provided DEVICE memory (the NCCL send buffer):
+ *   [ dcegm_summary | int32 sim_status (-1: not simulated) | int32 nT | double moments[nT_pad][DCEGM_SIM_NMOM] ]
+ * nT_pad >= nT lets batches of different nT share one record size (a sweep over grid sizes runs one solve per
+ * (na, ny, nT) group).  Moments are NaN beyond nT, when dcegm_simulate has not run, and for models whose status has a
+ * fatal bit or DCEGM_ST_NONMONO_FIRST (sim() interpolates period 1): a flagged model's moments are not a result. */
+size_t dcegm_sweep_record_bytes(int nT_pad);
+int  dcegm_sweep_records_to_device(dcegm_handle h, void* dst_device, size_t bytes, int nT_pad);
 /* one model's panel, column-major [agent + nsims*it] like the reference's matrices; ret_age [nsims].
  * Any destination may be NULL. */
 int  dcegm_fetch_sim_panel(dcegm_handle h, int model, double* w0, double* w1, double* cons, double* util,

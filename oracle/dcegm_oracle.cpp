@@ -348,6 +348,19 @@ inline bool strictly_increasing(const Line& L) {
         if (!(L[k].x > L[k - 1].x)) return false;
     return true;
 }
+// status bits of a stored line whose knot vector interpolate() (line.jl:236) rejects; it = 1-based period of the line.
+// Period-1 lines are never interpolated by the solve (dc_algo.jl:22-37 reads it+1 only): informational bit.
+inline unsigned knot_flags(const Line& L, int it) {
+    unsigned f = 0;
+    for (size_t k = 1; k < L.size(); k++) {
+        if (L[k].x > L[k - 1].x) continue;
+        if (it == 1)
+            f |= DCEGM_ST_NONMONO_FIRST;
+        else
+            f |= L[k].x == L[k - 1].x ? DCEGM_ST_DUP_KNOT : DCEGM_ST_NONMONOTONE;
+    }
+    return f;
+}
 
 // line.jl:40,348-351 — stable sort on x only
 inline void sortx(Line& L) {
@@ -678,7 +691,10 @@ void do_secondary(Line& vline, Line& cline, bool working, double ev0, const Par&
         for (int k = 0; k < nc; k++)
             if (!isrm[k]) kept.push_back(cout[k]);
         cout.swap(kept);
-        if (ins_left.size() != ins_right.size()) *status |= DCEGM_ST_MISALIGNED;
+        // the loop below runs over insert_left and indexes insert_right with it: a shorter insert_right is a
+        // BoundsError, a longer one is silently ignored
+        if (ins_right.size() < ins_left.size()) *status |= DCEGM_ST_MISALIGNED;
+        if (ins_right.size() > ins_left.size()) *status |= DCEGM_ST_EXTRA_RIGHT;
         // dc_algo.jl:486-492
         for (size_t i = 0; i < ins_left.size(); i++) {
             int j = -1;
@@ -817,13 +833,15 @@ void store_env(const OutView& o, int m, int it, int iy, const Envelope& e, unsig
 }
 
 // tail of a period step — dc_algo.jl:94-101 / 194-201
-void finish_step(Envelope& v, Envelope& c, double a0, double ev0, unsigned* status) {
+// it: 1-based period of the step.  Lines of period 1 are never interpolated by the solve (dc_algo.jl:22-37 reads
+// it+1 only): a defect there is informational (DCEGM_ST_NONMONO_FIRST), runf returns normally.
+void finish_step(Envelope& v, Envelope& c, double a0, double ev0, int it, unsigned* status) {
     v.vbound = ev0;
     c.env.insert(c.env.begin(), Pt{a0, 0.0});
     v.env.insert(v.env.begin(), Pt{a0, ev0});
     sortx(c.env);
-    // a line the next period's interpolate() would reject
-    if (!strictly_increasing(c.env) || !strictly_increasing(v.env)) *status |= DCEGM_ST_NONMONOTONE;
+    // a line the previous period's interpolate() would reject
+    *status |= knot_flags(c.env, it) | knot_flags(v.env, it);
     for (auto& q : c.env)
         if (!std::isfinite(q.x) || !std::isfinite(q.y)) *status |= DCEGM_ST_NONFINITE;
     for (auto& q : v.env)
@@ -920,7 +938,7 @@ void solve_f_one(const dcegm_param& pin, int m, const OutView& o, int literal, i
                     evn.env = vline;
                     ecn.env = cline;
                 }
-                finish_step(evn, ecn, avec[0], ev0, &status);
+                finish_step(evn, ecn, avec[0], ev0, it, &status);
                 c[at(id - 1, it - 1)] = ecn;
                 v[at(id - 1, it - 1)] = evn;
             }
@@ -1032,7 +1050,7 @@ void solve_g_one(const dcegm_param& pin, int m, const OutView& o, int literal, i
                         evn.env = vline;
                         ecn.env = cline;
                     }
-                    finish_step(evn, ecn, avec[0], ev0, &status);
+                    finish_step(evn, ecn, avec[0], ev0, it, &status);
                     c[at(id - 1, iy, it - 1)] = ecn;
                     v[at(id - 1, iy, it - 1)] = evn;
                 }
@@ -1109,7 +1127,7 @@ void solve_minimal_one(const dcegm_param& pin, int m, const OutView& o, int mode
                 if (ia == 0) ev0 = ev;
             }
         }
-        if (!strictly_increasing(cur)) status |= DCEGM_ST_NONMONOTONE;
+        status |= knot_flags(cur, it);
         store_line(o, m, it - 1, 0, 0, DCEGM_KIND_C, cur, &status);
         if (beq) {
             curv[0] = Pt{m_lo, ev0};

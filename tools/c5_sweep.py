@@ -37,20 +37,19 @@ for i in range(per):
     a.lambda_ = float(10 ** rng.uniform(np.log10(2e-7), 0))
 dev = torch.device("cuda", local)
 nT = 25
-sb, rec = SUMMARY_DTYPE.itemsize * per, nT * _abi.SIM_NMOM * 8
-send, sendm = torch.empty(sb, dtype=torch.uint8, device=dev), torch.empty(rec * per, dtype=torch.uint8, device=dev)
+rd = sweep.record_dtype(nT)
+rec = rd.itemsize  # dcegm_summary + simulation status + per-period moments: ONE all-gather per sweep
+send = torch.empty(rec * per, dtype=torch.uint8, device=dev)
 
 
 def job(s):
     s.solve(_abi.MODEL_G, arr, fetch=False)
     t_solve = s.timing().kernel_ms
-    s.summaries_to_device(send.data_ptr(), sb)
-    out = sweep.gather_summaries(send, n, SUMMARY_DTYPE.itemsize, dist if world > 1 else None)
     s.simulate()
-    s.sim_moments_to_device(sendm.data_ptr(), rec * per)
-    outm = sweep.gather_summaries(sendm, n, rec, dist if world > 1 else None)
+    s.sweep_records_to_device(send.data_ptr(), rec * per, nT)
+    out = sweep.gather_records(send, n, rec, dist if world > 1 else None)
     torch.cuda.synchronize()
-    return out, outm, t_solve
+    return out, t_solve
 
 
 with Solver(local) as s:
@@ -61,19 +60,23 @@ with Solver(local) as s:
             dist.barrier()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        out, outm, t_solve = job(s)
+        out, t_solve = job(s)
         if world > 1:
             dist.barrier()
         dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         best = min(best, float(dt.item()))
-    summ = sweep.summaries_from_bytes(out)
+    recs = np.frombuffer(out.cpu().numpy().tobytes(), dtype=rd)
+    st = recs["summary"]["status"].astype(np.int64)
+    ok = int(((st & _abi.ST_FATAL_MASK) == 0).sum())  # only models without a fatal status bit count as solved
     if rank == 0:
+        names = {b: k for k, b in vars(_abi).items() if k.startswith("ST_") and isinstance(b, int) and b and (b & (b - 1)) == 0}
         print(json.dumps({"config": f"C5 sweep: {n} GModels (na=100, ny=5, nT=25) + {nsims} agents each on {world} GPU(s)",
-                          "n_gpus": world, "models": n, "seconds": best, "models_per_s": n / best,
-                          "agent_periods_per_s": n * nsims * nT / best, "solve_kernel_ms_rank0": t_solve,
-                          "allgather_bytes": int(out.numel() + outm.numel()),
-                          "flagged_solve": int((summ["status"] != 0).sum())}))
+                          "n_gpus": world, "models": n, "solved": ok, "seconds": best, "models_per_s": ok / best,
+                          "agent_periods_per_s_all_models": n * nsims * nT / best, "solve_kernel_ms_rank0": t_solve,
+                          "allgather_bytes": int(out.numel()), "collectives_per_sweep": 1,
+                          "status_bits": {names[1 << b]: int(((st >> b) & 1).sum()) for b in range(16) if ((st >> b) & 1).any()},
+                          "masked_moment_models": int(np.isnan(recs["moments"][:, 0, 2]).sum())}))
 if world > 1:
     dist.destroy_process_group()

@@ -18,6 +18,16 @@ args = sys.argv[1:] or ["c2", "c5"]
 rng = np.random.default_rng(25032020)
 
 
+def solved(st):
+    """models whose status carries no fatal bit: only these count as solved (informational bits do not matter)"""
+    return int(((st.astype(np.int64) & _abi.ST_FATAL_MASK) == 0).sum())
+
+
+def bits(st):
+    names = {b: n for n, b in vars(_abi).items() if n.startswith("ST_") and isinstance(b, int) and b and (b & (b - 1)) == 0}
+    return {names[1 << b]: int(((st >> b) & 1).sum()) for b in range(16) if ((st >> b) & 1).any()}
+
+
 def timed(f, reps=3):
     f()
     ts = []
@@ -37,9 +47,10 @@ with Solver(0) as s:
             arr[i].beta, arr[i].R = float(b), float(r)
         s.upload(_abi.MODEL_MINIMAL, arr)
         dt = timed(s.run)
+        ok = solved(s.status())
         print(json.dumps({"config": "C2 minimal EGM x4096 (na=100, nT=25)", "kernel_ms": s.timing().kernel_ms,
-                          "models_per_s": n / (s.timing().kernel_ms * 1e-3), "wall_ms": dt * 1e3,
-                          "flagged": int((s.status() != 0).sum())}))
+                          "models_per_s": ok / (s.timing().kernel_ms * 1e-3), "wall_ms": dt * 1e3, "models": n,
+                          "solved": ok, "status_bits": bits(s.status())}))
     if "c5" in args:
         k = args.index("c5")
         nsims = int(args[k + 1]) if len(args) > k + 1 and args[k + 1].isdigit() else 100000
@@ -59,9 +70,10 @@ with Solver(0) as s:
         s.simulate()
         ts = time.perf_counter() - t0
         mom, hist, st = s.sim_moments()
+        ok = solved(s.status())
         print(json.dumps({"config": f"C5 shard: GModel x{n} (na=100, ny=5, nT=25) + sim of {nsims} agents each",
-                          "solve_kernel_ms": kms, "models_per_s": n / (kms * 1e-3), "sim_s": ts,
-                          "agent_periods_per_s": n * nsims * 25 / ts, "flagged_solve": int((s.status() != 0).sum()),
+                          "solve_kernel_ms": kms, "models_per_s": ok / (kms * 1e-3), "sim_s": ts, "models": n, "solved": ok,
+                          "status_bits": bits(s.status()), "agent_periods_per_s_all_models": n * nsims * 25 / ts,
                           "flagged_sim": int((st != 0).sum()), "mean_cons_t1": float(np.nanmean(mom[:, 0, 2]))}))
     if "c4" in args:
         k = args.index("c4")
@@ -78,6 +90,5 @@ with Solver(0) as s:
         dt = time.perf_counter() - t0
         st = s.status()
         print(json.dumps({"config": f"C4 fine grid: FModel x{n} (na=20000, nT=50, ny=32)", "kernel_ms": s.timing().kernel_ms,
-                          "models_per_s": n / dt, "flagged": int((st != 0).sum()),
-                          "status_bits": {int(b): int(((st >> b) & 1).sum()) for b in range(12) if ((st >> b) & 1).any()},
+                          "models_per_s": solved(st) / dt, "models": n, "solved": solved(st), "status_bits": bits(st),
                           "launches": s.timing().n_launches}))
