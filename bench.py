@@ -21,32 +21,41 @@ sys.path.insert(0, ROOT)
 
 import numpy as np  # noqa: E402
 
+from bench_configs import c3_params, run_c2, run_c4, run_c5, status_counts  # noqa: E402
+
 NA, NT, NY = 500, 25, 5
 BATCH = 4096
 # 2 lines x 2 choices x 24 periods x 501 points x 16 B + terminal 128 B + param 248 B
 ALGO_BYTES_PER_MODEL = 2 * 2 * 24 * 501 * 16 + 128 + 248
-# dram__bytes_read.sum + dram__bytes_write.sum of solve_f_kernel per model, from the `ncu --set full` capture
-# summarised in profiles/r1g_ncu_summary.md (11.53 MB + 885.39 MB for 1184 models)
-NCU_DRAM_BYTES_PER_MODEL = (11.529984e6 + 885.387008e6) / 1184
-# sm__inst_executed_pipe_fp64.sum of solve_f_kernel per model (warp instructions), same capture series
-# (profiles/r1g_solve_f_metrics.csv: 978 056 424 for 1184 models)
-NCU_FP64_WARP_INST_PER_MODEL = 978056424 / 1184
 WORKLOAD = "C3: retirement model (FModel) batch, na=500, nT=25, ny=5, log10(lambda)~U(log10 2e-6, log10 0.2), sigma~U(0,0.6)"
+KERNEL_SOURCES = ["solver_f.cu", "device_common.cuh", "egm_node.cuh", "egm_point.inc", "envelope.cuh", "dc_math.h", "Makefile"]
+COUNTERS_FILE = os.path.join(ROOT, "profiles", "solve_f_counters.json")
 
 
-def c3_params(n, seed=25032020, offset=0, na=None):
-    from dcegm_jl_b200 import Param
-    from dcegm_jl_b200.param import params_array
+def kernel_source_hash():
+    """sha256 over the sources solve_f_kernel is built from: ties the ncu counters under profiles/ to a build
+    (the GPU box has no .git, so a content hash stands in for the commit)"""
+    import hashlib
 
-    rng = np.random.default_rng(seed)
-    lam = 10 ** rng.uniform(np.log10(2e-6), np.log10(0.2), size=offset + n)
-    sig = rng.uniform(0, 0.6, size=offset + n)
-    base = Param(par=dict(na=na or NA, beta=0.95, R=1.05, nT=NT, ny=NY)).to_c()
-    arr = params_array([base] * n)
-    for i in range(n):
-        arr[i].lambda_ = float(lam[offset + i])
-        arr[i].sigma = float(sig[offset + i])
-    return arr
+    h = hashlib.sha256()
+    for f in KERNEL_SOURCES:
+        with open(os.path.join(ROOT, "dcegm.jl_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
+def ncu_counters():
+    """per-model ncu counters of solve_f_kernel (DRAM bytes, FP64-pipe warp instructions) — only if they were
+    captured on exactly the kernel sources of this build (tools/ncu_counters_json.py writes the file)"""
+    try:
+        with open(COUNTERS_FILE) as f:
+            c = json.load(f)
+    except Exception:
+        return None, "no profiles/solve_f_counters.json"
+    now = kernel_source_hash()
+    if c.get("source_sha16") != now:
+        return None, f"profiles/solve_f_counters.json was captured on sources {c.get('source_sha16')}, this build is {now}: stale, not printed"
+    return c, f"ncu capture {c.get('capture')} on sources {now} ({c.get('models')} models)"
 
 
 class ClockSampler:
@@ -99,7 +108,7 @@ def measured_peak():
 
 
 def cpu_reference_run(nmodels, threads, seed_offset=0):
-    """The CPU restatement of the reference path (oracle/), all host threads.  Returns models/s."""
+    """The CPU restatement of the reference path (oracle/), `threads` host threads.  Returns models/s."""
     from dcegm_jl_b200 import _abi
     from oracle import oracle
 
@@ -108,8 +117,39 @@ def cpu_reference_run(nmodels, threads, seed_offset=0):
     t0 = time.perf_counter()
     sol = oracle.solve(_abi.MODEL_F, arr, nthreads=threads)
     dt = time.perf_counter() - t0
-    ok = int((sol.status == 0).sum())  # models on which the reference algorithm would throw do not count
+    ok, _ = status_counts(sol.status)  # models on which the reference algorithm would throw do not count
     return ok / dt, dt
+
+
+def parity_in_run(solver, arr, threads, chunk=256):
+    """Checker leg (outside every timed region): the benchmarked batch, resident on the GPU from the timed solves,
+    against the CPU oracle in portable-math mode — status words, line lengths, envelope metadata, removed-point
+    bitmasks and every stored point of every model, bit for bit."""
+    from dcegm_jl_b200 import _abi
+    from dcegm_jl_b200.param import params_array
+    from oracle import oracle
+
+    n = len(arr)
+    out = {"models": n, "oracle_mode": "portable (dc_math.h arithmetic)", "status_equal": True, "lens_equal": True,
+           "meta_equal": True, "removed_equal": True, "points_compared": 0, "points_differ": 0}
+    t0 = time.perf_counter()
+    for c0 in range(0, n, chunk):
+        cnt = min(chunk, n - c0)
+        ref = oracle.solve(_abi.MODEL_F, params_array([arr[i] for i in range(c0, c0 + cnt)]), nthreads=threads, portable=True)
+        gpu = solver.fetch(c0, cnt)
+        out["status_equal"] &= bool(np.array_equal(gpu.status, ref.status))
+        out["lens_equal"] &= bool(np.array_equal(gpu.lens, ref.lens))
+        out["meta_equal"] &= bool(np.array_equal(gpu.meta, ref.meta))
+        out["removed_equal"] &= bool(np.array_equal(gpu.removed, ref.removed))
+        k = np.arange(ref.lay.cap)
+        m = np.broadcast_to((k[None, None, None, None, None, :] < ref.lens[..., None])[..., None], ref.lines.shape)
+        x, y = gpu.lines[m].view(np.int64), ref.lines[m].view(np.int64)
+        out["points_compared"] += int(x.size // 2)
+        out["points_differ"] += int((x != y).reshape(-1, 2).any(axis=1).sum())
+    out["seconds"] = round(time.perf_counter() - t0, 1)
+    out["all_equal"] = bool(out["status_equal"] and out["lens_equal"] and out["meta_equal"] and out["removed_equal"]
+                            and out["points_differ"] == 0)
+    return out
 
 
 def run_reference(args):
@@ -128,6 +168,7 @@ def run_reference(args):
         tot_t += dt
         tot_n += v_ * dt
     v = tot_n / tot_t
+    v1, dt1 = cpu_reference_run(48, 1)
     out = {
         "impl": "reference", "metric": "models solved/sec (500pts x 25T retirement model)", "value": v,
         "unit": "models/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
@@ -136,7 +177,10 @@ def run_reference(args):
         "config": {"workload": WORKLOAD, "models_per_step": sample},
         "cpu_baseline": {"value": v, "unit": "models/s", "cores": threads, "kind": "port",
                          "sample": f"{sample} models of the C3 batch per step, C++ restatement of DCEGM.jl "
-                                   f"(julia unavailable on this box), one model per task on {threads} threads"},
+                                   f"(julia unavailable on this box), one model per task on {threads} threads",
+                         "one_thread": {"value": v1, "unit": "models/s", "cores": 1,
+                                        "sample": f"first 48 models of the batch, {dt1:.1f} s; the published Julia figure is "
+                                                  "7.94 models/s on one laptop core (README.md:118-128)"}},
         "e2e": {"value": v, "unit": "models/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -150,7 +194,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--batch", type=int, default=BATCH, help="models per GPU")
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline and parity_in_run legs")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C2 / C4 / C5 lines")
     ap.add_argument("--na", type=int, default=NA, help="savings grid points (experiments only; the metric is quoted at 500)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -221,57 +266,106 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     tot_ms_max = float(t.item())
     st = solver.status()
-    n_flagged = int((st != 0).sum())
-    # models flagged by status (the reference algorithm itself would throw there) are not
-    # counted as solved
-    t = torch.tensor([float(nper - n_flagged)], dtype=torch.float64, device="cuda")
+    n_ok, st_bits = status_counts(st)
+    # models with a fatal status bit (the reference algorithm itself fails there) are not counted as solved
+    t = torch.tensor([float(n_ok)], dtype=torch.float64, device="cuda")
     if dist:
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
     solved = float(t.item())
     value = solved * args.steps / (tot_ms_max * 1e-3)
 
     # ---- end to end through the C ABI with host buffers ("e2e") ------------------------------
-    # host Param array -> dcegm_solve_f (host model setup + H2D + kernels) -> every stored polyline
-    # copied densely packed into pinned host memory, plus lens/meta/status.
+    # host Param array -> dcegm_solve_f_compact (host model setup + H2D + kernels) -> every stored polyline delivered
+    # into pinned host memory in the compact line format (include/dcegm.h: ordinates + abscissa runs, lossless),
+    # plus offsets / lens / run counts / status.
     nslots = nper * lay.nT * lay.nstate * 4
-    offsets = np.zeros(nslots + 1, np.int64)
-    npts = C.c_int64()
-    op = offsets.ctypes.data_as(C.POINTER(C.c_int64))
-    lib.dcegm_fetch_packed(h, 0, nper, None, 0, op, C.byref(npts))
-    cap_pts = int(npts.value * 1.05) + 1024
-    pinned = C.c_void_p()
-    assert lib.dcegm_host_alloc(C.byref(pinned), cap_pts * 16) == 0
+    woff = np.zeros(nslots + 1, np.int64)
     lens_h = np.zeros(nslots, np.int32)
+    aux_h = np.zeros(nslots, np.int32)
     stat_h = np.zeros(nper, np.int32)
+    nw = C.c_int64()
+    lp, ip = C.POINTER(C.c_int64), C.POINTER(C.c_int32)
+    wp, lnp, axp = woff.ctypes.data_as(lp), lens_h.ctypes.data_as(ip), aux_h.ctypes.data_as(ip)
+    assert lib.dcegm_fetch_compact(h, 0, nper, None, 0, wp, lnp, axp, C.byref(nw)) == 0, lib.dcegm_last_error(h)
+    cap_words = int(nw.value * 1.05) + 4096
+    npts_total = int(lens_h.sum())
+    pinned = C.c_void_p()
+    assert lib.dcegm_host_alloc(C.byref(pinned), max(cap_words * 8, npts_total * 16 + 4096)) == 0
+    pin_d = C.cast(pinned, C.POINTER(C.c_double))
     h2d = C.sizeof(arr) + 8 * (lay.nT - 1) * 2 * lay.ny * nper + 8 * lay.ny * nper + 8 * lay.na + 200 * nper
 
     def e2e_step():
-        # one public call: host setup + H2D + chunked solve, packing and D2H overlapped with the kernels
-        rc = lib.dcegm_solve_f_packed(h, arr, nper, 0, C.cast(pinned, C.POINTER(C.c_double)), cap_pts, op, C.byref(npts))
+        # one public call: host setup + H2D + chunked solve; encoding and D2H overlapped with the kernels
+        rc = lib.dcegm_solve_f_compact(h, arr, nper, 0, pin_d, cap_words, wp, lnp, axp, C.byref(nw))
         assert rc == 0, lib.dcegm_last_error(h)
-        lib.dcegm_status(h, stat_h.ctypes.data_as(C.POINTER(C.c_int32)))
-        return npts.value * 16 + nslots * 4 + nper * 4
+        lib.dcegm_status(h, stat_h.ctypes.data_as(ip))
+        return nw.value * 8 + (nslots + 1) * 8 + nslots * 8 + nper * 4
 
-    for _ in range(2):
-        e2e_step()
-    if dist:
-        dist.barrier()
-    t0 = time.perf_counter()
-    d2h = 0
-    step_ms = []
-    for _ in range(args.steps):
-        t1 = time.perf_counter()
-        d2h = e2e_step()
-        step_ms.append((time.perf_counter() - t1) * 1e3)
-    e2e_s = time.perf_counter() - t0
-    if os.environ.get("DCEGM_TRACE"):
-        print("e2e step wall ms:", [round(x, 2) for x in step_ms], file=sys.stderr)
-    t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-    if dist:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = solved * args.steps / float(t.item())
+    def e2e_xy_step():
+        # the same with every point delivered as (x, y) pairs (Vector{Point} layout, 16 B per point)
+        npts = C.c_int64()
+        rc = lib.dcegm_solve_f_packed(h, arr, nper, 0, pin_d, npts_total + 256, wp, C.byref(npts))
+        assert rc == 0, lib.dcegm_last_error(h)
+        lib.dcegm_status(h, stat_h.ctypes.data_as(ip))
+        return npts.value * 16 + (nslots + 1) * 8 + nper * 4
+
+    def timed_e2e(fn, steps):
+        for _ in range(2):
+            fn()
+        if dist:
+            dist.barrier()
+        t0 = time.perf_counter()
+        nbytes, step_ms = 0, []
+        for _ in range(steps):
+            t1 = time.perf_counter()
+            nbytes = fn()
+            step_ms.append((time.perf_counter() - t1) * 1e3)
+        secs = time.perf_counter() - t0
+        if os.environ.get("DCEGM_TRACE"):
+            print("e2e step wall ms:", [round(x, 2) for x in step_ms], file=sys.stderr)
+        tt = torch.tensor([secs], dtype=torch.float64, device="cuda")
+        if dist:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return solved * steps / float(tt.item()), nbytes, nbytes * steps / secs / 1e9
+
+    e2e_xy_value, d2h_xy, _ = timed_e2e(e2e_xy_step, min(args.steps, 3))
+    e2e_value, d2h, d2h_gbs = timed_e2e(e2e_step, args.steps)
     clocks = sampler.stop() if rank == 0 else None  # sampled over both timed regions (device-resident and e2e)
+    gbs_all = None
+    if dist:  # per-rank device-to-host rates (the host side limits e2e on a multi-GPU box)
+        g = torch.zeros(world, dtype=torch.float64, device="cuda")
+        g[rank] = d2h_gbs
+        dist.all_reduce(g, op=dist.ReduceOp.SUM)
+        gbs_all = [round(float(x), 2) for x in g.tolist()]
+
+    # expansion of the delivered records into (x, y) points on the host threads (not part of e2e: the host mirror
+    # decodes lines lazily, per Envelope); checked here against the resident solution's packed points
+    expand = None
+    if rank == 0:
+        xy = np.empty((npts_total, 2))
+        off = np.zeros(nslots + 1, np.int64)
+        npts = C.c_int64()
+        threads = os.cpu_count() or 1
+        t0 = time.perf_counter()
+        rc = lib.dcegm_expand_compact(h, 0, nper, pin_d, wp, lnp, axp, xy.ctypes.data_as(C.POINTER(C.c_double)), npts_total,
+                                      off.ctypes.data_as(lp), C.byref(npts), threads)
+        t_exp = time.perf_counter() - t0
+        assert rc == 0, lib.dcegm_last_error(h)
+        ref_xy, ref_off = solver.fetch_packed()
+        expand = {"ms": t_exp * 1e3, "threads": threads, "points": int(npts.value),
+                  "equals_packed_points_bitwise": bool(xy.tobytes() == ref_xy.tobytes() and np.array_equal(off, ref_off))}
+        del xy, ref_xy
     lib.dcegm_host_free(pinned)
+
+    configs = None
+    if not args.no_configs:
+        configs = {}
+        if world == 1:
+            configs["c2"] = run_c2(solver)
+            configs["c4"] = run_c4(solver)
+        configs["c5"] = run_c5(solver, local, world, rank, dist)
+        solver.upload(_abi.MODEL_F, arr)  # the benchmarked batch back into residence for the parity leg
+        solver.run()
 
     if rank == 0:
         peak, peak_src = measured_peak()
@@ -279,9 +373,13 @@ def main():
         # FP64 issue rate of this GPU, measured now (independent DFMA chains at full occupancy)
         dfma, dfma_ms = C.c_double(), C.c_double()
         lib.dcegm_debug_dfma_rate(local, C.byref(dfma), C.byref(dfma_ms))
-        fp64_achieved = NCU_FP64_WARP_INST_PER_MODEL * nper / (ms_kernel * 1e-3) / 1e9
         fp64_peak = dfma.value / 32 / 1e9
         achieved = ALGO_BYTES_PER_MODEL * nper / (ms_kernel * 1e-3) / 1e9  # bytes of one launch (rank 0) / its duration
+        ctr, ctr_src = ncu_counters()
+        traffic = fp64_achieved = None
+        if ctr:
+            traffic = (ctr["dram_bytes_read"] + ctr["dram_bytes_write"]) / ctr["models"] * nper
+            fp64_achieved = ctr["fp64_warp_inst"] / ctr["models"] * nper / (ms_kernel * 1e-3) / 1e9
         out = {
             "metric": "models solved/sec (500pts x 25T retirement model)", "value": value, "unit": "models/s",
             "n_gpus": world, "steps": args.steps, "warmup": W, "ms_per_step": tot_ms_max / args.steps,
@@ -290,31 +388,45 @@ def main():
             "config": {"workload": WORKLOAD, "models_per_gpu": nper, "global_batch": nper * world,
                        "l2": "256 MiB flush between timed steps; each step also writes 3.2 GB of lines (>> 126 MB L2)",
                        "vs_baseline_ref": "README.md:118-128: 125.947 ms median per solve = 7.94 models/s, 1 laptop core, Julia",
-                       "flagged_models_rank0": n_flagged, "models_counted": int(solved),
-                       "flagged_note": "status != 0 (non-monotone line: Interpolations.jl would throw) -> not counted; the oracle flags the same models"},
+                       "models_counted": int(solved), "flagged_models_rank0": nper - n_ok, "status_bits_rank0": st_bits,
+                       "flagged_note": "models with a fatal status bit are not counted as solved; at C3 all are DCEGM_ST_DUP_KNOT: the "
+                                       "reference's upper_env pushes an intersection found at a shared turning point twice "
+                                       "(envelope.jl:199, :212, :248-252; DESIGN.md §2)"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_DRAM_BYTES_PER_MODEL * nper, "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum (profiles/r1g_ncu_summary.md, r1g_solve_f_metrics.csv), bytes per launch scaled to this batch",
+                         "traffic": traffic, "traffic_source": ctr_src + ": dram__bytes_read.sum + dram__bytes_write.sum per launch, scaled to this batch",
                          "peak_source": peak_src,
                          "note": "dominant kernel solve_f_kernel is FP64-pipe bound by construction (SURVEY.md §8d): "
                                  "~70 FP64 instr per algorithmic byte; HBM fraction reported as the metric asks"},
             "roofline_fp64": {"bound": "fp64 pipe", "achieved": fp64_achieved, "peak": fp64_peak, "unit": "G warp-inst/s",
-                              "frac": fp64_achieved / fp64_peak if fp64_peak > 0 else None,
+                              "frac": fp64_achieved / fp64_peak if fp64_achieved and fp64_peak > 0 else None,
                               "peak_tflops": 2 * dfma.value / 1e12,
-                              "source": "achieved = FP64-pipe warp instructions per model (ncu sm__inst_executed_pipe_fp64.sum, "
-                                        "profiles/r1g_solve_f_metrics.csv) x models / kernel time; peak = dcegm_debug_dfma_rate measured in this run"},
+                              "source": "achieved = FP64-pipe warp instructions per model (sm__inst_executed_pipe_fp64.sum; " + ctr_src +
+                                        ") x models / kernel time; peak = dcegm_debug_dfma_rate measured in this run"},
             "e2e": {"value": e2e_value, "unit": "models/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "d2h_gbs": d2h * args.steps / e2e_s / 1e9,
-                    "note": "bound by the device-to-host transfer of every stored polyline (pinned D2H measures ~57 GB/s on these boxes)"},
+                    "d2h_gbs": d2h_gbs, "d2h_gbs_per_rank": gbs_all,
+                    "format": "compact lines (include/dcegm.h): ordinates + abscissa runs, lossless; expanded lazily per line by the host mirror",
+                    "expand_all_on_host": expand,
+                    "full_xy": {"value": e2e_xy_value, "unit": "models/s", "d2h_bytes_per_step": int(d2h_xy),
+                                "note": "the same call delivering every point as an (x, y) pair (dcegm_solve_f_packed)"},
+                    "note": "bound by the device-to-host transfer of the stored polylines over PCIe"},
             "gpu_launches": args.steps * 1,
             "clocks": clocks,
         }
+        if configs is not None:
+            out["configs"] = configs
         if not args.no_cpu:
             threads = os.cpu_count() or 1
-            sample = min(BATCH, 512 * threads)  # ~10-20 s of CPU work
+            sample = min(nper, BATCH, 512 * threads)  # ~10-20 s of CPU work
             v, dt = cpu_reference_run(sample, threads)
+            v1, dt1 = cpu_reference_run(48, 1)
             out["cpu_baseline"] = {"value": v, "unit": "models/s", "cores": threads, "kind": "port",
                                    "sample": f"first {sample} models of the same C3 batch, C++ restatement of DCEGM.jl "
-                                             f"(oracle/; julia unavailable on this box), {threads} host threads, {dt:.1f} s"}
+                                             f"(oracle/; julia unavailable on this box), {threads} host threads, {dt:.1f} s",
+                                   "one_thread": {"value": v1, "unit": "models/s", "cores": 1,
+                                                  "sample": f"first 48 models, {dt1:.1f} s; published Julia figure: 7.94 models/s "
+                                                            "on one laptop core (README.md:118-128)"}}
+            if args.na == NA:
+                out["parity_in_run"] = parity_in_run(solver, arr, threads)
         print(json.dumps(out))
     solver.close()
     if dist:

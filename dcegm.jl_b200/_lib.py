@@ -21,6 +21,8 @@ EXPORTS = [
     "dcegm_upload_g", "dcegm_upload_minimal", "dcegm_run", "dcegm_debug_math_check", "dcegm_debug_dfma_rate", "dcegm_solve_f_packed", "dcegm_solve_g_packed",
     "dcegm_simulate", "dcegm_fetch_sim_moments", "dcegm_fetch_sim_panel", "dcegm_sim_moments_to_device", "dcegm_solve_minimal_borrow", "dcegm_solve_minimal_bequest",
     "dcegm_sweep_record_bytes", "dcegm_sweep_records_to_device",
+    "dcegm_solve_f_compact", "dcegm_solve_g_compact", "dcegm_fetch_compact", "dcegm_expand_compact",
+    "dcegm_decode_compact_pair", "dcegm_get_grid", "dcegm_debug_host_table",
 ]
 
 
@@ -56,6 +58,14 @@ def load():
         getattr(lib, f).argtypes = [H, PP, C.c_int, C.c_uint]
     for f in ("dcegm_solve_f_packed", "dcegm_solve_g_packed"):
         getattr(lib, f).argtypes = [H, PP, C.c_int, C.c_uint, dp, C.c_size_t, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    lp = C.POINTER(C.c_int64)
+    for f in ("dcegm_solve_f_compact", "dcegm_solve_g_compact"):
+        getattr(lib, f).argtypes = [H, PP, C.c_int, C.c_uint, dp, C.c_size_t, lp, ip, ip, lp]
+    lib.dcegm_fetch_compact.argtypes = [H, C.c_int, C.c_int, dp, C.c_size_t, lp, ip, ip, lp]
+    lib.dcegm_expand_compact.argtypes = [H, C.c_int, C.c_int, dp, lp, ip, ip, dp, C.c_size_t, lp, lp, C.c_int]
+    lib.dcegm_decode_compact_pair.argtypes = [dp, C.c_int, dp, C.c_int, C.c_int, dp, C.c_int, C.c_int, dp, dp]
+    lib.dcegm_get_grid.argtypes = [H, C.c_int, dp, C.c_int, C.POINTER(C.c_int)]
+    lib.dcegm_debug_host_table.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, dp, dp]
     lib.dcegm_simulate.argtypes = [H, C.c_uint, C.POINTER(_abi.dcegm_sim_shocks)]
     lib.dcegm_fetch_sim_moments.argtypes = [H, C.c_int, C.c_int, dp, ip, ip]
     lib.dcegm_fetch_sim_panel.argtypes = [H, C.c_int, dp, dp, dp, dp, dp, dp, ip, ip, ip]

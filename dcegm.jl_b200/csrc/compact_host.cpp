@@ -1,0 +1,116 @@
+// compact_host.cpp — host-side decoder of the compact line format (compact_lines.cu, include/dcegm.h): rebuilds
+// the (x, y) points of stored polylines — Vector{Point} of line.jl:1-4 — from ordinates + abscissa runs.
+// Pure host code (no CUDA): one IEEE addition per GRID point, copies otherwise; the result is bit-identical to
+// what dcegm_fetch_packed delivers (tests/test_gpu_compact.py).
+#include <cstdint>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+#include "host_setup.hpp"
+
+namespace dcegm {
+
+namespace {
+
+inline uint64_t word_bits(double w) {
+    uint64_t b;
+    memcpy(&b, &w, 8);
+    return b;
+}
+
+// One slot: rec = y[n] | run[nrun] | xs[nx].  xc/nc: decoded points (interleaved x, y) of the slot's policy line for
+// REF runs (null for a policy line).  Writes n interleaved points to out.  false when the record is inconsistent.
+bool decode_slot(const double* rec, int n, int nrun, int nx, const double* a, int na, const double* xc, int nc, double* out) {
+    if (n == 0) return nrun == 0 && nx == 0;
+    if (nrun < 1) return false;
+    const double* runs = rec + n;
+    const double* xs = runs + nrun;
+    int ix = 0;
+    for (int r = 0; r < nrun; r++) {
+        const uint64_t e = word_bits(runs[r]);
+        const int pos = (int)(e & 0xffff), src = (int)((e >> 16) & 0xffff), kind = (int)((e >> 32) & 0xffff);
+        const int end = r + 1 < nrun ? (int)(word_bits(runs[r + 1]) & 0xffff) : n;
+        if ((r == 0 && pos != 0) || end <= pos || end > n) return false;
+        const int len = end - pos;
+        switch (kind) {
+            case 0:  // GRID: x = a[i] + y
+                if (src + len > na) return false;
+                for (int j = 0; j < len; j++) {
+                    const double y = rec[pos + j];
+                    out[2 * (pos + j)] = a[src + j] + y;
+                    out[2 * (pos + j) + 1] = y;
+                }
+                break;
+            case 1:  // REF: the policy line's abscissae
+                if (!xc || src + len > nc) return false;
+                for (int j = 0; j < len; j++) {
+                    out[2 * (pos + j)] = xc[2 * (src + j)];
+                    out[2 * (pos + j) + 1] = rec[pos + j];
+                }
+                break;
+            case 2:  // EXPLICIT
+                if (ix + len > nx) return false;
+                for (int j = 0; j < len; j++) {
+                    out[2 * (pos + j)] = xs[ix++];
+                    out[2 * (pos + j) + 1] = rec[pos + j];
+                }
+                break;
+            default:
+                return false;
+        }
+    }
+    return ix == nx;
+}
+
+}  // namespace
+
+// one (policy, value) slot pair of a model with savings grid a[na]; 0 or -1
+int decode_compact_pair(const double* a, int na, const double* rec_c, int n_c, int aux_c, const double* rec_v, int n_v, int aux_v,
+                        double* xy_c, double* xy_v) {
+    if (!decode_slot(rec_c, n_c, aux_c & 0xffff, (aux_c >> 16) & 0xffff, a, na, nullptr, 0, xy_c)) return -1;
+    if (n_v == 0) return (aux_v == 0) ? 0 : -1;
+    return decode_slot(rec_v, n_v, aux_v & 0xffff, (aux_v >> 16) & 0xffff, a, na, xy_c, n_c, xy_v) ? 0 : -1;
+}
+
+// Expands the compact records of `count` models (slots in layout order, first model = `first` of the batch the tables
+// were built for) into densely packed points: offsets[nslots + 1] (points), xy interleaved.  woff: word offsets of the
+// slots relative to `words`.  Returns 0, -1 (inconsistent record) or -5 (cap_points too small).
+int expand_compact(const HostTables& tab, int nT, int nstate, int first, int count, const double* words, const int64_t* woff,
+                   const int32_t* lens, const int32_t* aux, double* xy, size_t cap_points, int64_t* offsets, int nthreads) {
+    const size_t per = (size_t)nT * nstate * 4;
+    const size_t nsl = per * count;
+    offsets[0] = 0;
+    for (size_t s = 0; s < nsl; s++) offsets[s + 1] = offsets[s] + lens[s];
+    if (!xy) return 0;
+    if ((size_t)offsets[nsl] > cap_points) return -5;
+    if (nthreads < 1) nthreads = 1;
+    if (nthreads > count) nthreads = count > 0 ? count : 1;
+    std::vector<int> bad(nthreads, 0);
+    auto work = [&](int t) {
+        for (int m = t; m < count; m += nthreads) {
+            const DevModel& p = tab.models[first + m];
+            const double* a = tab.grids.data() + (size_t)p.grid * p.na;
+            for (size_t q = 0; q < per; q += 2) {
+                const size_t sc = (size_t)m * per + q, sv = sc + 1;
+                double* oc = xy + 2 * offsets[sc];
+                double* ov = xy + 2 * offsets[sv];
+                if (!decode_slot(words + woff[sc], lens[sc], aux[sc] & 0xffff, (aux[sc] >> 16) & 0xffff, a, p.na, nullptr, 0, oc) ||
+                    !decode_slot(words + woff[sv], lens[sv], aux[sv] & 0xffff, (aux[sv] >> 16) & 0xffff, a, p.na, oc, lens[sc], ov))
+                    bad[t] = 1;
+            }
+        }
+    };
+    if (nthreads == 1) {
+        work(0);
+    } else {
+        std::vector<std::thread> th;
+        for (int t = 0; t < nthreads; t++) th.emplace_back(work, t);
+        for (auto& x : th) x.join();
+    }
+    for (int b : bad)
+        if (b) return -1;
+    return 0;
+}
+
+}  // namespace dcegm

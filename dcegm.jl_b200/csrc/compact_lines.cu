@@ -1,0 +1,210 @@
+// compact_lines.cu — lossless compact encoding of the stored polylines for the device-to-host transfer.
+//
+// A stored line is a Vector{Point} (line.jl:1-4, 16 B per point), but almost every abscissa is redundant:
+//   * policy lines are (avec + c0, c0) (dc_algo.jl:65): x = a[i] + y for the savings grid point i the point came from;
+//   * the value line of the same (period, state, choice) has the abscissae of its policy line (dc_algo.jl:78:
+//     same avec + c0; the envelope keeps or drops points of both lines together, dc_algo.jl:482, and the inserted
+//     kink pair sits at the intersection's x, dc_algo.jl:486-492).
+// The encoder ships the ordinates and, instead of the abscissae, a few RUNS that say where each stretch of
+// abscissae comes from; only points for which neither rule reproduces the stored x BIT FOR BIT (left kink points,
+// bend-back points of the value line, ...) carry an explicit x.  The rules are verified per point on the device, so
+// the encoding is lossless whatever the solver produced (non-monotone or non-finite lines included).
+//
+// Record of one line slot, in 8-byte words (include/dcegm.h, "compact lines"):
+//     y[n] | run[nrun] | xs[nx]
+//     run = pos | src << 16 | kind << 32 : points pos .. (next run's pos or n) - 1 take their abscissae from
+//       kind 0 (GRID)     x[pos + j] = a[src + j] + y[pos + j]          (one IEEE addition, as the kernels did)
+//       kind 1 (REF)      x[pos + j] = x of point src + j of the policy line of the same (model, it, iy, id)
+//       kind 2 (EXPLICIT) x[pos + j] = the next unread word of xs
+// Two passes per chunk: compact_count_kernel (sizes) -> chunk_offsets_kernel (prefix offsets, solver_misc.cu) ->
+// compact_write_kernel.  One CTA per (policy, value) slot pair.
+#include "device_common.cuh"
+
+namespace dcegm {
+
+namespace {
+
+constexpr int kCT = 256;  // threads per CTA of the two kernels
+constexpr unsigned kKindGrid = 0, kKindRef = 1, kKindExplicit = 2;
+constexpr unsigned kNoCode = 0xffffffffu;
+
+__device__ __forceinline__ bool same_bits(double a, double b) { return __double_as_longlong(a) == __double_as_longlong(b); }
+
+// number of entries <= q in the ascending array x[0], x[stride], ... (n entries); 0 for NaN
+__device__ __forceinline__ int count_le_strided(const double* __restrict__ x, int stride, int n, double q) {
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (x[(size_t)mid * stride] <= q)
+            lo = mid + 1;
+        else
+            hi = mid;
+    }
+    return lo;
+}
+
+// kind << 16 | src of one point
+__device__ __forceinline__ unsigned classify(double2 pt, bool value_line, const double* __restrict__ a, int na,
+                                             const double2* __restrict__ Lc, int nc) {
+    if (!value_line) {
+        const int cnt = count_le_strided(a, 1, na, pt.x - pt.y);
+#pragma unroll
+        for (int o = 0; o < 4; o++) {
+            const int i = cnt - 1 + (o == 0 ? 0 : o == 1 ? 1 : o == 2 ? -1 : 2);
+            if (i >= 0 && i < na && same_bits(a[i] + pt.y, pt.x)) return (kKindGrid << 16) | (unsigned)i;
+        }
+    } else {
+        const int j = count_le_strided(&Lc[0].x, 2, nc, pt.x) - 1;
+        if (j >= 0 && same_bits(Lc[j].x, pt.x)) return (kKindRef << 16) | (unsigned)j;
+    }
+    return kKindExplicit << 16;
+}
+
+__device__ __forceinline__ bool starts_run(unsigned prev, unsigned cur) {
+    if (prev == kNoCode || (prev >> 16) != (cur >> 16)) return true;
+    return (cur >> 16) != kKindExplicit && (cur & 0xffffu) != (prev & 0xffffu) + 1;
+}
+
+// One line: classification, run boundaries and (WRITE) the record.  All kCT threads call it.  force_explicit: the
+// count pass found the run form longer than one explicit run (n + 1 + n words), which is then what is written.
+template <bool WRITE>
+__device__ void encode_line(const double2* __restrict__ L, int n, bool value_line, const double* __restrict__ a, int na,
+                            const double2* __restrict__ Lc, int nc, bool force_explicit, int nrun_known, double* __restrict__ rec,
+                            int* nrun_out, int* nx_out) {
+    __shared__ unsigned s_code[kCT + 1];
+    __shared__ int s_warp[kCT / 32];
+    __shared__ int s_tot;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    int run_base = 0, x_base = 0;
+    unsigned carry = kNoCode;
+    for (int k0 = 0; k0 < n; k0 += kCT) {
+        const int k = k0 + tid;
+        double2 pt = make_double2(0.0, 0.0);
+        unsigned code = kNoCode;
+        if (k < n) {
+            pt = L[k];
+            code = force_explicit ? (kKindExplicit << 16) : classify(pt, value_line, a, na, Lc, nc);
+        }
+        s_code[tid + 1] = code;
+        if (tid == 0) s_code[0] = carry;
+        __syncthreads();
+        const bool flag = k < n && starts_run(s_code[tid], code);
+        const bool isx = k < n && (code >> 16) == kKindExplicit;
+        // exclusive block scan of (flag, isx) packed into one int (n < 65536: no carry between the halves)
+        const int v = (flag ? 1 : 0) | (isx ? 1 << 16 : 0);
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_warp[wid] = inc;
+        const unsigned last_code = s_code[(n - k0 < kCT ? n - k0 : kCT)];
+        __syncthreads();
+        if (tid == 0) {
+            int run = 0;
+            for (int w = 0; w < kCT / 32; w++) {
+                const int t = s_warp[w];
+                s_warp[w] = run;
+                run += t;
+            }
+            s_tot = run;
+        }
+        __syncthreads();
+        const int excl = s_warp[wid] + inc - v;
+        if (WRITE && k < n) {
+            rec[k] = pt.y;
+            if (flag) {
+                const unsigned long long e = (unsigned long long)k | ((unsigned long long)(code & 0xffffu) << 16) |
+                                             ((unsigned long long)(code >> 16) << 32);
+                rec[n + run_base + (excl & 0xffff)] = __longlong_as_double((long long)e);
+            }
+            if (isx) rec[n + nrun_known + x_base + (excl >> 16)] = pt.x;
+        }
+        run_base += s_tot & 0xffff;
+        x_base += s_tot >> 16;
+        carry = last_code;
+        __syncthreads();
+    }
+    *nrun_out = run_base;
+    *nx_out = x_base;
+}
+
+}  // namespace
+
+// sizes of the compact records of the slot pairs [first_pair, first_pair + gridDim.x):
+// aux[slot] = nrun | nx << 16, wsize[slot] = n + nrun + nx (words)
+__global__ void __launch_bounds__(kCT) compact_count_kernel(DeviceBatch B, size_t first_pair, int32_t* __restrict__ aux,
+                                                            int32_t* __restrict__ wsize, int32_t* __restrict__ aux_host,
+                                                            int32_t* __restrict__ lens_host) {
+    const size_t q = first_pair + blockIdx.x;
+    const size_t sc = 2 * q, sv = sc + 1;
+    const int m = (int)(sc / ((size_t)B.lay.nT * B.lay.nstate * 4));
+    const DevModel& p = B.models[m];
+    const double* a = B.grids + (size_t)p.grid * p.na;
+    const int cap = B.lay.cap;
+    int nc = B.lens[sc], nv = B.lens[sv];
+    nc = nc < cap ? nc : cap;
+    nv = nv < cap ? nv : cap;
+    const double2* Lc = B.lines + sc * (size_t)cap;
+    const double2* Lv = B.lines + sv * (size_t)cap;
+    for (int which = 0; which < 2; which++) {
+        const int n = which ? nv : nc;
+        int nrun, nx;
+        encode_line<false>(which ? Lv : Lc, n, which == 1, a, p.na, Lc, nc, false, 0, nullptr, &nrun, &nx);
+        if (nrun + nx > n + 1) {  // one explicit run is shorter
+            nrun = 1;
+            nx = n;
+        }
+        if (threadIdx.x == 0) {
+            const size_t s = (which ? sv : sc) - 2 * first_pair;
+            aux[s] = nrun | (nx << 16);
+            wsize[s] = n + nrun + nx;
+            if (aux_host) {  // host-mapped copies: no small transfer queues behind the bulk device-to-host copies
+                aux_host[s] = nrun | (nx << 16);
+                lens_host[s] = n;
+            }
+        }
+    }
+}
+
+// writes the records at the word offsets off[] (prefix sums of wsize over the chunk's slots)
+__global__ void __launch_bounds__(kCT) compact_write_kernel(DeviceBatch B, size_t first_pair, const int32_t* __restrict__ aux,
+                                                            const long long* __restrict__ off, double* __restrict__ dst) {
+    const size_t q = first_pair + blockIdx.x;
+    const size_t sc = 2 * q, sv = sc + 1;
+    const int m = (int)(sc / ((size_t)B.lay.nT * B.lay.nstate * 4));
+    const DevModel& p = B.models[m];
+    const double* a = B.grids + (size_t)p.grid * p.na;
+    const int cap = B.lay.cap;
+    int nc = B.lens[sc], nv = B.lens[sv];
+    nc = nc < cap ? nc : cap;
+    nv = nv < cap ? nv : cap;
+    const double2* Lc = B.lines + sc * (size_t)cap;
+    const double2* Lv = B.lines + sv * (size_t)cap;
+    for (int which = 0; which < 2; which++) {
+        const int n = which ? nv : nc;
+        const size_t s = (which ? sv : sc) - 2 * first_pair;
+        const int ax = aux[s];
+        const int nrun = ax & 0xffff, nx = (ax >> 16) & 0xffff;
+        int r, x;
+        encode_line<true>(which ? Lv : Lc, n, which == 1, a, p.na, Lc, nc, n > 0 && nrun == 1 && nx == n, nrun, dst + off[s], &r, &x);
+    }
+}
+
+cudaError_t launch_compact_count(const DeviceBatch& B, int first, int count, int32_t* aux, int32_t* wsize, int32_t* aux_host,
+                                 int32_t* lens_host, cudaStream_t stream) {
+    const size_t pairs_per = (size_t)B.lay.nT * B.lay.nstate * 2;
+    if (count <= 0) return cudaSuccess;
+    compact_count_kernel<<<(unsigned)(pairs_per * count), kCT, 0, stream>>>(B, pairs_per * first, aux, wsize, aux_host, lens_host);
+    return cudaGetLastError();
+}
+cudaError_t launch_compact_write(const DeviceBatch& B, int first, int count, const int32_t* aux, const long long* off, double* dst,
+                                 cudaStream_t stream) {
+    const size_t pairs_per = (size_t)B.lay.nT * B.lay.nstate * 2;
+    if (count <= 0) return cudaSuccess;
+    compact_write_kernel<<<(unsigned)(pairs_per * count), kCT, 0, stream>>>(B, pairs_per * first, aux, off, dst);
+    return cudaGetLastError();
+}
+
+}  // namespace dcegm

@@ -3,6 +3,10 @@
 // CPU path: every solve runs the sm_100a kernels of solver_*.cu.
 #include <cuda_runtime.h>
 
+#include <sys/syscall.h>
+#include <unistd.h>
+
+#include <cctype>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -25,10 +29,18 @@ cudaError_t launch_pack_lines(const DeviceBatch& B, int first, int count, const 
                               cudaStream_t stream);
 cudaError_t launch_chunk_offsets(const int32_t* lens, size_t nsl, int cap, long long* d_off, long long* h_off_mapped,
                                  cudaStream_t stream);
+cudaError_t launch_compact_count(const DeviceBatch& B, int first, int count, int32_t* aux, int32_t* wsize, int32_t* aux_host,
+                                 int32_t* lens_host, cudaStream_t stream);
+cudaError_t launch_compact_write(const DeviceBatch& B, int first, int count, const int32_t* aux, const long long* off, double* dst,
+                                 cudaStream_t stream);
 cudaError_t launch_sweep_records(const dcegm_summary* summ, const double* mom, const int32_t* sim_status, int nmodels, int nT,
                                  int nT_pad, size_t rec_bytes, unsigned char* dst, cudaStream_t stream);
 cudaError_t launch_sim(const DeviceBatch& B, const SimBatch& Sb, int first, int count, cudaStream_t stream);
 size_t sim_smem_bytes(const dcegm_layout& l);
+int expand_compact(const HostTables& tab, int nT, int nstate, int first, int count, const double* words, const int64_t* woff,
+                   const int32_t* lens, const int32_t* aux, double* xy, size_t cap_points, int64_t* offsets, int nthreads);
+int decode_compact_pair(const double* a, int na, const double* rec_c, int n_c, int aux_c, const double* rec_v, int n_v, int aux_v,
+                        double* xy_c, double* xy_v);
 size_t solver_f_smem_bytes(int cap, int isec_cap);
 size_t solver_g_smem_bytes(int cap, int isec_cap, int na, int ny);
 }  // namespace dcegm
@@ -47,7 +59,9 @@ struct dcegm_ctx {
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     std::vector<cudaEvent_t> ev_pool;                 // per-chunk events of the pipelined solve
     long long* pin_off = nullptr;
+    int32_t* pin_aux = nullptr;   // compact delivery: per-slot run/explicit counts and lengths of a chunk (host-mapped)
     size_t pin_slots = 0;
+    DevBuf cmp_aux, cmp_wsize;
     DevBuf pack_xy2;
     DevBuf big_scratch;   // fine-grid retirement solver (solver_f_big.cu): per-model working lines + envelope scratch
     bool big = false;     // the uploaded batch runs on the fine-grid solver
@@ -215,10 +229,15 @@ int run(dcegm_ctx* h) {
 // are packed densely (s_pack) and copied to the caller's buffer (s_copy), so that the D2H transfer of
 // chunk c overlaps the kernels of chunk c+1...  The only host round trip per chunk is its line lengths
 // (for the prefix offsets the caller gets back anyway).
+// compact != 0: the chunks are delivered in the compact line format (compact_lines.cu; include/dcegm.h): xy receives
+// 8-byte words, cap_points / offsets / npoints count words, lens_out / aux_out receive the per-slot lengths and
+// run counts.
 int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsigned flags, double* xy,
-                 size_t cap_points, int64_t* offsets, int64_t* npoints) {
+                 size_t cap_points, int64_t* offsets, int64_t* npoints, int compact = 0, int32_t* lens_out = nullptr,
+                 int32_t* aux_out = nullptr) {
     if (!h) return DCEGM_E_INVALID;
     if (!xy || !offsets || !npoints) return fail(h, DCEGM_E_INVALID, "xy/offsets/npoints is null");
+    if (compact && (!lens_out || !aux_out)) return fail(h, DCEGM_E_INVALID, "lens/aux is null");
     if (flags & DCEGM_SUMMARY_ONLY) return fail(h, DCEGM_E_INVALID, "DCEGM_SUMMARY_ONLY keeps no lines to pack");
     const bool trace = getenv("DCEGM_TRACE") != nullptr;  // host timestamps of the pipeline on stderr
     const auto tr0 = std::chrono::steady_clock::now();
@@ -262,16 +281,26 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     const size_t cslots = per * chunk;
     if (h->pin_slots < cslots) {
         if (h->pin_off) cudaFreeHost(h->pin_off);
+        if (h->pin_aux) cudaFreeHost(h->pin_aux);
         h->pin_off = nullptr;
+        h->pin_aux = nullptr;
         h->pin_slots = 0;
         // host-mapped: written by chunk_offsets_kernel, read by the host after an event (no copy-engine transfer)
         CK(cudaHostAlloc((void**)&h->pin_off, sizeof(long long) * (cslots + 1), cudaHostAllocMapped));
+        CK(cudaHostAlloc((void**)&h->pin_aux, sizeof(int32_t) * 2 * cslots, cudaHostAllocMapped));
         h->pin_slots = cslots;
     }
     long long* pin_off_dev = nullptr;
+    int32_t* pin_aux_dev = nullptr;
     CK(cudaHostGetDevicePointer((void**)&pin_off_dev, h->pin_off, 0));
+    CK(cudaHostGetDevicePointer((void**)&pin_aux_dev, h->pin_aux, 0));
     if ((rc = ensure(h, h->pack_off, sizeof(long long) * (cslots + 1), false))) return rc;
-    const size_t pack_bytes = sizeof(double2) * cslots * l.cap;
+    if (compact) {
+        if ((rc = ensure(h, h->cmp_aux, sizeof(int32_t) * cslots, false))) return rc;
+        if ((rc = ensure(h, h->cmp_wsize, sizeof(int32_t) * cslots, false))) return rc;
+    }
+    // compact records never exceed 2 n + 1 words (one explicit run), packed lines 2 n
+    const size_t pack_bytes = compact ? sizeof(double) * cslots * (2 * (size_t)l.cap + 1) : sizeof(double2) * cslots * l.cap;
     if ((rc = ensure(h, h->pack_xy, pack_bytes, false))) return rc;
     if (nchunks > 1)
         if ((rc = ensure(h, h->pack_xy2, pack_bytes, false))) return rc;
@@ -299,24 +328,40 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
         const size_t nsl = per * cnt;
         CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * c], 0));
         if (c >= 1) CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * (c - 1) + 1], 0));  // pack_off still read by pack c-1
-        cudaError_t e = launch_chunk_offsets(B.lens + per * c0, nsl, l.cap, (long long*)h->pack_off.p, pin_off_dev, h->s_pack);
+        cudaError_t e;
+        if (compact) {
+            e = launch_compact_count(B, c0, cnt, (int32_t*)h->cmp_aux.p, (int32_t*)h->cmp_wsize.p, pin_aux_dev,
+                                     pin_aux_dev + cslots, h->s_pack);
+            if (e != cudaSuccess) return cuda_fail(h, e, "compact count kernel");
+            e = launch_chunk_offsets((const int32_t*)h->cmp_wsize.p, nsl, 0x7fffffff, (long long*)h->pack_off.p, pin_off_dev, h->s_pack);
+        } else {
+            e = launch_chunk_offsets(B.lens + per * c0, nsl, l.cap, (long long*)h->pack_off.p, pin_off_dev, h->s_pack);
+        }
         if (e != cudaSuccess) return cuda_fail(h, e, "offsets kernel");
         CK(cudaStreamSynchronize(h->s_pack));
         if (trace) fprintf(stderr, "[dcegm] %8.3f ms chunk %d solved, offsets on host\n", trace_ms(), c);
         const long long run_ = h->pin_off[nsl];
         int64_t* go = offsets + per * c0;
         for (size_t s = 0; s <= nsl; s++) go[s] = base + h->pin_off[s];
+        if (compact) {
+            memcpy(aux_out + per * c0, h->pin_aux, sizeof(int32_t) * nsl);
+            memcpy(lens_out + per * c0, h->pin_aux + cslots, sizeof(int32_t) * nsl);
+        }
         if ((size_t)(base + run_) > cap_points) {
             err = fail(h, DCEGM_E_CAPACITY, "dcegm_solve_*_packed: destination too small");
             break;
         }
         double2* buf = (double2*)((c & 1) ? h->pack_xy2.p : h->pack_xy.p);
         if (c >= 2) CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * (c - 2) + 2], 0));  // buffer free again
-        e = launch_pack_lines(B, c0, cnt, (const long long*)h->pack_off.p, buf, h->s_pack);
+        if (compact)
+            e = launch_compact_write(B, c0, cnt, (const int32_t*)h->cmp_aux.p, (const long long*)h->pack_off.p, (double*)buf, h->s_pack);
+        else
+            e = launch_pack_lines(B, c0, cnt, (const long long*)h->pack_off.p, buf, h->s_pack);
         if (e != cudaSuccess) return cuda_fail(h, e, "pack kernel");
         CK(cudaEventRecord(h->ev_pool[3 * c + 1], h->s_pack));
         CK(cudaStreamWaitEvent(h->s_copy, h->ev_pool[3 * c + 1], 0));
-        CK(cudaMemcpyAsync(xy + 2 * base, buf, sizeof(double2) * (size_t)run_, cudaMemcpyDeviceToHost, h->s_copy));
+        const size_t unit = compact ? sizeof(double) : sizeof(double2);
+        CK(cudaMemcpyAsync((char*)xy + unit * (size_t)base, buf, unit * (size_t)run_, cudaMemcpyDeviceToHost, h->s_copy));
         CK(cudaEventRecord(h->ev_pool[3 * c + 2], h->s_copy));
         base += run_;
     }
@@ -324,9 +369,9 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     CK(cudaStreamSynchronize(h->s_pack));
     if (trace) fprintf(stderr, "[dcegm] %8.3f ms all packed (%d chunks of %d)\n", trace_ms(), nchunks, chunk);
     CK(cudaStreamSynchronize(h->s_copy));
-    if (trace) fprintf(stderr, "[dcegm] %8.3f ms all copied: %.1f MB\n", trace_ms(), base * 16.0 / 1e6);
+    if (trace) fprintf(stderr, "[dcegm] %8.3f ms all copied: %.1f MB\n", trace_ms(), base * (compact ? 8.0 : 16.0) / 1e6);
     CK(cudaEventElapsedTime(&h->timing.kernel_ms, h->ev[2], h->ev[3]));
-    h->timing.n_launches = launches + 2 * nchunks;
+    h->timing.n_launches = launches + (compact ? 3 : 2) * nchunks;
     h->solved = true;
     *npoints = base;
     return err;
@@ -425,7 +470,7 @@ int dcegm_destroy(dcegm_handle h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     DevBuf* bufs[] = {&h->models, &h->grids, &h->off, &h->wgt, &h->lines, &h->lens, &h->vbound, &h->meta, &h->isects,
-                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2, &h->big_scratch,
+                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2, &h->big_scratch, &h->cmp_aux, &h->cmp_wsize,
                       &h->simm, &h->yvec, &h->mom, &h->rhist, &h->sstat, &h->pan_d, &h->pan_i, &h->pan_ret,
                       &h->sh_w, &h->sh_d, &h->sh_r, &h->sh_w0, &h->sh_y0};
     for (DevBuf* b : bufs)
@@ -434,6 +479,7 @@ int dcegm_destroy(dcegm_handle h) {
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : h->ev_pool) cudaEventDestroy(ev);
     if (h->pin_off) cudaFreeHost(h->pin_off);
+    if (h->pin_aux) cudaFreeHost(h->pin_aux);
     if (h->s_pack) cudaStreamDestroy(h->s_pack);
     if (h->s_copy) cudaStreamDestroy(h->s_copy);
     cudaStreamDestroy(h->stream);
@@ -443,9 +489,40 @@ int dcegm_destroy(dcegm_handle h) {
 
 const char* dcegm_last_error(dcegm_handle h) { return h ? h->err.c_str() : "null handle"; }
 
+// Pinned host memory on the NUMA node of the current CUDA device: on a multi-GPU box every rank's device-to-host
+// stream then lands in the memory behind its own root complex instead of wherever the process happened to start.
+// Linux memory policy via raw syscalls (no libnuma in the image); failures are ignored (default placement).
+// DCEGM_NUMA=0 switches it off.
 int dcegm_host_alloc(void** ptr, size_t bytes) {
     if (!ptr) return DCEGM_E_INVALID;
-    return cudaHostAlloc(ptr, bytes, cudaHostAllocDefault) == cudaSuccess ? DCEGM_OK : DCEGM_E_CUDA;
+    int node = -1;
+    const char* env = getenv("DCEGM_NUMA");
+    if (!env || atoi(env) != 0) {
+        int dev = 0;
+        char bus[32] = {0};
+        if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetPCIBusId(bus, sizeof bus, dev) == cudaSuccess) {
+            for (char* c = bus; *c; c++) *c = (char)tolower(*c);
+            const std::string path = std::string("/sys/bus/pci/devices/") + bus + "/numa_node";
+            if (FILE* f = fopen(path.c_str(), "r")) {
+                if (fscanf(f, "%d", &node) != 1) node = -1;
+                fclose(f);
+            }
+        }
+    }
+    bool policy_set = false;
+#if defined(__linux__) && defined(SYS_set_mempolicy)
+    if (node >= 0 && node < 1024) {
+        unsigned long mask[16] = {0};
+        mask[node / (8 * sizeof(unsigned long))] = 1UL << (node % (8 * sizeof(unsigned long)));
+        policy_set = syscall(SYS_set_mempolicy, 1 /* MPOL_PREFERRED */, mask, (unsigned long)(8 * sizeof mask)) == 0;
+    }
+#endif
+    const cudaError_t e = cudaHostAlloc(ptr, bytes, cudaHostAllocDefault);
+#if defined(__linux__) && defined(SYS_set_mempolicy)
+    if (policy_set) syscall(SYS_set_mempolicy, 0 /* MPOL_DEFAULT */, nullptr, 0UL);
+#endif
+    if (getenv("DCEGM_TRACE")) fprintf(stderr, "[dcegm] host_alloc %zu B: numa node %d, policy %s\n", bytes, node, policy_set ? "preferred" : "default");
+    return e == cudaSuccess ? DCEGM_OK : DCEGM_E_CUDA;
 }
 int dcegm_host_free(void* ptr) { return cudaFreeHost(ptr) == cudaSuccess ? DCEGM_OK : DCEGM_E_CUDA; }
 
@@ -583,6 +660,119 @@ int dcegm_fetch_packed(dcegm_handle h, int first, int count, double* xy, size_t 
     if (e != cudaSuccess) return cuda_fail(h, e, "pack kernel");
     CK(cudaMemcpyAsync(xy, h->pack_xy.p, sizeof(double2) * (size_t)*npoints, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
+    return DCEGM_OK;
+}
+
+int dcegm_solve_f_compact(dcegm_handle h, const dcegm_param* p, int n, unsigned flags, double* words, size_t cap_words,
+                          int64_t* woffsets, int32_t* lens, int32_t* aux, int64_t* nwords) {
+    return solve_packed(h, DCEGM_MODEL_F, p, n, flags, words, cap_words, woffsets, nwords, 1, lens, aux);
+}
+int dcegm_solve_g_compact(dcegm_handle h, const dcegm_param* p, int n, unsigned flags, double* words, size_t cap_words,
+                          int64_t* woffsets, int32_t* lens, int32_t* aux, int64_t* nwords) {
+    return solve_packed(h, DCEGM_MODEL_G, p, n, flags, words, cap_words, woffsets, nwords, 1, lens, aux);
+}
+
+int dcegm_fetch_compact(dcegm_handle h, int first, int count, double* words, size_t cap_words, int64_t* woffsets, int32_t* lens,
+                        int32_t* aux, int64_t* nwords) {
+    int rc = need_solution(h);
+    if (rc) return rc;
+    if ((rc = check_range(h, first, count))) return rc;
+    if (!woffsets || !nwords || !lens || !aux) return fail(h, DCEGM_E_INVALID, "woffsets/lens/aux/nwords is null");
+    if (!h->batch.lines) return fail(h, DCEGM_E_NOSOLUTION, "solve with DCEGM_SUMMARY_ONLY keeps no lines");
+    const dcegm_layout& l = h->batch.lay;
+    const size_t per = (size_t)l.nT * l.nstate * 4, nsl = per * count;
+    woffsets[0] = 0;
+    *nwords = 0;
+    if (nsl == 0) return DCEGM_OK;
+    if ((rc = ensure(h, h->cmp_aux, sizeof(int32_t) * nsl, false))) return rc;
+    if ((rc = ensure(h, h->cmp_wsize, sizeof(int32_t) * nsl, false))) return rc;
+    if ((rc = ensure(h, h->pack_off, sizeof(long long) * (nsl + 1), false))) return rc;
+    cudaError_t e = launch_compact_count(h->batch, first, count, (int32_t*)h->cmp_aux.p, (int32_t*)h->cmp_wsize.p, nullptr, nullptr, h->stream);
+    if (e != cudaSuccess) return cuda_fail(h, e, "compact count kernel");
+    std::vector<int32_t> wsize(nsl);
+    CK(cudaMemcpyAsync(wsize.data(), h->cmp_wsize.p, sizeof(int32_t) * nsl, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(aux, h->cmp_aux.p, sizeof(int32_t) * nsl, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(lens, h->batch.lens + per * first, sizeof(int32_t) * nsl, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    for (size_t s = 0; s < nsl; s++) {
+        lens[s] = lens[s] < l.cap ? lens[s] : l.cap;
+        woffsets[s + 1] = woffsets[s] + wsize[s];
+    }
+    *nwords = woffsets[nsl];
+    if (!words) return DCEGM_OK;
+    if ((size_t)*nwords > cap_words) return fail(h, DCEGM_E_CAPACITY, "dcegm_fetch_compact: destination too small");
+    if ((rc = ensure(h, h->pack_xy, sizeof(double) * (size_t)*nwords, false))) return rc;
+    CK(cudaMemcpyAsync(h->pack_off.p, woffsets, sizeof(int64_t) * (nsl + 1), cudaMemcpyHostToDevice, h->stream));
+    e = launch_compact_write(h->batch, first, count, (const int32_t*)h->cmp_aux.p, (const long long*)h->pack_off.p, (double*)h->pack_xy.p, h->stream);
+    if (e != cudaSuccess) return cuda_fail(h, e, "compact write kernel");
+    CK(cudaMemcpyAsync(words, h->pack_xy.p, sizeof(double) * (size_t)*nwords, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return DCEGM_OK;
+}
+
+int dcegm_expand_compact(dcegm_handle h, int first, int count, const double* words, const int64_t* woffsets, const int32_t* lens,
+                         const int32_t* aux, double* xy, size_t cap_points, int64_t* offsets, int64_t* npoints, int nthreads) {
+    if (!h) return DCEGM_E_INVALID;
+    if (!h->uploaded) return fail(h, DCEGM_E_NOSOLUTION, "dcegm_expand_compact needs the batch of the last solve (savings grids)");
+    if (!words || !woffsets || !lens || !aux || !offsets || !npoints) return fail(h, DCEGM_E_INVALID, "null argument");
+    const dcegm_layout& l = h->batch.lay;
+    if (first < 0 || count < 0 || first + count > l.nmodels) return fail(h, DCEGM_E_INVALID, "model range out of bounds");
+    const int rc = expand_compact(h->tab, l.nT, l.nstate, first, count, words, woffsets, lens, aux, xy, cap_points, offsets, nthreads);
+    *npoints = offsets[(size_t)l.nT * l.nstate * 4 * count];
+    if (rc == -5) return fail(h, DCEGM_E_CAPACITY, "dcegm_expand_compact: destination too small");
+    if (rc) return fail(h, DCEGM_E_INVALID, "dcegm_expand_compact: inconsistent compact record");
+    return DCEGM_OK;
+}
+
+int dcegm_decode_compact_pair(const double* grid, int na, const double* rec_c, int n_c, int aux_c, const double* rec_v, int n_v,
+                              int aux_v, double* xy_c, double* xy_v) {
+    if (!grid || na < 1 || !xy_c || (n_c > 0 && !rec_c) || (n_v > 0 && (!rec_v || !xy_v))) return DCEGM_E_INVALID;
+    return decode_compact_pair(grid, na, rec_c, n_c, aux_c, rec_v, n_v, aux_v, xy_c, xy_v) ? DCEGM_E_INVALID : DCEGM_OK;
+}
+
+int dcegm_get_grid(dcegm_handle h, int model, double* grid, int cap, int* na) {
+    if (!h) return DCEGM_E_INVALID;
+    if (!h->uploaded) return fail(h, DCEGM_E_NOSOLUTION, "no batch uploaded");
+    if (model < 0 || model >= h->batch.lay.nmodels || !na) return fail(h, DCEGM_E_INVALID, "model out of range");
+    const DevModel& p = h->tab.models[model];
+    *na = p.na;
+    if (!grid) return DCEGM_OK;
+    if (cap < p.na) return fail(h, DCEGM_E_CAPACITY, "dcegm_get_grid: destination too small");
+    memcpy(grid, h->tab.grids.data() + (size_t)p.grid * p.na, sizeof(double) * p.na);
+    return DCEGM_OK;
+}
+
+// ---- diagnostics: the host-side model constructors (host_setup.cpp), callable without a device --------
+int dcegm_debug_host_table(int which, int n, double p0, double p1, double p2, int iarg, double* out0, double* out1) {
+    if (n < 1 || !out0) return DCEGM_E_INVALID;
+    std::vector<double> a, b;
+    switch (which) {
+        case 0:  // range(p0, stop = p1, length = n)
+            linrange(p0, p1, n, out0);
+            return DCEGM_OK;
+        case 1:  // quadpoints(n, 0, 1): nodes, weights
+            if (!out1) return DCEGM_E_INVALID;
+            gauss_legendre01(n, a, b);
+            break;
+        case 2:  // quantile(Normal(0, 1), p0)
+            out0[0] = normal_quantile(p0);
+            return DCEGM_OK;
+        case 3:  // gausshermite(n): nodes, weights
+            if (!out1) return DCEGM_E_INVALID;
+            gauss_hermite(n, a, b);
+            break;
+        case 4:  // rouwenhorst(rho = p0, mu = p1, sigma = p2, n): support, transition matrix (row-major)
+            if (!out1) return DCEGM_E_INVALID;
+            rouwenhorst(p0, p1, p2, n, a, b);
+            break;
+        case 5:  // scaleGrid(p0, p1, n; logorder = iarg)
+            scale_grid(p0, p1, n, iarg, out0);
+            return DCEGM_OK;
+        default:
+            return DCEGM_E_INVALID;
+    }
+    memcpy(out0, a.data(), sizeof(double) * a.size());
+    memcpy(out1, b.data(), sizeof(double) * b.size());
     return DCEGM_OK;
 }
 

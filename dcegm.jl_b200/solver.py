@@ -138,6 +138,48 @@ class Solver:
         self._ck(fn(self.h, arr, n, flags, _dp(xy), xy.shape[0], offsets.ctypes.data_as(C.POINTER(C.c_int64)), C.byref(npts)))
         return xy[: npts.value], offsets
 
+    def fetch_compact(self, first=0, count=None):
+        """models [first, first + count) of the resident solution in the compact line format -> CompactLines"""
+        from .compact import CompactLines
+
+        lay = self.layout()
+        count = lay.nmodels - first if count is None else count
+        nsl = count * lay.nT * lay.nstate * 4
+        woff = np.zeros(nsl + 1, np.int64)
+        lens = np.zeros(nsl, np.int32)
+        aux = np.zeros(nsl, np.int32)
+        nw = C.c_int64()
+        lp, ip = C.POINTER(C.c_int64), C.POINTER(C.c_int32)
+        args = (woff.ctypes.data_as(lp), lens.ctypes.data_as(ip), aux.ctypes.data_as(ip), C.byref(nw))
+        self._ck(self.lib.dcegm_fetch_compact(self.h, first, count, None, 0, *args))
+        words = np.zeros(max(nw.value, 1))
+        self._ck(self.lib.dcegm_fetch_compact(self.h, first, count, _dp(words), len(words), *args))
+        return CompactLines(lay.nT, lay.nstate, count, words[: nw.value], woff, lens, aux, solver=self, first=first)
+
+    def solve_compact(self, model, params, keep_dirty=False, words=None):
+        """Solve and deliver every stored polyline in the compact line format through the chunked pipeline
+        (dcegm_solve_*_compact) -> CompactLines"""
+        from .compact import CompactLines
+
+        arr = params if isinstance(params, C.Array) else params_array(params)
+        fn = {_abi.MODEL_F: self.lib.dcegm_solve_f_compact, _abi.MODEL_G: self.lib.dcegm_solve_g_compact}[model]
+        n = len(arr)
+        nstate = arr[0].ny if model == _abi.MODEL_G else 1
+        nsl = n * arr[0].nT * nstate * 4
+        na = arr[0].na
+        cap = (na + na // 10 + 2 * max(na // 16, 32) + 2 + 7) // 8 * 8
+        if words is None:
+            words = np.empty(nsl * (cap + cap // 4) + 1024)  # typical records are ~1.02 n words; E_CAPACITY otherwise
+        woff = np.zeros(nsl + 1, np.int64)
+        lens = np.zeros(nsl, np.int32)
+        aux = np.zeros(nsl, np.int32)
+        nw = C.c_int64()
+        lp, ip = C.POINTER(C.c_int64), C.POINTER(C.c_int32)
+        flags = _abi.KEEP_DIRTY if keep_dirty else 0
+        self._ck(fn(self.h, arr, n, flags, _dp(words), len(words), woff.ctypes.data_as(lp), lens.ctypes.data_as(ip),
+                    aux.ctypes.data_as(ip), C.byref(nw)))
+        return CompactLines(arr[0].nT, nstate, n, words[: nw.value], woff, lens, aux, solver=self, first=0)
+
     # ---- forward simulation of the resident solution (simulate.jl:61-203) -----------------------
     def simulate(self, panel=False, shocks=None):
         """shocks: None (counter-based draws keyed by Param.rseed) or a dict of the reference's raw rand()

@@ -250,6 +250,39 @@ int  dcegm_fetch_dirty(dcegm_handle h, int first, int count, double* dirty);
  * query npoints/offsets only. */
 int  dcegm_fetch_packed(dcegm_handle h, int first, int count, double* xy, size_t cap_points,
                         int64_t* offsets, int64_t* npoints);
+/* ---- compact lines: the same polylines in half the bytes --------------------------------------------
+ * A stored line is a Vector{Point} (line.jl:1-4), 16 B per point, but nearly every abscissa is redundant: a
+ * policy line is (avec + c0, c0) (dc_algo.jl:65), so x = a[i] + y for the savings grid point i a point came from,
+ * and the value line of the same (period, state, choice) shares the policy line's abscissae (dc_algo.jl:78, :482,
+ * :486-492).  The compact form ships the ordinates plus a few RUNS naming the source of each stretch of abscissae;
+ * points for which neither rule reproduces the stored x bit for bit (verified per point on the device) carry an
+ * explicit x.  Record of one line slot (slots in layout order [model][it][iy][id][kind]), in 8-byte words:
+ *     y[n] | run[nrun] | xs[nx]          n = lens[slot], nrun = aux[slot] & 0xffff, nx = aux[slot] >> 16
+ *     run (64-bit integer) = pos | src << 16 | kind << 32; it covers points pos .. (next run's pos, or n) - 1:
+ *       kind 0  x[pos + j] = a[src + j] + y[pos + j]     (a: the model's savings grid, dcegm_get_grid; one IEEE add)
+ *       kind 1  x[pos + j] = x of point src + j of the POLICY line of the same (model, it, iy, id)   (value lines only)
+ *       kind 2  x[pos + j] = next unread word of xs
+ * woffsets[nslots + 1] are prefix offsets in words into `words`.  dcegm_solve_*_compact is dcegm_solve_*_packed with
+ * this delivery format (same chunked pipeline; `words` from dcegm_host_alloc makes the copies asynchronous);
+ * cap_words = nslots * (2 * cap + 1) always fits.  dcegm_fetch_compact encodes models [first, first + count) of the
+ * resident solution (words == NULL: sizes only).  dcegm_expand_compact rebuilds the densely packed points of
+ * dcegm_fetch_packed (bit-identical: tests/test_gpu_compact.py) on `nthreads` host threads, for the batch of the
+ * handle's last solve; woffsets / lens / aux point at the first slot of model `first`, woffsets values are relative
+ * to `words`.  dcegm_decode_compact_pair is the handle-free primitive a lazy host mirror calls per Envelope: the
+ * policy record (and optionally the value record) of one (model, it, iy, id) -> interleaved points. */
+int  dcegm_solve_f_compact(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags, double* words,
+                           size_t cap_words, int64_t* woffsets, int32_t* lens, int32_t* aux, int64_t* nwords);
+int  dcegm_solve_g_compact(dcegm_handle h, const dcegm_param* params, int nmodels, unsigned flags, double* words,
+                           size_t cap_words, int64_t* woffsets, int32_t* lens, int32_t* aux, int64_t* nwords);
+int  dcegm_fetch_compact(dcegm_handle h, int first, int count, double* words, size_t cap_words, int64_t* woffsets,
+                         int32_t* lens, int32_t* aux, int64_t* nwords);
+int  dcegm_expand_compact(dcegm_handle h, int first, int count, const double* words, const int64_t* woffsets,
+                          const int32_t* lens, const int32_t* aux, double* xy, size_t cap_points, int64_t* offsets,
+                          int64_t* npoints, int nthreads);
+int  dcegm_decode_compact_pair(const double* grid, int na, const double* rec_c, int n_c, int aux_c, const double* rec_v,
+                               int n_v, int aux_v, double* xy_c, double* xy_v);
+/* the savings grid avec of one model of the last uploaded batch (param.jl:199, :288); grid == NULL: *na only */
+int  dcegm_get_grid(dcegm_handle h, int model, double* grid, int cap, int* na);
 int  dcegm_status(dcegm_handle h, int32_t* per_model_status);   /* nmodels entries */
 int  dcegm_summaries(dcegm_handle h, dcegm_summary* dst);       /* nmodels records, host */
 /* device-to-device copy of the summaries into caller-provided device memory (the send
@@ -332,6 +365,14 @@ int  dcegm_fetch_sim_panel(dcegm_handle h, int model, double* w0, double* w1, do
  * results that differ from the IEEE operations: mismatches2[0] divisions, [1] reciprocals. */
 int  dcegm_debug_math_check(unsigned long long n, unsigned long long seed, int emin, int emax,
                             unsigned long long* mismatches2);
+
+/* The host-side model constructors of the library (csrc/host_setup.cpp), callable without a device, so that the
+ * tables the kernels receive can be checked against independent implementations (tests/test_host_setup_tables.py):
+ * which = 0 range(p0, stop=p1, length=n) -> out0[n] (param.jl:199);  1 quadpoints(n,0,1) -> nodes out0[n], weights
+ * out1[n] (utils.jl:261-297);  2 quantile(Normal(0,1), p0) -> out0[0] (param.jl:195-196);  3 gausshermite(n) -> out0[n],
+ * out1[n] (param.jl:279);  4 rouwenhorst(rho=p0, mu=p1, sigma=p2, n) -> support out0[n], transition matrix out1[n*n]
+ * row-major (utils.jl:178-197);  5 scaleGrid(p0, p1, n; logorder=iarg) -> out0[n] (utils.jl:200-238). */
+int  dcegm_debug_host_table(int which, int n, double p0, double p1, double p2, int iarg, double* out0, double* out1);
 
 /* FP64 issue rate of the device: thread-level DFMA per second retired by a kernel of independent DFMA chains
  * at full occupancy (no memory traffic); *ms = duration of the best repetition.  The solver kernels are bound by
