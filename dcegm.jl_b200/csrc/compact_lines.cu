@@ -16,8 +16,8 @@
 //       kind 0 (GRID)     x[pos + j] = a[src + j] + y[pos + j]          (one IEEE addition, as the kernels did)
 //       kind 1 (REF)      x[pos + j] = x of point src + j of the policy line of the same (model, it, iy, id)
 //       kind 2 (EXPLICIT) x[pos + j] = the next unread word of xs
-// Two passes per chunk: compact_count_kernel (sizes) -> chunk_offsets_kernel (prefix offsets, solver_misc.cu) ->
-// compact_write_kernel.  One CTA per (policy, value) slot pair.
+// Two passes per chunk: compact_count_kernel (per-point codes, sizes) -> chunk_offsets_kernel (prefix offsets,
+// solver_misc.cu) -> compact_write_kernel (streams lines + codes into the records).  One CTA per (policy, value) slot pair.
 #include "device_common.cuh"
 
 namespace dcegm {
@@ -43,16 +43,34 @@ __device__ __forceinline__ int count_le_strided(const double* __restrict__ x, in
     return lo;
 }
 
-// kind << 16 | src of one point
-__device__ __forceinline__ unsigned classify(double2 pt, bool value_line, const double* __restrict__ a, int na,
-                                             const double2* __restrict__ Lc, int nc) {
+// kind << 16 | src of one point.  Policy points: the grid index is first guessed arithmetically (uniform grids:
+// three independent probes), then searched (any ascending grid).  Value points: exact match of the abscissa in the
+// policy line, searched in the shared-memory copy xs_c of its abscissae when it was staged (nc <= kStageCap),
+// else in global memory.
+constexpr int kStageCap = 1024;
+__device__ __forceinline__ unsigned classify(double2 pt, bool value_line, const double* __restrict__ a, int na, double a0,
+                                             double inv_da, const double2* __restrict__ Lc, int nc,
+                                             const double* __restrict__ xs_c) {
     if (!value_line) {
-        const int cnt = count_le_strided(a, 1, na, pt.x - pt.y);
+        const double d = pt.x - pt.y;
+        const double t = (d - a0) * inv_da;
+        if (t > -1.0 && t < (double)na) {  // false for NaN
+            const int g = (int)(t + 0.5);
+#pragma unroll
+            for (int o = 0; o < 3; o++) {
+                const int i = g + (o == 0 ? 0 : o == 1 ? -1 : 1);
+                if (i >= 0 && i < na && same_bits(a[i] + pt.y, pt.x)) return (kKindGrid << 16) | (unsigned)i;
+            }
+        }
+        const int cnt = count_le_strided(a, 1, na, d);
 #pragma unroll
         for (int o = 0; o < 4; o++) {
             const int i = cnt - 1 + (o == 0 ? 0 : o == 1 ? 1 : o == 2 ? -1 : 2);
             if (i >= 0 && i < na && same_bits(a[i] + pt.y, pt.x)) return (kKindGrid << 16) | (unsigned)i;
         }
+    } else if (xs_c) {
+        const int j = count_le_strided(xs_c, 1, nc, pt.x) - 1;
+        if (j >= 0 && same_bits(xs_c[j], pt.x)) return (kKindRef << 16) | (unsigned)j;
     } else {
         const int j = count_le_strided(&Lc[0].x, 2, nc, pt.x) - 1;
         if (j >= 0 && same_bits(Lc[j].x, pt.x)) return (kKindRef << 16) | (unsigned)j;
@@ -65,12 +83,22 @@ __device__ __forceinline__ bool starts_run(unsigned prev, unsigned cur) {
     return (cur >> 16) != kKindExplicit && (cur & 0xffffu) != (prev & 0xffffu) + 1;
 }
 
-// One line: classification, run boundaries and (WRITE) the record.  All kCT threads call it.  force_explicit: the
-// count pass found the run form longer than one explicit run (n + 1 + n words), which is then what is written.
+struct ClassifyCtx {
+    const double* a;
+    int na;
+    double a0, inv_da;
+    const double2* Lc;
+    int nc;
+    const double* xs_c;  // shared-memory copy of the policy line's abscissae or null
+};
+
+// One line: run boundaries and (WRITE) the record.  All kCT threads call it.  The count pass (WRITE = false)
+// classifies every point and keeps the codes in `codes` (global scratch, one word per point); the write pass reads
+// them back.  force_explicit: the count pass found the run form longer than one explicit run (n + 1 + n words),
+// which is then what is written.
 template <bool WRITE>
-__device__ void encode_line(const double2* __restrict__ L, int n, bool value_line, const double* __restrict__ a, int na,
-                            const double2* __restrict__ Lc, int nc, bool force_explicit, int nrun_known, double* __restrict__ rec,
-                            int* nrun_out, int* nx_out) {
+__device__ void encode_line(const double2* __restrict__ L, int n, bool value_line, const ClassifyCtx& cx, unsigned* __restrict__ codes,
+                            bool force_explicit, int nrun_known, double* __restrict__ rec, int* nrun_out, int* nx_out) {
     __shared__ unsigned s_code[kCT + 1];
     __shared__ int s_warp[kCT / 32];
     __shared__ int s_tot;
@@ -83,7 +111,12 @@ __device__ void encode_line(const double2* __restrict__ L, int n, bool value_lin
         unsigned code = kNoCode;
         if (k < n) {
             pt = L[k];
-            code = force_explicit ? (kKindExplicit << 16) : classify(pt, value_line, a, na, Lc, nc);
+            if (WRITE) {
+                code = force_explicit ? (kKindExplicit << 16) : codes[k];
+            } else {
+                code = classify(pt, value_line, cx.a, cx.na, cx.a0, cx.inv_da, cx.Lc, cx.nc, cx.xs_c);
+                codes[k] = code;
+            }
         }
         s_code[tid + 1] = code;
         if (tid == 0) s_code[0] = carry;
@@ -132,32 +165,44 @@ __device__ void encode_line(const double2* __restrict__ L, int n, bool value_lin
 
 }  // namespace
 
-// sizes of the compact records of the slot pairs [first_pair, first_pair + gridDim.x):
-// aux[slot] = nrun | nx << 16, wsize[slot] = n + nrun + nx (words)
+// sizes of the compact records of the slot pairs [first_pair, first_pair + gridDim.x) and the per-point codes:
+// aux[slot] = nrun | nx << 16, wsize[slot] = n + nrun + nx (words), codes[slot][cap]
 __global__ void __launch_bounds__(kCT) compact_count_kernel(DeviceBatch B, size_t first_pair, int32_t* __restrict__ aux,
-                                                            int32_t* __restrict__ wsize, int32_t* __restrict__ aux_host,
-                                                            int32_t* __restrict__ lens_host) {
+                                                            int32_t* __restrict__ wsize, unsigned* __restrict__ codes,
+                                                            int32_t* __restrict__ aux_host, int32_t* __restrict__ lens_host) {
+    __shared__ double s_xc[kStageCap];
     const size_t q = first_pair + blockIdx.x;
     const size_t sc = 2 * q, sv = sc + 1;
     const int m = (int)(sc / ((size_t)B.lay.nT * B.lay.nstate * 4));
     const DevModel& p = B.models[m];
-    const double* a = B.grids + (size_t)p.grid * p.na;
     const int cap = B.lay.cap;
     int nc = B.lens[sc], nv = B.lens[sv];
     nc = nc < cap ? nc : cap;
     nv = nv < cap ? nv : cap;
-    const double2* Lc = B.lines + sc * (size_t)cap;
+    ClassifyCtx cx;
+    cx.a = B.grids + (size_t)p.grid * p.na;
+    cx.na = p.na;
+    cx.a0 = cx.a[0];
+    cx.inv_da = p.na > 1 ? 1.0 / (cx.a[1] - cx.a[0]) : 0.0;
+    cx.Lc = B.lines + sc * (size_t)cap;
+    cx.nc = nc;
+    cx.xs_c = nullptr;
     const double2* Lv = B.lines + sv * (size_t)cap;
+    if (nc <= kStageCap && nv > 0) {
+        for (int k = threadIdx.x; k < nc; k += kCT) s_xc[k] = cx.Lc[k].x;
+        cx.xs_c = s_xc;
+        __syncthreads();
+    }
     for (int which = 0; which < 2; which++) {
         const int n = which ? nv : nc;
+        const size_t s = (which ? sv : sc) - 2 * first_pair;
         int nrun, nx;
-        encode_line<false>(which ? Lv : Lc, n, which == 1, a, p.na, Lc, nc, false, 0, nullptr, &nrun, &nx);
+        encode_line<false>(which ? Lv : cx.Lc, n, which == 1, cx, codes + s * (size_t)cap, false, 0, nullptr, &nrun, &nx);
         if (nrun + nx > n + 1) {  // one explicit run is shorter
             nrun = 1;
             nx = n;
         }
         if (threadIdx.x == 0) {
-            const size_t s = (which ? sv : sc) - 2 * first_pair;
             aux[s] = nrun | (nx << 16);
             wsize[s] = n + nrun + nx;
             if (aux_host) {  // host-mapped copies: no small transfer queues behind the bulk device-to-host copies
@@ -170,16 +215,15 @@ __global__ void __launch_bounds__(kCT) compact_count_kernel(DeviceBatch B, size_
 
 // writes the records at the word offsets off[] (prefix sums of wsize over the chunk's slots)
 __global__ void __launch_bounds__(kCT) compact_write_kernel(DeviceBatch B, size_t first_pair, const int32_t* __restrict__ aux,
-                                                            const long long* __restrict__ off, double* __restrict__ dst) {
+                                                            const unsigned* __restrict__ codes, const long long* __restrict__ off,
+                                                            double* __restrict__ dst) {
     const size_t q = first_pair + blockIdx.x;
     const size_t sc = 2 * q, sv = sc + 1;
-    const int m = (int)(sc / ((size_t)B.lay.nT * B.lay.nstate * 4));
-    const DevModel& p = B.models[m];
-    const double* a = B.grids + (size_t)p.grid * p.na;
     const int cap = B.lay.cap;
     int nc = B.lens[sc], nv = B.lens[sv];
     nc = nc < cap ? nc : cap;
     nv = nv < cap ? nv : cap;
+    ClassifyCtx cx{};
     const double2* Lc = B.lines + sc * (size_t)cap;
     const double2* Lv = B.lines + sv * (size_t)cap;
     for (int which = 0; which < 2; which++) {
@@ -188,22 +232,23 @@ __global__ void __launch_bounds__(kCT) compact_write_kernel(DeviceBatch B, size_
         const int ax = aux[s];
         const int nrun = ax & 0xffff, nx = (ax >> 16) & 0xffff;
         int r, x;
-        encode_line<true>(which ? Lv : Lc, n, which == 1, a, p.na, Lc, nc, n > 0 && nrun == 1 && nx == n, nrun, dst + off[s], &r, &x);
+        encode_line<true>(which ? Lv : Lc, n, which == 1, cx, const_cast<unsigned*>(codes) + s * (size_t)cap,
+                          n > 0 && nrun == 1 && nx == n, nrun, dst + off[s], &r, &x);
     }
 }
 
-cudaError_t launch_compact_count(const DeviceBatch& B, int first, int count, int32_t* aux, int32_t* wsize, int32_t* aux_host,
-                                 int32_t* lens_host, cudaStream_t stream) {
+cudaError_t launch_compact_count(const DeviceBatch& B, int first, int count, int32_t* aux, int32_t* wsize, unsigned* codes,
+                                 int32_t* aux_host, int32_t* lens_host, cudaStream_t stream) {
     const size_t pairs_per = (size_t)B.lay.nT * B.lay.nstate * 2;
     if (count <= 0) return cudaSuccess;
-    compact_count_kernel<<<(unsigned)(pairs_per * count), kCT, 0, stream>>>(B, pairs_per * first, aux, wsize, aux_host, lens_host);
+    compact_count_kernel<<<(unsigned)(pairs_per * count), kCT, 0, stream>>>(B, pairs_per * first, aux, wsize, codes, aux_host, lens_host);
     return cudaGetLastError();
 }
-cudaError_t launch_compact_write(const DeviceBatch& B, int first, int count, const int32_t* aux, const long long* off, double* dst,
-                                 cudaStream_t stream) {
+cudaError_t launch_compact_write(const DeviceBatch& B, int first, int count, const int32_t* aux, const unsigned* codes,
+                                 const long long* off, double* dst, cudaStream_t stream) {
     const size_t pairs_per = (size_t)B.lay.nT * B.lay.nstate * 2;
     if (count <= 0) return cudaSuccess;
-    compact_write_kernel<<<(unsigned)(pairs_per * count), kCT, 0, stream>>>(B, pairs_per * first, aux, off, dst);
+    compact_write_kernel<<<(unsigned)(pairs_per * count), kCT, 0, stream>>>(B, pairs_per * first, aux, codes, off, dst);
     return cudaGetLastError();
 }
 

@@ -29,10 +29,10 @@ cudaError_t launch_pack_lines(const DeviceBatch& B, int first, int count, const 
                               cudaStream_t stream);
 cudaError_t launch_chunk_offsets(const int32_t* lens, size_t nsl, int cap, long long* d_off, long long* h_off_mapped,
                                  cudaStream_t stream);
-cudaError_t launch_compact_count(const DeviceBatch& B, int first, int count, int32_t* aux, int32_t* wsize, int32_t* aux_host,
-                                 int32_t* lens_host, cudaStream_t stream);
-cudaError_t launch_compact_write(const DeviceBatch& B, int first, int count, const int32_t* aux, const long long* off, double* dst,
-                                 cudaStream_t stream);
+cudaError_t launch_compact_count(const DeviceBatch& B, int first, int count, int32_t* aux, int32_t* wsize, unsigned* codes,
+                                 int32_t* aux_host, int32_t* lens_host, cudaStream_t stream);
+cudaError_t launch_compact_write(const DeviceBatch& B, int first, int count, const int32_t* aux, const unsigned* codes,
+                                 const long long* off, double* dst, cudaStream_t stream);
 cudaError_t launch_sweep_records(const dcegm_summary* summ, const double* mom, const int32_t* sim_status, int nmodels, int nT,
                                  int nT_pad, size_t rec_bytes, unsigned char* dst, cudaStream_t stream);
 cudaError_t launch_sim(const DeviceBatch& B, const SimBatch& Sb, int first, int count, cudaStream_t stream);
@@ -61,7 +61,7 @@ struct dcegm_ctx {
     long long* pin_off = nullptr;
     int32_t* pin_aux = nullptr;   // compact delivery: per-slot run/explicit counts and lengths of a chunk (host-mapped)
     size_t pin_slots = 0;
-    DevBuf cmp_aux, cmp_wsize;
+    DevBuf cmp_aux, cmp_wsize, cmp_codes;
     DevBuf pack_xy2;
     DevBuf big_scratch;   // fine-grid retirement solver (solver_f_big.cu): per-model working lines + envelope scratch
     bool big = false;     // the uploaded batch runs on the fine-grid solver
@@ -255,10 +255,11 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     std::vector<int> cstart, ccount;
     {
         int per_chunk = 2 * wave;
-        while ((nmodels - wave + per_chunk - 1) / per_chunk + 1 > 16) per_chunk += wave;
+        while ((nmodels - wave + per_chunk - 1) / per_chunk + 2 > 16) per_chunk += wave;
         int c0 = 0;
         while (c0 < nmodels) {
-            int cnt = cstart.empty() && nmodels > wave ? wave : per_chunk;
+            // half a wave first (one CTA per SM: the shortest time to the first transfer), then one wave, then per_chunk
+            int cnt = nmodels > 2 * wave ? (cstart.empty() ? wave / 2 : cstart.size() == 1 ? wave : per_chunk) : per_chunk;
             if (h->big) cnt = 148 * ((nmodels + 148 * 16 - 1) / (148 * 16));  // fine-grid solver: one envelope CTA per SM
             cnt = cnt < nmodels - c0 ? cnt : nmodels - c0;
             cstart.push_back(c0);
@@ -270,7 +271,12 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     int chunk = 0;
     for (int c : ccount) chunk = c > chunk ? c : chunk;
     if (!h->s_pack) {
-        CK(cudaStreamCreateWithFlags(&h->s_pack, cudaStreamNonBlocking));
+        // DCEGM_PACK_PRIO=1 runs the packing kernels at the highest stream priority (measured slower: they take SM slots
+        // from the solver, which then feeds the copy engine late — profiles/r2_e2e_pipeline.md)
+        int prio_lo = 0, prio_hi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+        const char* pp = getenv("DCEGM_PACK_PRIO");
+        CK(cudaStreamCreateWithPriority(&h->s_pack, cudaStreamNonBlocking, pp && atoi(pp) ? prio_hi : prio_lo));
         CK(cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking));
     }
     while (h->ev_pool.size() < (size_t)3 * nchunks) {
@@ -298,6 +304,7 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     if (compact) {
         if ((rc = ensure(h, h->cmp_aux, sizeof(int32_t) * cslots, false))) return rc;
         if ((rc = ensure(h, h->cmp_wsize, sizeof(int32_t) * cslots, false))) return rc;
+        if ((rc = ensure(h, h->cmp_codes, sizeof(unsigned) * cslots * l.cap, false))) return rc;
     }
     // compact records never exceed 2 n + 1 words (one explicit run), packed lines 2 n
     const size_t pack_bytes = compact ? sizeof(double) * cslots * (2 * (size_t)l.cap + 1) : sizeof(double2) * cslots * l.cap;
@@ -330,8 +337,8 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
         if (c >= 1) CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * (c - 1) + 1], 0));  // pack_off still read by pack c-1
         cudaError_t e;
         if (compact) {
-            e = launch_compact_count(B, c0, cnt, (int32_t*)h->cmp_aux.p, (int32_t*)h->cmp_wsize.p, pin_aux_dev,
-                                     pin_aux_dev + cslots, h->s_pack);
+            e = launch_compact_count(B, c0, cnt, (int32_t*)h->cmp_aux.p, (int32_t*)h->cmp_wsize.p, (unsigned*)h->cmp_codes.p,
+                                     pin_aux_dev, pin_aux_dev + cslots, h->s_pack);
             if (e != cudaSuccess) return cuda_fail(h, e, "compact count kernel");
             e = launch_chunk_offsets((const int32_t*)h->cmp_wsize.p, nsl, 0x7fffffff, (long long*)h->pack_off.p, pin_off_dev, h->s_pack);
         } else {
@@ -354,7 +361,8 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
         double2* buf = (double2*)((c & 1) ? h->pack_xy2.p : h->pack_xy.p);
         if (c >= 2) CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * (c - 2) + 2], 0));  // buffer free again
         if (compact)
-            e = launch_compact_write(B, c0, cnt, (const int32_t*)h->cmp_aux.p, (const long long*)h->pack_off.p, (double*)buf, h->s_pack);
+            e = launch_compact_write(B, c0, cnt, (const int32_t*)h->cmp_aux.p, (const unsigned*)h->cmp_codes.p,
+                                     (const long long*)h->pack_off.p, (double*)buf, h->s_pack);
         else
             e = launch_pack_lines(B, c0, cnt, (const long long*)h->pack_off.p, buf, h->s_pack);
         if (e != cudaSuccess) return cuda_fail(h, e, "pack kernel");
@@ -470,7 +478,7 @@ int dcegm_destroy(dcegm_handle h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     DevBuf* bufs[] = {&h->models, &h->grids, &h->off, &h->wgt, &h->lines, &h->lens, &h->vbound, &h->meta, &h->isects,
-                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2, &h->big_scratch, &h->cmp_aux, &h->cmp_wsize,
+                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2, &h->big_scratch, &h->cmp_aux, &h->cmp_wsize, &h->cmp_codes,
                       &h->simm, &h->yvec, &h->mom, &h->rhist, &h->sstat, &h->pan_d, &h->pan_i, &h->pan_ret,
                       &h->sh_w, &h->sh_d, &h->sh_r, &h->sh_w0, &h->sh_y0};
     for (DevBuf* b : bufs)
@@ -687,7 +695,9 @@ int dcegm_fetch_compact(dcegm_handle h, int first, int count, double* words, siz
     if ((rc = ensure(h, h->cmp_aux, sizeof(int32_t) * nsl, false))) return rc;
     if ((rc = ensure(h, h->cmp_wsize, sizeof(int32_t) * nsl, false))) return rc;
     if ((rc = ensure(h, h->pack_off, sizeof(long long) * (nsl + 1), false))) return rc;
-    cudaError_t e = launch_compact_count(h->batch, first, count, (int32_t*)h->cmp_aux.p, (int32_t*)h->cmp_wsize.p, nullptr, nullptr, h->stream);
+    if ((rc = ensure(h, h->cmp_codes, sizeof(unsigned) * nsl * l.cap, false))) return rc;
+    cudaError_t e = launch_compact_count(h->batch, first, count, (int32_t*)h->cmp_aux.p, (int32_t*)h->cmp_wsize.p,
+                                         (unsigned*)h->cmp_codes.p, nullptr, nullptr, h->stream);
     if (e != cudaSuccess) return cuda_fail(h, e, "compact count kernel");
     std::vector<int32_t> wsize(nsl);
     CK(cudaMemcpyAsync(wsize.data(), h->cmp_wsize.p, sizeof(int32_t) * nsl, cudaMemcpyDeviceToHost, h->stream));
@@ -703,7 +713,8 @@ int dcegm_fetch_compact(dcegm_handle h, int first, int count, double* words, siz
     if ((size_t)*nwords > cap_words) return fail(h, DCEGM_E_CAPACITY, "dcegm_fetch_compact: destination too small");
     if ((rc = ensure(h, h->pack_xy, sizeof(double) * (size_t)*nwords, false))) return rc;
     CK(cudaMemcpyAsync(h->pack_off.p, woffsets, sizeof(int64_t) * (nsl + 1), cudaMemcpyHostToDevice, h->stream));
-    e = launch_compact_write(h->batch, first, count, (const int32_t*)h->cmp_aux.p, (const long long*)h->pack_off.p, (double*)h->pack_xy.p, h->stream);
+    e = launch_compact_write(h->batch, first, count, (const int32_t*)h->cmp_aux.p, (const unsigned*)h->cmp_codes.p,
+                             (const long long*)h->pack_off.p, (double*)h->pack_xy.p, h->stream);
     if (e != cudaSuccess) return cuda_fail(h, e, "compact write kernel");
     CK(cudaMemcpyAsync(words, h->pack_xy.p, sizeof(double) * (size_t)*nwords, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
