@@ -7,6 +7,7 @@
 #include <unistd.h>
 
 #include <cctype>
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -23,6 +24,9 @@ cudaError_t launch_solve_f(const DeviceBatch& B, int first, int count, cudaStrea
 cudaError_t launch_solve_f_big(const DeviceBatch& B, int first, int count, unsigned char* scratch, cudaStream_t stream,
                                int* nlaunch);
 size_t solver_f_big_scratch_bytes(int cap, int isec_cap);
+cudaError_t launch_solve_g_big(const DeviceBatch& B, int first, int count, unsigned char* scratch, cudaStream_t stream,
+                               int* nlaunch);
+size_t solver_g_big_scratch_bytes(int cap, int isec_cap, int ny);
 cudaError_t launch_solve_g(const DeviceBatch& B, int first, int count, cudaStream_t stream);
 cudaError_t launch_solve_minimal(const DeviceBatch& B, int first, int count, cudaStream_t stream);
 cudaError_t launch_pack_lines(const DeviceBatch& B, int first, int count, const long long* d_offsets, double2* d_dst,
@@ -35,8 +39,8 @@ cudaError_t launch_compact_write(const DeviceBatch& B, int first, int count, con
                                  const long long* off, double* dst, cudaStream_t stream);
 cudaError_t launch_sweep_records(const dcegm_summary* summ, const double* mom, const int32_t* sim_status, int nmodels, int nT,
                                  int nT_pad, size_t rec_bytes, unsigned char* dst, cudaStream_t stream);
-cudaError_t launch_sim(const DeviceBatch& B, const SimBatch& Sb, int first, int count, cudaStream_t stream);
-size_t sim_smem_bytes(const dcegm_layout& l);
+cudaError_t launch_sim(const DeviceBatch& B, const SimBatch& Sb, int first, int count, int max_smem_optin, cudaStream_t stream);
+size_t sim_smem_bytes(const dcegm_layout& l, bool global_lines);
 int expand_compact(const HostTables& tab, int nT, int nstate, int first, int count, const double* words, const int64_t* woff,
                    const int32_t* lens, const int32_t* aux, double* xy, size_t cap_points, int64_t* offsets, int nthreads);
 int decode_compact_pair(const double* a, int na, const double* rec_c, int n_c, int aux_c, const double* rec_v, int n_v, int aux_v,
@@ -62,6 +66,7 @@ struct dcegm_ctx {
     int32_t* pin_aux = nullptr;   // compact delivery: per-slot run/explicit counts and lengths of a chunk (host-mapped)
     size_t pin_slots = 0;
     DevBuf cmp_aux, cmp_wsize, cmp_codes;
+    DevBuf order;         // launch order of whole-batch solves (costliest models first)
     DevBuf pack_xy2;
     DevBuf big_scratch;   // fine-grid retirement solver (solver_f_big.cu): per-model working lines + envelope scratch
     bool big = false;     // the uploaded batch runs on the fine-grid solver
@@ -124,10 +129,13 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
     size_t smem = model == DCEGM_MODEL_F   ? solver_f_smem_bytes(lay.cap, lay.isec_cap)
                   : model == DCEGM_MODEL_G ? solver_g_smem_bytes(lay.cap, lay.isec_cap, na, ny)
                                            : (size_t)(6 * (na + 1) * 8 + 1024);
-    // retirement model on a grid too fine for one SM's shared memory: the fine-grid solver (lines in global memory)
-    h->big = model == DCEGM_MODEL_F &&
+    // retirement / general model on a grid too fine for one SM's shared memory: the fine-grid solvers (lines in
+    // global memory, solver_f_big.cu / solver_g_big.cu)
+    const bool can_big = model == DCEGM_MODEL_F || model == DCEGM_MODEL_G;
+    h->big = can_big &&
              ((flags & DCEGM_FORCE_FINE_GRID) || lay.cap >= 2 * kSearchTop || (long long)smem > (long long)h->max_smem_optin);
     if (h->big) lay.seg_cap = lay.cap;
+    if (h->big && model == DCEGM_MODEL_G && ny > kMaxNy) return fail(h, DCEGM_E_INVALID, "ny > 64 is not supported by the fine-grid general-model solver");
     if (h->big && lay.cap >= 65536) return fail(h, DCEGM_E_INVALID, "na too large: polylines are indexed with 16 bits (na < ~52000)");
     if (!h->big && lay.cap >= 2 * kSearchTop) return fail(h, DCEGM_E_INVALID, "na too large for the shared-memory resident solver");
     if (!h->big && (long long)smem > (long long)h->max_smem_optin) {
@@ -157,8 +165,11 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
         if ((rc = ensure(h, h->dirty, sizeof(double2) * nslots * na, true))) return rc;
     if ((rc = ensure(h, h->status, sizeof(int32_t) * nmodels, true))) return rc;
     if ((rc = ensure(h, h->summaries, sizeof(dcegm_summary) * nmodels, true))) return rc;
-    if (h->big)
-        if ((rc = ensure(h, h->big_scratch, solver_f_big_scratch_bytes(lay.cap, lay.isec_cap) * nmodels, false))) return rc;
+    if (h->big) {
+        const size_t per_model = model == DCEGM_MODEL_F ? solver_f_big_scratch_bytes(lay.cap, lay.isec_cap)
+                                                        : solver_g_big_scratch_bytes(lay.cap, lay.isec_cap, ny);
+        if ((rc = ensure(h, h->big_scratch, per_model * nmodels, false))) return rc;
+    }
 
     CK(cudaEventRecord(h->ev[0], h->stream));
     CK(cudaMemcpyAsync(h->models.p, h->tab.models.data(), sizeof(DevModel) * nmodels, cudaMemcpyHostToDevice, h->stream));
@@ -189,6 +200,22 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
     B.dirty = lay.has_dirty ? (double2*)h->dirty.p : nullptr;
     B.status = (int32_t*)h->status.p;
     B.summaries = (dcegm_summary*)h->summaries.p;
+    B.order = nullptr;
+    // Whole-batch solves start the costliest models first (longest-processing-time order): one CTA solves one model, and
+    // the envelope makes small-lambda models several times dearer than smooth ones, so the last wave should be cheap ones.
+    // The taste-shock scale is the predictor.  Chunked solves (dcegm_solve_*_packed/_compact) keep the batch order.
+    {
+        const char* e = getenv("DCEGM_LPT");
+        if ((model == DCEGM_MODEL_F || model == DCEGM_MODEL_G) && !h->big && nmodels > 1 && (!e || atoi(e) != 0)) {
+            std::vector<int32_t> ord(nmodels);
+            for (int i = 0; i < nmodels; i++) ord[i] = i;
+            std::stable_sort(ord.begin(), ord.end(), [&](int32_t a, int32_t b) { return params[a].lambda < params[b].lambda; });
+            if ((rc = ensure(h, h->order, sizeof(int32_t) * nmodels, false))) return rc;
+            CK(cudaMemcpyAsync(h->order.p, ord.data(), sizeof(int32_t) * nmodels, cudaMemcpyHostToDevice, h->stream));
+            CK(cudaStreamSynchronize(h->stream));
+            B.order = (const int32_t*)h->order.p;
+        }
+    }
     h->flags = flags;
     h->uploaded = true;
     return DCEGM_OK;
@@ -196,6 +223,8 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
 
 cudaError_t launch_range(dcegm_ctx* h, const DeviceBatch& B, int first, int count, cudaStream_t stream) {
     h->launches_last = 1;
+    if (h->big && B.lay.model == DCEGM_MODEL_G)
+        return launch_solve_g_big(B, first, count, (unsigned char*)h->big_scratch.p, stream, &h->launches_last);
     if (h->big) return launch_solve_f_big(B, first, count, (unsigned char*)h->big_scratch.p, stream, &h->launches_last);
     if (B.lay.model == DCEGM_MODEL_F) return launch_solve_f(B, first, count, stream);
     if (B.lay.model == DCEGM_MODEL_G) return launch_solve_g(B, first, count, stream);
@@ -319,8 +348,10 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     CK(cudaMemsetAsync(B.meta, 0, sizeof(dcegm_env_meta) * nstates, h->stream));
     CK(cudaMemsetAsync(B.vbound, 0, sizeof(double) * nstates * 2, h->stream));
     int launches = 0;
+    DeviceBatch Bc = B;  // chunks are contiguous model ranges: batch order
+    Bc.order = nullptr;
     for (int c = 0; c < nchunks; c++) {
-        cudaError_t e = launch_range(h, B, cstart[c], ccount[c], h->stream);
+        cudaError_t e = launch_range(h, Bc, cstart[c], ccount[c], h->stream);
         if (e != cudaSuccess) return cuda_fail(h, e, "kernel launch");
         launches += h->launches_last;
         CK(cudaEventRecord(h->ev_pool[3 * c], h->stream));
@@ -478,7 +509,7 @@ int dcegm_destroy(dcegm_handle h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     DevBuf* bufs[] = {&h->models, &h->grids, &h->off, &h->wgt, &h->lines, &h->lens, &h->vbound, &h->meta, &h->isects,
-                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2, &h->big_scratch, &h->cmp_aux, &h->cmp_wsize, &h->cmp_codes,
+                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2, &h->big_scratch, &h->cmp_aux, &h->cmp_wsize, &h->cmp_codes, &h->order,
                       &h->simm, &h->yvec, &h->mom, &h->rhist, &h->sstat, &h->pan_d, &h->pan_i, &h->pan_ret,
                       &h->sh_w, &h->sh_d, &h->sh_r, &h->sh_w0, &h->sh_y0};
     for (DevBuf* b : bufs)
@@ -830,7 +861,8 @@ int dcegm_simulate(dcegm_handle h, unsigned flags, const dcegm_sim_shocks* sh) {
     const dcegm_layout& l = B.lay;
     if (l.model != DCEGM_MODEL_F && l.model != DCEGM_MODEL_G) return fail(h, DCEGM_E_INVALID, "dcegm_simulate: the resident solution is not an FModel / GModel");
     if (!B.lines) return fail(h, DCEGM_E_NOSOLUTION, "dcegm_simulate needs the stored lines (solve without DCEGM_SUMMARY_ONLY)");
-    if ((long long)sim_smem_bytes(l) > (long long)h->max_smem_optin) return fail(h, DCEGM_E_INVALID, "dcegm_simulate: lines of one period do not fit into shared memory");
+    // lines of one period that do not fit into shared memory are read in place (sim_kernel<.., GL = true>)
+    if ((long long)sim_smem_bytes(l, true) > (long long)h->max_smem_optin) return fail(h, DCEGM_E_INVALID, "dcegm_simulate: nT * ny tables do not fit into shared memory");
     if (l.ny > 256 || l.nT > 65533) return fail(h, DCEGM_E_INVALID, "dcegm_simulate: ny <= 256 and nT <= 65533 (packed agent state)");
     const int n = l.nmodels, nT = l.nT;
     const bool panel = flags & DCEGM_SIM_PANEL;
@@ -881,7 +913,7 @@ int dcegm_simulate(dcegm_handle h, unsigned flags, const dcegm_sim_shocks* sh) {
         if ((rc = up(h->sh_y0, sh->ystate0, sizeof(int32_t) * nsims, (const void**)&Sb.y0))) return rc;
     }
     CK(cudaEventRecord(h->ev[0], h->stream));
-    cudaError_t e = launch_sim(B, Sb, 0, n, h->stream);
+    cudaError_t e = launch_sim(B, Sb, 0, n, h->max_smem_optin, h->stream);
     if (e != cudaSuccess) return cuda_fail(h, e, "simulation kernel launch");
     CK(cudaEventRecord(h->ev[1], h->stream));
     CK(cudaStreamSynchronize(h->stream));

@@ -64,6 +64,7 @@ struct DeviceBatch {
     int32_t* status;         // [nmodels]
     dcegm_summary* summaries;  // [nmodels]
     int first;               // first model of this launch (grid = number of models of the launch)
+    const int32_t* order;    // launch order of a whole-batch solve: CTA b solves model order[b] (null: model first + b)
 };
 
 // inputs / outputs of the forward simulator (solver_sim.cu)
@@ -204,8 +205,11 @@ __device__ __forceinline__ int knot_bucket(const KnotIndex& K, double q) {
 }
 // largest power of two nb such that nlines tables of nb+1 entries fit into `bytes`
 __host__ __device__ inline int knot_index_buckets(int bytes, int nlines) {
+#ifndef DC_KNOT_MAXNB
+#define DC_KNOT_MAXNB 2048
+#endif
     int nb = 16;
-    while (nb < 2048 && nlines * (2 * nb + 8) * 2 <= bytes) nb *= 2;  // stride (nb + 8) entries: 16-byte aligned
+    while (nb < DC_KNOT_MAXNB && nlines * (2 * nb + 8) * 2 <= bytes) nb *= 2;  // stride (nb + 8) entries: 16-byte aligned
     return nb;
 }
 // lo / inv / top of the index over knots x[0..n) with nb buckets

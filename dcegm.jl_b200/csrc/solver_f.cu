@@ -41,7 +41,7 @@ __device__ unsigned long long dc_phase_total[kPhaseSlots];
 #endif
 
 __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_f_kernel(DeviceBatch B) {
-    const int m = B.first + blockIdx.x;
+    const int m = B.order ? B.order[B.first + blockIdx.x] : B.first + blockIdx.x;
     const int tid = threadIdx.x;
 #ifdef DCEGM_PHASE_CLOCKS
     if (tid == 0) {
@@ -76,7 +76,11 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_f_kernel(DeviceBat
                             isfinite(p.oneover_oneminusgamma) && dc_is_norm_pos(p.cfloor) && p.lambda > 1e-100 && p.lambda < 1e100;
     // knot-index tables alias the envelope's Tx/Ty arrays (free during the EGM step)
     const int tab0 = S.o_d(3);
+#ifdef DC_KNOT_WIDE  // the tables may run over the whole envelope scratch behind the dirty line (free during the EGM step)
+    const int nbuck = knot_index_buckets((int)S.bytes() - 3 * P.cap8, 3);
+#else
     const int nbuck = knot_index_buckets(2 * P.cap8, 3);
+#endif
     const int tab_stride = (nbuck + 8) * 2;
     // this period's income offsets and the quadrature weights, staged once (the EGM loops read them per node)
     __shared__ double s_off[2 * kMaxNy], s_wgt[kMaxNy];

@@ -71,7 +71,7 @@ __device__ inline void store_line_g(const DeviceBatch& B, int m, int it, int iy,
 // Top = largest step of the fixed-trip knot search (lines hold fewer than 2*Top points; chosen at launch from cap)
 template <int Top>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBatch B) {
-    const int m = B.first + blockIdx.x;
+    const int m = B.order ? B.order[B.first + blockIdx.x] : B.first + blockIdx.x;
     const int tid = threadIdx.x;
     __shared__ DevModel s_p;
     __shared__ int s_status;

@@ -31,8 +31,10 @@ constexpr int kSimSubMax = 8;
 __host__ __device__ constexpr int sim_sub(int model) { return model == DCEGM_MODEL_G ? 8 : 1; }
 
 
-size_t sim_smem_bytes(const dcegm_layout& l) {
-    const size_t lines = (size_t)l.nstate * 8 * l.cap * sizeof(double);
+// global_lines: the variant that reads the polylines in place (HBM / L2) instead of staging them per period — for
+// lines too long for shared memory
+size_t sim_smem_bytes(const dcegm_layout& l, bool global_lines) {
+    const size_t lines = global_lines ? 0 : (size_t)l.nstate * 8 * l.cap * sizeof(double);
     const size_t tabs = ((size_t)l.ny * l.ny + (size_t)l.nT * l.ny + (size_t)l.nT * DCEGM_SIM_NMOM +
                          (size_t)kSimSubMax * kWarps * DCEGM_SIM_NMOM +
                          (size_t)l.nstate * 2) * sizeof(double);
@@ -50,8 +52,46 @@ __device__ __forceinline__ double sim_vfun(bool worker_line, bool terminal, doub
     return interp_y<Top>(vx, vy, n, m1);
 }
 
-// Top = largest step of the fixed-trip knot search: lines hold fewer than 2*Top points (chosen at launch from cap)
-template <int MODEL, int Top>
+// The same interpolation on a stored line (interleaved (x, y) points in HBM): the operations of interp_y / interp_at
+// (device_common.cuh) in the same order, so both variants of the simulator give the same bits.
+template <int Top>
+__device__ __forceinline__ double interp_y_aos(const double2* __restrict__ L, int n, double q) {
+    int lo = 0;
+#pragma unroll
+    for (int step = Top; step >= 1; step >>= 1) {
+        const int idx = lo + step - 1;
+        const bool ok = idx < n && L[idx < n ? idx : 0].x <= q;
+        lo = ok ? lo + step : lo;
+    }
+    int i = lo - 1;
+    i = i < 0 ? 0 : i;
+    i = i > n - 2 ? n - 2 : i;
+    const double2 p0 = L[0], p1 = L[1], pa = L[n - 2], pb = L[n - 1];
+    if (q < p0.x) {
+        double d = p1.x - p0.x;
+        return p0.y + ((p1.y - p0.y) / d) * (q - p0.x);
+    }
+    if (q > pb.x) {
+        double d = pb.x - pa.x;
+        return pb.y + ((pb.y - pa.y) / d) * (q - pb.x);
+    }
+    const double2 a = L[i], b = L[i + 1];
+    double f = (q - a.x) / (b.x - a.x);
+    return (1.0 - f) * a.y + f * b.y;
+}
+
+template <int Top>
+__device__ __forceinline__ double sim_vfun_aos(bool worker_line, bool terminal, double c1, double m1, const double2* L, int n,
+                                               double vb, const DevModel& p) {
+    if (terminal && p.nu > 0) return p.nu * u_plain(c1 + p.bbar, p) - 0.0;
+    const bool mask = terminal || (m1 < L[1].x);
+    if (mask) return u_work(c1, worker_line, p) + p.beta * vb;
+    return interp_y_aos<Top>(L, n, m1);
+}
+
+// Top = largest step of the fixed-trip knot search: lines hold fewer than 2*Top points (chosen at launch from cap).
+// GL: read the lines in place (global memory) instead of staging each period's lines into shared memory.
+template <int MODEL, int Top, bool GL = false>
 __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatch Sb) {
     const int m = B.first + blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -74,7 +114,7 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
 
     // shared-memory map
     double* ln = reinterpret_cast<double*>(dc_smem);                 // [nstate][id][kind][x|y][cap]
-    double* gg = ln + (size_t)nstate * 8 * cap;                      // [ny][ny] cumulative transition rows
+    double* gg = ln + (GL ? (size_t)0 : (size_t)nstate * 8 * cap);   // [ny][ny] cumulative transition rows
     double* inctab = gg + ny * ny;                                   // [nT][ny] income(it+1, yvec)
     double* mom = inctab + nT * ny;                                  // [nT][NMOM]
     double* red = mom + nT * DCEGM_SIM_NMOM;                         // [kSimSub][kWarps][NMOM] warp sums of one period
@@ -141,7 +181,7 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
                 lens[s] = n < cap ? n : cap;
             }
             for (int s = tid; s < nstate * 2; s += kThreads) vb[s] = B.vbound[((size_t)m * nT + it) * nstate * 2 + s];
-            {   // all (slot, point) pairs of the period in one flat loop: independent loads, no per-slot chain
+            if (!GL) {   // all (slot, point) pairs of the period in one flat loop: independent loads, no per-slot chain
                 const size_t slot0 = ((size_t)m * nT + it) * nstate * 4;
                 const double2* src0 = B.lines + slot0 * (size_t)cap;
                 const int32_t* len0 = B.lens + slot0;
@@ -238,7 +278,11 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
                 // ---- consumption, utility, end-of-period wealth (simulate.jl:106-110) ----
                 const int st = MODEL == DCEGM_MODEL_G ? ysa : 0;
                 const int id = wk ? 0 : 1;
-                const double cons = interp_y<Top>(line(st, id, 0, 0), line(st, id, 0, 1), lens[(st * 2 + id) * 2 + 0], w0);
+                // lines of this period in HBM (GL variant): slot (st, id, kind)
+                const double2* gl0 = B.lines + (((size_t)m * nT + it) * nstate * 4) * (size_t)cap;
+                auto gline = [&](int st_, int id_, int kind_) { return gl0 + (size_t)((st_ * 2 + id_) * 2 + kind_) * cap; };
+                const double cons = GL ? interp_y_aos<Top>(gline(st, id, 0), lens[(st * 2 + id) * 2 + 0], w0)
+                                       : interp_y<Top>(line(st, id, 0, 0), line(st, id, 0, 1), lens[(st * 2 + id) * 2 + 0], w0);
                 const double util = u_work(cons, wk, p);
                 double w1n = w0 - cons;
                 if (MODEL == DCEGM_MODEL_F) w1n = w1n > a_hi ? a_hi : (w1n < a_lo ? a_lo : w1n);  // clamp!, simulate.jl:109
@@ -248,10 +292,16 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
                 const bool term = it == nT - 1;
                 double pw = 0.0;  // retirees: simulate.jl:121 sets 0 whatever the values are
                 if (wk) {
-                    const double v1 = sim_vfun<Top>(true, term, cons, w0, line(st, 0, 1, 0), line(st, 0, 1, 1),
-                                                    lens[(st * 2 + 0) * 2 + 1], vb[st * 2 + 0], p);
-                    const double v2 = sim_vfun<Top>(false, term, cons, w0, line(st, 1, 1, 0), line(st, 1, 1, 1),
-                                                    lens[(st * 2 + 1) * 2 + 1], vb[st * 2 + 1], p);
+                    double v1, v2;
+                    if (GL) {
+                        v1 = sim_vfun_aos<Top>(true, term, cons, w0, gline(st, 0, 1), lens[(st * 2 + 0) * 2 + 1], vb[st * 2 + 0], p);
+                        v2 = sim_vfun_aos<Top>(false, term, cons, w0, gline(st, 1, 1), lens[(st * 2 + 1) * 2 + 1], vb[st * 2 + 1], p);
+                    } else {
+                        v1 = sim_vfun<Top>(true, term, cons, w0, line(st, 0, 1, 0), line(st, 0, 1, 1),
+                                           lens[(st * 2 + 0) * 2 + 1], vb[st * 2 + 0], p);
+                        v2 = sim_vfun<Top>(false, term, cons, w0, line(st, 1, 1, 0), line(st, 1, 1, 1),
+                                           lens[(st * 2 + 1) * 2 + 1], vb[st * 2 + 1], p);
+                    }
                     // the larger value's exponential is exp(0) = 1 exactly: one dc_exp instead of two
                     const bool w_hi = v1 > v2;
                     const double mx = w_hi ? v1 : v2;
@@ -320,19 +370,22 @@ __global__ void __launch_bounds__(kThreads, 3) sim_kernel(DeviceBatch B, SimBatc
     if (tid == 0) Sb.sim_status[m] = s_status;
 }
 
-cudaError_t launch_sim(const DeviceBatch& B0, const SimBatch& Sb, int first, int count, cudaStream_t stream) {
+cudaError_t launch_sim(const DeviceBatch& B0, const SimBatch& Sb, int first, int count, int max_smem_optin, cudaStream_t stream) {
     DeviceBatch B = B0;
     B.first = first;
-    const size_t smem = sim_smem_bytes(B.lay);
+    const bool gl = sim_smem_bytes(B.lay, false) > (size_t)max_smem_optin || B.lay.cap >= 2 * kSearchTop;
+    const size_t smem = sim_smem_bytes(B.lay, gl);
     cudaError_t e = cudaSuccess;
-#define DC_SIM_LAUNCH(MODEL, TOP)                                                                                  \
-    do {                                                                                                           \
-        e = cudaFuncSetAttribute(sim_kernel<MODEL, TOP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        if (e != cudaSuccess) return e;                                                                            \
-        sim_kernel<MODEL, TOP><<<count, kThreads, smem, stream>>>(B, Sb);                                          \
+#define DC_SIM_LAUNCH(...)                                                                                          \
+    do {                                                                                                            \
+        e = cudaFuncSetAttribute(sim_kernel<__VA_ARGS__>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);  \
+        if (e != cudaSuccess) return e;                                                                             \
+        sim_kernel<__VA_ARGS__><<<count, kThreads, smem, stream>>>(B, Sb);                                          \
     } while (0)
     const bool small = B.lay.cap < 256;  // na <= ~170: eight search steps instead of eleven
-    if (B.lay.model == DCEGM_MODEL_F) {
+    if (gl) {  // lines too long for shared memory: read in place, 16-step searches (cap < 65536)
+        if (B.lay.model == DCEGM_MODEL_F) DC_SIM_LAUNCH(DCEGM_MODEL_F, MemGlobal::kTop, true); else DC_SIM_LAUNCH(DCEGM_MODEL_G, MemGlobal::kTop, true);
+    } else if (B.lay.model == DCEGM_MODEL_F) {
         if (small) DC_SIM_LAUNCH(DCEGM_MODEL_F, 128); else DC_SIM_LAUNCH(DCEGM_MODEL_F, kSearchTop);
     } else {
         if (small) DC_SIM_LAUNCH(DCEGM_MODEL_G, 128); else DC_SIM_LAUNCH(DCEGM_MODEL_G, kSearchTop);

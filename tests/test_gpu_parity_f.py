@@ -174,14 +174,12 @@ def test_errors_are_codes_not_crashes(solver):
     with pytest.raises(_lib.DcegmError) as e:
         solver.solve(_abi.MODEL_F, [Param(par=dict(na=100)), Param(par=dict(na=200))])
     assert e.value.code == _abi.E_INVALID and "share" in str(e.value)
-    # grids too fine for shared memory go to the fine-grid solver (tests/test_gpu_parity_f_big.py); its polylines
-    # are indexed with 16 bits, and the general model has no fine-grid variant
-    with pytest.raises(_lib.DcegmError) as e:
-        solver.solve(_abi.MODEL_F, [Param(par=dict(na=60000))])
-    assert e.value.code == _abi.E_INVALID and "16 bits" in str(e.value)
-    with pytest.raises(_lib.DcegmError) as e:
-        solver.solve(_abi.MODEL_G, [Param(par=dict(na=5000))])
-    assert e.value.code == _abi.E_INVALID
+    # grids too fine for shared memory go to the fine-grid solvers (tests/test_gpu_parity_f_big.py,
+    # tests/test_gpu_parity_g_big.py); their polylines are indexed with 16 bits
+    for model in (_abi.MODEL_F, _abi.MODEL_G):
+        with pytest.raises(_lib.DcegmError) as e:
+            solver.solve(model, [Param(par=dict(na=60000))])
+        assert e.value.code == _abi.E_INVALID and "16 bits" in str(e.value)
 
 
 @pytest.mark.parametrize("n,na", [(5, 120), (700, 40)])
