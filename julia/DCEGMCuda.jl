@@ -51,13 +51,17 @@ end
 lasterr() = unsafe_string(ccall((:dcegm_last_error, LIB), Cstring, (Ptr{Cvoid},), handle()))
 check(rc) = rc == 0 || error("libdcegm_cuda ($rc): " * lasterr())
 
-# per-model status bits -> the exceptions the reference would raise (SURVEY.md §5)
+# per-model status bits -> the exceptions the reference would raise (SURVEY.md §5; bit values: include/dcegm.h).
+# Informational bits (DCEGM_ST_EXTRA_RIGHT 0x1000, DCEGM_ST_NONMONO_FIRST 0x2000) do not raise: runf returns normally.
+const ST_INFO_MASK = 0x1000 | 0x2000
 function raise_for_status(st::Integer)
-    st == 0 && return
-    st & 0x004 != 0 && error("knot-vectors must be unique and sorted in increasing order")  # line.jl:236
-    st & 0x008 != 0 && throw(ArgumentError("The interval [a,b] is not a bracketing interval"))  # envelope.jl:199
-    st & 0x020 != 0 && error("an upper envelope requires by definition at least 2 lines.")  # envelope.jl:149
-    st & 0x400 != 0 && error("neg cons")                                                     # simulate.jl:111-116
+    st & ~ST_INFO_MASK == 0 && return
+    st & 0x0004 != 0 && error("knot-vectors must be unique and sorted in increasing order")  # line.jl:236 (decreasing knots)
+    st & 0x4000 != 0 && error("knot-vectors must be unique and sorted in increasing order")  # line.jl:236 (repeated knot)
+    st & 0x0008 != 0 && throw(ArgumentError("The interval [a,b] is not a bracketing interval"))  # envelope.jl:199
+    st & 0x0010 != 0 && throw(BoundsError())                                                     # dc_algo.jl:486-491
+    st & 0x0020 != 0 && error("an upper envelope requires by definition at least 2 lines.")  # envelope.jl:149
+    st & 0x0400 != 0 && error("neg cons")                                                     # simulate.jl:111-116
     error("dcegm status 0x$(string(st, base = 16))")
 end
 
@@ -181,6 +185,44 @@ function solve_batch(ps::Vector{Param}; model = :f)
                 handle(), cp, length(cp), 0, xy, length(xy), off, np))
     st = Vector{Int32}(undef, length(ps)); check(ccall((:dcegm_status, LIB), Cint, (Ptr{Cvoid}, Ptr{Int32}), handle(), st))
     resize!(xy, np[]); xy, off, st   # line s (0-based slot order of include/dcegm.h) = xy[off[s+1]+1 : off[s+2]]
+end
+
+# ---- the same sweep in the compact line format (include/dcegm.h "compact lines"): half the bytes over PCIe; lines are
+# rebuilt lazily, one Envelope pair at a time, by the handle-free decoder ------------------------------------------
+struct CompactBatch
+    words::Vector{Float64}; woff::Vector{Int64}; lens::Vector{Int32}; aux::Vector{Int32}
+    grids::Vector{Vector{Float64}}   # savings grid of every model (dcegm_get_grid)
+    nT::Int; nstate::Int
+end
+
+function solve_batch_compact(ps::Vector{Param}; model = :f)
+    cp = CParam.(ps); l0 = ps[1]
+    nstate = model == :g ? l0.ny : 1
+    nslot = length(ps) * l0.nT * nstate * 4
+    cap = 8 * cld(l0.na + l0.na ÷ 10 + 2 * max(l0.na ÷ 16, 32) + 2, 8)
+    words = Vector{Float64}(undef, nslot * (2 * cap + 1)); woff = Vector{Int64}(undef, nslot + 1)
+    lens = Vector{Int32}(undef, nslot); aux = Vector{Int32}(undef, nslot); nw = Ref{Int64}(0)
+    f = model == :g ? :dcegm_solve_g_compact : :dcegm_solve_f_compact
+    check(ccall((f, LIB), Cint, (Ptr{Cvoid}, Ptr{CParam}, Cint, Cuint, Ptr{Float64}, Csize_t, Ptr{Int64}, Ptr{Int32}, Ptr{Int32}, Ref{Int64}),
+                handle(), cp, length(cp), 0, words, length(words), woff, lens, aux, nw))
+    resize!(words, nw[])
+    grids = map(0:length(ps)-1) do m
+        na = Ref{Cint}(0); g = Vector{Float64}(undef, ps[m + 1].na)
+        check(ccall((:dcegm_get_grid, LIB), Cint, (Ptr{Cvoid}, Cint, Ptr{Float64}, Cint, Ref{Cint}), handle(), m, g, length(g), na)); g
+    end
+    CompactBatch(words, woff, lens, aux, grids, l0.nT, nstate)
+end
+
+# policy and value line (Vector{Point}) of model m (1-based), period it, state iy, choice id
+function lines(b::CompactBatch, m, it, iy, id)
+    sc = ((((m - 1) * b.nT + (it - 1)) * b.nstate + (iy - 1)) * 2 + (id - 1)) * 2   # 0-based slot of the policy line
+    nc, nv = b.lens[sc + 1], b.lens[sc + 2]
+    c = Vector{Point{Float64}}(undef, nc); v = Vector{Point{Float64}}(undef, nv); g = b.grids[m]
+    rc = ccall((:dcegm_decode_compact_pair, LIB), Cint,
+               (Ptr{Float64}, Cint, Ptr{Float64}, Cint, Cint, Ptr{Float64}, Cint, Cint, Ptr{Cvoid}, Ptr{Cvoid}),
+               g, length(g), pointer(b.words, b.woff[sc + 1] + 1), nc, b.aux[sc + 1], pointer(b.words, b.woff[sc + 2] + 1), nv, b.aux[sc + 2], c, v)
+    rc == 0 || error("inconsistent compact record")
+    MLine(c), MLine(v)
 end
 
 end # module
