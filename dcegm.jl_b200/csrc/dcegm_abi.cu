@@ -67,6 +67,11 @@ struct dcegm_ctx {
     size_t pin_slots = 0;
     DevBuf cmp_aux, cmp_wsize, cmp_codes;
     DevBuf order;         // launch order of whole-batch solves (costliest models first)
+    // host tables of the last upload, page-locked in place (cudaHostRegister) so that their H2D copies run at full
+    // PCIe rate instead of through the driver's staging buffer; re-registered only when a vector moved or grew
+    struct Pinned { const void* p = nullptr; size_t bytes = 0; };
+    Pinned pin_tab[6];
+    long long pin_sig[5] = {-1, -1, -1, -1, -1};  // (model, nmodels, na, ny, nT) the registrations belong to
     DevBuf pack_xy2;
     DevBuf big_scratch;   // fine-grid retirement solver (solver_f_big.cu): per-model working lines + envelope scratch
     bool big = false;     // the uploaded batch runs on the fine-grid solver
@@ -116,6 +121,18 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
     if (!params || nmodels <= 0) return fail(h, DCEGM_E_INVALID, "params is null or nmodels <= 0");
     CK(cudaSetDevice(h->device));
     h->uploaded = h->solved = false;
+    {
+        // a batch of another geometry reallocates the table vectors: release their page locks first
+        const long long sig[5] = {model, nmodels, params[0].na, params[0].ny, params[0].nT};
+        if (memcmp(sig, h->pin_sig, sizeof sig) != 0) {
+            for (auto& r : h->pin_tab) {
+                if (r.p) cudaHostUnregister(const_cast<void*>(r.p));
+                r.p = nullptr;
+                r.bytes = 0;
+            }
+            memcpy(h->pin_sig, sig, sizeof sig);
+        }
+    }
     auto t0 = std::chrono::steady_clock::now();
     const char* why = "";
     if (!build_tables(model, params, nmodels, h->tab, &why)) return fail(h, DCEGM_E_INVALID, why);
@@ -171,6 +188,24 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
         if ((rc = ensure(h, h->big_scratch, per_model * nmodels, false))) return rc;
     }
 
+    {
+        const void* ptr[6] = {h->tab.models.data(), h->tab.grids.data(), h->tab.off.data(), h->tab.wgt.data(), h->tab.sim.data(), h->tab.yvec.data()};
+        const size_t len[6] = {sizeof(DevModel) * h->tab.models.size(), 0 /* grids: size varies with the parameters */, sizeof(double) * h->tab.off.size(),
+                               sizeof(double) * h->tab.wgt.size(), sizeof(SimModel) * h->tab.sim.size(), sizeof(double) * h->tab.yvec.size()};
+        for (int i = 0; i < 6; i++) {
+            dcegm_ctx::Pinned& r = h->pin_tab[i];
+            if (r.p == ptr[i] && r.bytes == len[i]) continue;
+            if (r.p) cudaHostUnregister(const_cast<void*>(r.p));
+            r.p = nullptr;
+            r.bytes = 0;
+            if (len[i] >= (64u << 10) && cudaHostRegister(const_cast<void*>(ptr[i]), len[i], cudaHostRegisterDefault) == cudaSuccess) {
+                r.p = ptr[i];
+                r.bytes = len[i];
+            } else {
+                cudaGetLastError();  // small tables, or registration refused: pageable copy
+            }
+        }
+    }
     CK(cudaEventRecord(h->ev[0], h->stream));
     CK(cudaMemcpyAsync(h->models.p, h->tab.models.data(), sizeof(DevModel) * nmodels, cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(h->grids.p, h->tab.grids.data(), sizeof(double) * h->tab.grids.size(), cudaMemcpyHostToDevice, h->stream));
@@ -519,6 +554,8 @@ int dcegm_destroy(dcegm_handle h) {
     for (auto& ev : h->ev_pool) cudaEventDestroy(ev);
     if (h->pin_off) cudaFreeHost(h->pin_off);
     if (h->pin_aux) cudaFreeHost(h->pin_aux);
+    for (auto& r : h->pin_tab)
+        if (r.p) cudaHostUnregister(const_cast<void*>(r.p));
     if (h->s_pack) cudaStreamDestroy(h->s_pack);
     if (h->s_copy) cudaStreamDestroy(h->s_copy);
     cudaStreamDestroy(h->stream);

@@ -43,7 +43,24 @@ with Solver(0) as s:
         rc = lib.dcegm_solve_f_packed(h, arr, n, 0, C.cast(pinned, C.POINTER(C.c_double)), cap_pts, op, C.byref(npts))
         assert rc == 0, lib.dcegm_last_error(h)
         ts.append(time.perf_counter() - t0)
+    # the same in the compact line format (dcegm_solve_f_compact): ordinates + abscissa runs
+    woff = np.zeros(nslots + 1, np.int64)
+    lens = np.zeros(nslots, np.int32)
+    aux = np.zeros(nslots, np.int32)
+    nw = C.c_int64()
+    lp, ip = C.POINTER(C.c_int64), C.POINTER(C.c_int32)
+    tc = []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        rc = lib.dcegm_solve_f_compact(h, arr, n, 0, C.cast(pinned, C.POINTER(C.c_double)), cap_pts * 2, woff.ctypes.data_as(lp),
+                                       lens.ctypes.data_as(ip), aux.ctypes.data_as(ip), C.byref(nw))
+        assert rc == 0, lib.dcegm_last_error(h)
+        tc.append(time.perf_counter() - t0)
+    st = s.status()
+    ok = int(((st.astype(np.int64) & _abi.ST_FATAL_MASK) == 0).sum())
     lib.dcegm_host_free(pinned)
+    print(json.dumps({"config": f"C4 e2e compact: FModel x{n} through dcegm_solve_f_compact", "e2e_ms": min(tc[1:]) * 1e3,
+                      "d2h_bytes": int(nw.value * 8), "solved": ok, "models_per_s_e2e_solved": ok / min(tc[1:])}))
     print(json.dumps({"config": f"C4 e2e: FModel x{n} (na=20000, nT=50, ny=32) through dcegm_solve_f_packed",
                       "resident_solve_ms": kernel_ms, "e2e_ms": min(ts[1:]) * 1e3, "d2h_bytes": int(npts.value * 16),
                       "d2h_gbs": npts.value * 16 / min(ts[1:]) / 1e9, "models_per_s_e2e": n / min(ts[1:])}))
