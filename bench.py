@@ -201,6 +201,12 @@ def main():
     if args.impl == "reference":
         return run_reference(args)
 
+    # stdout carries exactly one JSON line: libraries that print there while the job runs (NCCL's version banner on
+    # some boxes) go to stderr instead
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
+
     import torch
 
     from dcegm_jl_b200 import _abi
@@ -427,7 +433,10 @@ def main():
                                                             "on one laptop core (README.md:118-128)"}}
             if args.na == NA:
                 out["parity_in_run"] = parity_in_run(solver, arr, threads)
-        print(json.dumps(out))
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        print(json.dumps(out), flush=True)
+        os.dup2(2, 1)
     solver.close()
     if dist:
         dist.destroy_process_group()
