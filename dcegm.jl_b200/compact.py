@@ -82,10 +82,12 @@ class CompactLines:
 
     def runs(self, slot):
         """[(pos, src, kind)] of one slot (diagnostics, tests)"""
-        n = int(self.lens[slot])
         nrun = int(self.aux[slot]) & 0xFFFF
         w0 = int(self.woffsets[slot])
-        e = self.words[w0 + n: w0 + n + nrun].view(np.uint64)
+        if int(self.lens[slot]) == 0:
+            return []
+        yw = int(self.words[w0: w0 + 1].view(np.uint64)[0])
+        e = self.words[w0 + 1 + yw: w0 + 1 + yw + nrun].view(np.uint64)
         return [(int(v & 0xFFFF), int((v >> 16) & 0xFFFF), int((v >> 32) & 0xFFFF)) for v in e]
 
 
@@ -93,6 +95,31 @@ def encode_reference(lines_c, lines_v, grid):
     """Pure-numpy encoder of ONE (policy, value) pair following the format's rules (tests of the host decoder on a
     machine without a GPU; the product encoder is csrc/compact_lines.cu).  lines_*: (n, 2) arrays.  Returns
     (rec_c, aux_c, rec_v, aux_v)."""
+
+    def enc_y(y):
+        """ordinate section: I_0 | I_1 - I_0 | width bytes | payload of second differences (blocks of 32)"""
+        n = len(y)
+        if n == 0:
+            return np.zeros(0)
+        I = np.ascontiguousarray(y, float).view(np.uint64)
+        with np.errstate(over="ignore"):
+            head = [I[0]] + ([I[1:2] - I[0:1]][0].tolist() if n > 1 else [])
+            R = (I[2:] - 2 * I[1:-1] + I[:-2]).astype(np.uint64) if n > 2 else np.zeros(0, np.uint64)
+        widths, payload = [], bytearray()
+        for b0 in range(0, len(R), 32):
+            blk = R[b0:b0 + 32].view(np.int64)
+            w = 0
+            for r in blk:
+                r = int(r)
+                if r:
+                    bits = (r if r >= 0 else ~r).bit_length() + 1
+                    w = max(w, (bits + 7) // 8)
+            widths.append(w)
+            for r in blk:
+                payload += int(r).to_bytes(8, "little", signed=True)[:w]
+        wb = bytes(widths) + bytes(-len(widths) % 8)
+        payload += bytes(-len(payload) % 8)
+        return np.concatenate([np.array(head, np.uint64), np.frombuffer(wb + bytes(payload), np.uint64)]).view(np.float64)
 
     def enc(L, codes):
         n = len(L)
@@ -107,7 +134,11 @@ def encode_reference(lines_c, lines_v, grid):
             prev = (kind, src)
         if len(runs) + len(xs) > n + 1:
             runs, xs = [KIND_EXPLICIT << 32], list(L[:, 0])
-        rec = np.concatenate([L[:, 1], np.array(runs, np.uint64).view(np.float64), np.array(xs, float)]) if n else np.zeros(0)
+        if n == 0:
+            return np.zeros(0), 0
+        ysec = enc_y(L[:, 1])
+        rec = np.concatenate([np.array([len(ysec)], np.uint64).view(np.float64), ysec,
+                              np.array(runs, np.uint64).view(np.float64), np.array(xs, float)])
         return rec, len(runs) | (len(xs) << 16)
 
     cc = []

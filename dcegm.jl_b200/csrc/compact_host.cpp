@@ -19,12 +19,53 @@ inline uint64_t word_bits(double w) {
     return b;
 }
 
-// One slot: rec = y[n] | run[nrun] | xs[nx].  xc/nc: decoded points (interleaved x, y) of the slot's policy line for
-// REF runs (null for a policy line).  Writes n interleaved points to out.  false when the record is inconsistent.
+// The ordinate section (compact_lines.cu): I_0 | I_1 - I_0 | width bytes | payload of second differences of the
+// 64-bit patterns, blocks of 32.  Writes the n ordinates to out[2 k + 1].  false when the section is inconsistent.
+bool decode_y(const double* sec, int yw, int n, double* out) {
+    if (n <= 0) return yw == 0;
+    const int m = n > 2 ? n - 2 : 0, nblk = (m + 31) / 32;
+    const int head = (n < 2 ? n : 2) + (nblk + 7) / 8;
+    if (yw < head) return false;
+    uint64_t i0 = word_bits(sec[0]), i1 = n > 1 ? i0 + word_bits(sec[1]) : 0;
+    memcpy(&out[1], &i0, 8);
+    if (n > 1) memcpy(&out[3], &i1, 8);
+    const unsigned char* wb = reinterpret_cast<const unsigned char*>(sec + (n < 2 ? n : 2));
+    const unsigned char* pay = reinterpret_cast<const unsigned char*>(sec + head);
+    const size_t pay_cap = (size_t)(yw - head) * 8;
+    size_t at = 0;
+    uint64_t a = i0, b = i1;  // I_(k-2), I_(k-1)
+    for (int blk = 0; blk < nblk; blk++) {
+        const int w = wb[blk];
+        const int cnt = m - blk * 32 < 32 ? m - blk * 32 : 32;
+        if (w > 8 || at + (size_t)w * cnt > pay_cap) return false;
+        for (int j = 0; j < cnt; j++) {
+            uint64_t r = 0;
+            if (w) {
+                memcpy(&r, pay + at, w);  // little-endian host
+                if (w < 8 && (r >> (8 * w - 1)) & 1) r |= ~uint64_t(0) << (8 * w);  // sign extension
+                at += w;
+            }
+            const uint64_t c = r + 2 * b - a;
+            const int k = 2 + blk * 32 + j;
+            memcpy(&out[2 * k + 1], &c, 8);
+            a = b;
+            b = c;
+        }
+    }
+    return (at + 7) / 8 == (size_t)(yw - head);
+}
+
+// One slot: rec = head | ysec[yw] | run[nrun] | xs[nx].  xc/nc: decoded points (interleaved x, y) of the slot's policy
+// line for REF runs (null for a policy line).  Writes n interleaved points to out.  false when the record is
+// inconsistent.
 bool decode_slot(const double* rec, int n, int nrun, int nx, const double* a, int na, const double* xc, int nc, double* out) {
     if (n == 0) return nrun == 0 && nx == 0;
     if (nrun < 1) return false;
-    const double* runs = rec + n;
+    const uint64_t yw64 = word_bits(rec[0]);
+    if (yw64 > (uint64_t)n + (uint64_t)n / 256 + 4) return false;
+    const int yw = (int)yw64;
+    if (!decode_y(rec + 1, yw, n, out)) return false;
+    const double* runs = rec + 1 + yw;
     const double* xs = runs + nrun;
     int ix = 0;
     for (int r = 0; r < nrun; r++) {
@@ -36,25 +77,15 @@ bool decode_slot(const double* rec, int n, int nrun, int nx, const double* a, in
         switch (kind) {
             case 0:  // GRID: x = a[i] + y
                 if (src + len > na) return false;
-                for (int j = 0; j < len; j++) {
-                    const double y = rec[pos + j];
-                    out[2 * (pos + j)] = a[src + j] + y;
-                    out[2 * (pos + j) + 1] = y;
-                }
+                for (int j = 0; j < len; j++) out[2 * (pos + j)] = a[src + j] + out[2 * (pos + j) + 1];
                 break;
             case 1:  // REF: the policy line's abscissae
                 if (!xc || src + len > nc) return false;
-                for (int j = 0; j < len; j++) {
-                    out[2 * (pos + j)] = xc[2 * (src + j)];
-                    out[2 * (pos + j) + 1] = rec[pos + j];
-                }
+                for (int j = 0; j < len; j++) out[2 * (pos + j)] = xc[2 * (src + j)];
                 break;
             case 2:  // EXPLICIT
                 if (ix + len > nx) return false;
-                for (int j = 0; j < len; j++) {
-                    out[2 * (pos + j)] = xs[ix++];
-                    out[2 * (pos + j) + 1] = rec[pos + j];
-                }
+                for (int j = 0; j < len; j++) out[2 * (pos + j)] = xs[ix++];
                 break;
             default:
                 return false;

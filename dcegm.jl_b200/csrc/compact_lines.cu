@@ -10,8 +10,14 @@
 // bend-back points of the value line, ...) carry an explicit x.  The rules are verified per point on the device, so
 // the encoding is lossless whatever the solver produced (non-monotone or non-finite lines included).
 //
+// The ordinates themselves are smooth along a line, so they travel as the SECOND DIFFERENCES of their 64-bit patterns
+// (integer arithmetic modulo 2^64: exactly invertible), packed in blocks of 32 values with one byte width per block.
+//
 // Record of one line slot, in 8-byte words (include/dcegm.h, "compact lines"):
-//     y[n] | run[nrun] | xs[nx]
+//     head | ysec[yw] | run[nrun] | xs[nx]          head = yw (words of the ordinate section)
+//     ysec = I_0 | I_1 - I_0 | width bytes w_b of the ceil((n-2)/32) blocks, padded to 8 | payload, padded to 8
+//       I_k = bit pattern of y_k; block b holds R_k = I_k - 2 I_(k-1) + I_(k-2) for k = 2 + 32 b .. as little-endian
+//       two's-complement integers of w_b bytes (w_b = 0: all zero)
 //     run = pos | src << 16 | kind << 32 : points pos .. (next run's pos or n) - 1 take their abscissae from
 //       kind 0 (GRID)     x[pos + j] = a[src + j] + y[pos + j]          (one IEEE addition, as the kernels did)
 //       kind 1 (REF)      x[pos + j] = x of point src + j of the policy line of the same (model, it, iy, id)
@@ -98,7 +104,8 @@ struct ClassifyCtx {
 // which is then what is written.
 template <bool WRITE>
 __device__ void encode_line(const double2* __restrict__ L, int n, bool value_line, const ClassifyCtx& cx, unsigned* __restrict__ codes,
-                            bool force_explicit, int nrun_known, double* __restrict__ rec, int* nrun_out, int* nx_out) {
+                            bool force_explicit, double* __restrict__ rec_runs, double* __restrict__ rec_xs, int* nrun_out,
+                            int* nx_out) {
     __shared__ unsigned s_code[kCT + 1];
     __shared__ int s_warp[kCT / 32];
     __shared__ int s_tot;
@@ -146,13 +153,12 @@ __device__ void encode_line(const double2* __restrict__ L, int n, bool value_lin
         __syncthreads();
         const int excl = s_warp[wid] + inc - v;
         if (WRITE && k < n) {
-            rec[k] = pt.y;
             if (flag) {
                 const unsigned long long e = (unsigned long long)k | ((unsigned long long)(code & 0xffffu) << 16) |
                                              ((unsigned long long)(code >> 16) << 32);
-                rec[n + run_base + (excl & 0xffff)] = __longlong_as_double((long long)e);
+                rec_runs[run_base + (excl & 0xffff)] = __longlong_as_double((long long)e);
             }
-            if (isx) rec[n + nrun_known + x_base + (excl >> 16)] = pt.x;
+            if (isx) rec_xs[x_base + (excl >> 16)] = pt.x;
         }
         run_base += s_tot & 0xffff;
         x_base += s_tot >> 16;
@@ -163,10 +169,83 @@ __device__ void encode_line(const double2* __restrict__ L, int n, bool value_lin
     *nx_out = x_base;
 }
 
+// bytes of the shortest two's-complement form of r (0 for r == 0)
+__device__ __forceinline__ int signed_bytes(long long r) {
+    if (r == 0) return 0;
+    const int bits = 65 - __clzll(r ^ (r >> 63));  // magnitude bits + sign bit
+    return (bits + 7) >> 3;
+}
+__host__ __device__ inline int ysec_head_words(int n) {  // raw words + width bytes, in words
+    const int nblk = n > 2 ? (n - 2 + 31) / 32 : 0;
+    return (n < 2 ? n : 2) + (nblk + 7) / 8;
+}
+
+// The ordinate section of one line.  Count pass (WRITE = false): returns its size in words.  Write pass: fills `sec`
+// (8-byte aligned).  Warps and blocks of 32 residuals coincide, so a block's width is one warp reduction.
+template <bool WRITE>
+__device__ int encode_y(const double2* __restrict__ L, int n, double* __restrict__ sec) {
+    __shared__ int s_blk[kCT / 32];
+    __shared__ int s_sum;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (n == 0) return 0;
+    const int m = n > 2 ? n - 2 : 0;            // residuals
+    const int nblk = (m + 31) / 32;
+    const int head = ysec_head_words(n);
+    unsigned char* wbytes = reinterpret_cast<unsigned char*>(sec + (n < 2 ? n : 2));
+    unsigned char* payload = reinterpret_cast<unsigned char*>(sec + head);
+    if (WRITE && tid == 0) {
+        const long long i0 = __double_as_longlong(L[0].y);
+        sec[0] = __longlong_as_double(i0);
+        if (n > 1) sec[1] = __longlong_as_double((long long)((unsigned long long)__double_as_longlong(L[1].y) - (unsigned long long)i0));
+        for (int b = nblk; b < ((nblk + 7) / 8) * 8; b++) wbytes[b] = 0;  // padding of the width bytes
+    }
+    int base = 0;  // payload bytes of the tiles done so far (block-uniform)
+    for (int j0 = 0; j0 < m; j0 += kCT) {
+        const int j = j0 + tid;
+        long long r = 0;
+        if (j < m) {
+            const unsigned long long a = (unsigned long long)__double_as_longlong(L[j + 2].y);
+            const unsigned long long b = (unsigned long long)__double_as_longlong(L[j + 1].y);
+            const unsigned long long c = (unsigned long long)__double_as_longlong(L[j].y);
+            r = (long long)(a - 2ULL * b + c);
+        }
+        const int w = __reduce_max_sync(0xffffffffu, j < m ? signed_bytes(r) : 0);
+        const int cnt = m - (j0 + wid * 32) < 32 ? (m - (j0 + wid * 32) > 0 ? m - (j0 + wid * 32) : 0) : 32;
+        if (lane == 0) s_blk[wid] = w * cnt;
+        __syncthreads();
+        if (tid == 0) {
+            int run = 0;
+            for (int q = 0; q < kCT / 32; q++) {
+                const int t = s_blk[q];
+                s_blk[q] = run;
+                run += t;
+            }
+            s_sum = run;
+        }
+        __syncthreads();
+        if (WRITE && j < m) {
+            if (lane == 0) wbytes[(j0 >> 5) + wid] = (unsigned char)w;
+            unsigned char* dst = payload + base + s_blk[wid] + lane * w;
+            unsigned long long u = (unsigned long long)r;
+            for (int i = 0; i < w; i++) {
+                dst[i] = (unsigned char)(u & 0xffu);
+                u >>= 8;
+            }
+        }
+        base += s_sum;
+        __syncthreads();
+    }
+    if (WRITE && tid < 8) {  // padding of the payload
+        const int pad = ((base + 7) & ~7) - base;
+        if (tid < pad) payload[base + tid] = 0;
+    }
+    return head + (base + 7) / 8;
+}
+
 }  // namespace
 
 // sizes of the compact records of the slot pairs [first_pair, first_pair + gridDim.x) and the per-point codes:
-// aux[slot] = nrun | nx << 16, wsize[slot] = n + nrun + nx (words), codes[slot][cap]
+// aux[slot] = nrun | nx << 16, wsize[slot] = 1 + yw + nrun + nx (words; 0 for an empty slot), codes[slot][cap]
 __global__ void __launch_bounds__(kCT) compact_count_kernel(DeviceBatch B, size_t first_pair, int32_t* __restrict__ aux,
                                                             int32_t* __restrict__ wsize, unsigned* __restrict__ codes,
                                                             int32_t* __restrict__ aux_host, int32_t* __restrict__ lens_host) {
@@ -197,14 +276,15 @@ __global__ void __launch_bounds__(kCT) compact_count_kernel(DeviceBatch B, size_
         const int n = which ? nv : nc;
         const size_t s = (which ? sv : sc) - 2 * first_pair;
         int nrun, nx;
-        encode_line<false>(which ? Lv : cx.Lc, n, which == 1, cx, codes + s * (size_t)cap, false, 0, nullptr, &nrun, &nx);
+        encode_line<false>(which ? Lv : cx.Lc, n, which == 1, cx, codes + s * (size_t)cap, false, nullptr, nullptr, &nrun, &nx);
         if (nrun + nx > n + 1) {  // one explicit run is shorter
             nrun = 1;
             nx = n;
         }
+        const int yw = encode_y<false>(which ? Lv : cx.Lc, n, nullptr);
         if (threadIdx.x == 0) {
             aux[s] = nrun | (nx << 16);
-            wsize[s] = n + nrun + nx;
+            wsize[s] = n > 0 ? 1 + yw + nrun + nx : 0;
             if (aux_host) {  // host-mapped copies: no small transfer queues behind the bulk device-to-host copies
                 aux_host[s] = nrun | (nx << 16);
                 lens_host[s] = n;
@@ -231,9 +311,13 @@ __global__ void __launch_bounds__(kCT) compact_write_kernel(DeviceBatch B, size_
         const size_t s = (which ? sv : sc) - 2 * first_pair;
         const int ax = aux[s];
         const int nrun = ax & 0xffff, nx = (ax >> 16) & 0xffff;
+        if (n == 0) continue;  // block-uniform
+        double* rec = dst + off[s];
+        const int yw = encode_y<true>(which ? Lv : Lc, n, rec + 1);
+        if (threadIdx.x == 0) rec[0] = __longlong_as_double((long long)yw);
         int r, x;
         encode_line<true>(which ? Lv : Lc, n, which == 1, cx, const_cast<unsigned*>(codes) + s * (size_t)cap,
-                          n > 0 && nrun == 1 && nx == n, nrun, dst + off[s], &r, &x);
+                          nrun == 1 && nx == n, rec + 1 + yw, rec + 1 + yw + nrun, &r, &x);
     }
 }
 

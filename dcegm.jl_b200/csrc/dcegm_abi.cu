@@ -370,8 +370,8 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
         if ((rc = ensure(h, h->cmp_wsize, sizeof(int32_t) * cslots, false))) return rc;
         if ((rc = ensure(h, h->cmp_codes, sizeof(unsigned) * cslots * l.cap, false))) return rc;
     }
-    // compact records never exceed 2 n + 1 words (one explicit run), packed lines 2 n
-    const size_t pack_bytes = compact ? sizeof(double) * cslots * (2 * (size_t)l.cap + 1) : sizeof(double2) * cslots * l.cap;
+    // compact records never exceed 2 n + n / 256 + 4 words (full-width ordinates, one explicit run), packed lines 2 n
+    const size_t pack_bytes = compact ? sizeof(double) * cslots * (2 * (size_t)l.cap + l.cap / 256 + 4) : sizeof(double2) * cslots * l.cap;
     if ((rc = ensure(h, h->pack_xy, pack_bytes, false))) return rc;
     if (nchunks > 1)
         if ((rc = ensure(h, h->pack_xy2, pack_bytes, false))) return rc;
@@ -383,8 +383,22 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     CK(cudaMemsetAsync(B.meta, 0, sizeof(dcegm_env_meta) * nstates, h->stream));
     CK(cudaMemsetAsync(B.vbound, 0, sizeof(double) * nstates * 2, h->stream));
     int launches = 0;
-    DeviceBatch Bc = B;  // chunks are contiguous model ranges: batch order
+    DeviceBatch Bc = B;
     Bc.order = nullptr;
+    // chunks are contiguous model ranges (their lines are delivered in batch order); inside a chunk the costliest
+    // models (smallest taste-shock scale) start first, so that the tail of every chunk's launch is made of cheap ones
+    if (!h->big && nchunks > 1 && (model == DCEGM_MODEL_F || model == DCEGM_MODEL_G)) {
+        std::vector<int32_t> ord(nmodels);
+        for (int i = 0; i < nmodels; i++) ord[i] = i;
+        for (int c = 0; c < nchunks; c++)
+            std::stable_sort(ord.begin() + cstart[c], ord.begin() + cstart[c] + ccount[c],
+                             [&](int32_t a, int32_t b) { return params[a].lambda < params[b].lambda; });
+        if ((rc = ensure(h, h->order, sizeof(int32_t) * nmodels, false))) return rc;
+        CK(cudaMemcpyAsync(h->order.p, ord.data(), sizeof(int32_t) * nmodels, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaStreamSynchronize(h->stream));  // ord goes out of scope
+        Bc.order = (const int32_t*)h->order.p;
+        h->batch.order = Bc.order;  // still a permutation of the batch: later whole-batch runs may use it
+    }
     for (int c = 0; c < nchunks; c++) {
         cudaError_t e = launch_range(h, Bc, cstart[c], ccount[c], h->stream);
         if (e != cudaSuccess) return cuda_fail(h, e, "kernel launch");

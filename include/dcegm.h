@@ -256,15 +256,20 @@ int  dcegm_fetch_packed(dcegm_handle h, int first, int count, double* xy, size_t
  * and the value line of the same (period, state, choice) shares the policy line's abscissae (dc_algo.jl:78, :482,
  * :486-492).  The compact form ships the ordinates plus a few RUNS naming the source of each stretch of abscissae;
  * points for which neither rule reproduces the stored x bit for bit (verified per point on the device) carry an
- * explicit x.  Record of one line slot (slots in layout order [model][it][iy][id][kind]), in 8-byte words:
- *     y[n] | run[nrun] | xs[nx]          n = lens[slot], nrun = aux[slot] & 0xffff, nx = aux[slot] >> 16
+ * explicit x.  The ordinates, smooth along a line, travel as the second differences of their 64-bit patterns (integer
+ * arithmetic modulo 2^64, exactly invertible), byte-packed in blocks of 32.  Record of one line slot (slots in layout
+ * order [model][it][iy][id][kind]; an empty slot has no record), in 8-byte words:
+ *     head | ysec[yw] | run[nrun] | xs[nx]     head = yw; n = lens[slot], nrun = aux[slot] & 0xffff, nx = aux[slot] >> 16
+ *     ysec = I_0 | I_1 - I_0 | width bytes w_b of the ceil((n-2)/32) blocks, zero-padded to 8 | payload, zero-padded to 8
+ *       I_k = bit pattern of y_k; block b holds R_k = I_k - 2 I_(k-1) + I_(k-2), k = 2 + 32 b .., as little-endian
+ *       two's-complement integers of w_b bytes each (w_b = 0: all zero, 8: raw); n = 1: I_0 only
  *     run (64-bit integer) = pos | src << 16 | kind << 32; it covers points pos .. (next run's pos, or n) - 1:
  *       kind 0  x[pos + j] = a[src + j] + y[pos + j]     (a: the model's savings grid, dcegm_get_grid; one IEEE add)
  *       kind 1  x[pos + j] = x of point src + j of the POLICY line of the same (model, it, iy, id)   (value lines only)
  *       kind 2  x[pos + j] = next unread word of xs
  * woffsets[nslots + 1] are prefix offsets in words into `words`.  dcegm_solve_*_compact is dcegm_solve_*_packed with
  * this delivery format (same chunked pipeline; `words` from dcegm_host_alloc makes the copies asynchronous);
- * cap_words = nslots * (2 * cap + 1) always fits.  dcegm_fetch_compact encodes models [first, first + count) of the
+ * cap_words = nslots * (2 * cap + cap / 256 + 4) always fits (a C3 batch needs 0.49 words per point).  dcegm_fetch_compact encodes models [first, first + count) of the
  * resident solution (words == NULL: sizes only).  dcegm_expand_compact rebuilds the densely packed points of
  * dcegm_fetch_packed (bit-identical: tests/test_gpu_compact.py) on `nthreads` host threads, for the batch of the
  * handle's last solve; woffsets / lens / aux point at the first slot of model `first`, woffsets values are relative

@@ -47,7 +47,7 @@ def test_oracle_lines_roundtrip(oracle):
                 assert xv.tobytes() == np.ascontiguousarray(Lv).tobytes()
                 words_compact += len(rc) + len(rv)
                 words_full += 2 * (nc + nv)
-    assert words_compact < 0.56 * words_full  # the format halves the bytes
+    assert words_compact < 0.42 * words_full  # x dropped, ordinates packed: about a third of the bytes at na = 120
 
 
 def test_run_kinds_and_rejection():
@@ -57,22 +57,53 @@ def test_run_kinds_and_rejection():
     Lv = np.array([[0.0, -1.0], [1.5, -0.5], [2.0, 9.0], [3.5, 0.25]])
     rc, ac, rv, av = encode_reference(Lc, Lv, grid)
     assert (ac & 0xFFFF, ac >> 16) == (3, 1) and (av & 0xFFFF, av >> 16) == (3, 1)
-    runs_c = rc[4:7].view(np.uint64)
+    ywc, ywv = int(rc[:1].view(np.uint64)[0]), int(rv[:1].view(np.uint64)[0])  # head word: size of the ordinate section
+    assert ywc == 2 + 1 + 2 and ywv == 2 + 1 + 2  # I_0, I_1 - I_0, one word of width bytes, 2 residuals of 8 bytes
+    runs_c = rc[1 + ywc:1 + ywc + 3].view(np.uint64)
     assert [(int(v & 0xFFFF), int(v >> 16 & 0xFFFF), int(v >> 32)) for v in runs_c] == [(0, 0, KIND_GRID), (2, 0, KIND_EXPLICIT), (3, 3, KIND_GRID)]
-    runs_v = rv[4:7].view(np.uint64)
+    runs_v = rv[1 + ywv:1 + ywv + 3].view(np.uint64)
     assert [(int(v & 0xFFFF), int(v >> 16 & 0xFFFF), int(v >> 32)) for v in runs_v] == [(0, 0, KIND_REF), (2, 0, KIND_EXPLICIT), (3, 3, KIND_REF)]
     code, xc, xv = decode(grid, rc, 4, ac, rv, 4, av)
     assert code == 0 and np.array_equal(xc, Lc) and np.array_equal(xv, Lv)
     # a run that points beyond the grid, a missing explicit word, a run list that does not start at 0
+    r0 = 1 + ywc  # first run word
     bad = rc.copy()
-    bad[4:5] = np.array([0 | (3 << 16) | (KIND_GRID << 32)], np.uint64).view(np.float64)
+    bad[r0:r0 + 1] = np.array([0 | (3 << 16) | (KIND_GRID << 32)], np.uint64).view(np.float64)
     assert decode(grid, bad, 4, ac, rv, 4, av)[0] == _abi.E_INVALID
     assert decode(grid, rc, 4, 3, rv, 4, av)[0] == _abi.E_INVALID
     bad = rc.copy()
-    bad[4:5] = np.array([1 | (0 << 16) | (KIND_GRID << 32)], np.uint64).view(np.float64)
+    bad[r0:r0 + 1] = np.array([1 | (0 << 16) | (KIND_GRID << 32)], np.uint64).view(np.float64)
+    assert decode(grid, bad, 4, ac, rv, 4, av)[0] == _abi.E_INVALID
+    # an ordinate section that claims more words than the line can need, a block width above 8
+    bad = rc.copy()
+    bad[0:1] = np.array([1000], np.uint64).view(np.float64)
+    assert decode(grid, bad, 4, ac, rv, 4, av)[0] == _abi.E_INVALID
+    bad = rc.copy()
+    wb = bad[3:4].view(np.uint8)
+    wb[0] = 9
     assert decode(grid, bad, 4, ac, rv, 4, av)[0] == _abi.E_INVALID
     # empty slots
     assert decode(grid, np.zeros(1), 0, 0, np.zeros(1), 0, 0)[0] == 0
+
+
+def test_ordinate_packing_roundtrip_on_hostile_values():
+    """second differences of the bit patterns wrap modulo 2^64: any doubles survive, whatever their order of magnitude"""
+    rng = np.random.default_rng(5)
+    grid = np.array([0.0, 1.0])
+    for n in (1, 2, 3, 33, 34, 35, 70, 300):
+        y = rng.standard_normal(n) * 10.0 ** rng.integers(-300, 300, n)
+        y[rng.integers(0, n, 2)] = [np.inf, -0.0]
+        if n > 5:
+            y[5] = np.nan
+            y[n // 2:n // 2 + 3] = 1.25  # a stretch of equal values: zero residuals
+        L = np.stack([np.arange(n) * 7.0 + 100.0, y], axis=1)
+        rc, ac, rv, av = encode_reference(L, L[:0], grid)
+        code, xc, _ = decode(grid, rc, n, ac, np.zeros(1), 0, 0)
+        assert code == 0 and xc.tobytes() == L.tobytes(), n
+    smooth = np.stack([np.linspace(1, 2, 500) + 100, np.sqrt(np.linspace(1, 2, 500))], axis=1)
+    rc, ac, _, _ = encode_reference(smooth, smooth[:0], grid)
+    yw = int(rc[:1].view(np.uint64)[0])
+    assert yw <= 0.65 * 500  # smooth ordinates: 5 bytes per value instead of 8
 
 
 def test_negative_zero_and_nan_abscissae_survive():

@@ -1,6 +1,6 @@
 """Compact line delivery (dcegm_solve_*_compact / dcegm_fetch_compact): expanding the compact records on the host
 gives the densely packed points of dcegm_fetch_packed BIT FOR BIT — retirement model incl. envelope-heavy and
-status-flagged draws, fine-grid solver, general model — in about half the bytes."""
+status-flagged draws, fine-grid solver, general model — in about a third of the bytes."""
 import numpy as np
 import pytest
 
@@ -39,7 +39,7 @@ def test_retirement_batch_pipeline_equals_packed():
     with Solver(0) as s:
         cl = s.solve_compact(_abi.MODEL_F, ps)
         assert int(s.status()[91]) == _abi.ST_DUP_KNOT
-        r = check(s, cl, 0.53)
+        r = check(s, cl, 0.36)
         # the non-pipelined encoder of the resident solution gives the same stream
         cl2 = s.fetch_compact()
         assert cl2.words.tobytes() == cl.words.tobytes() and np.array_equal(cl2.woffsets, cl.woffsets)
@@ -62,7 +62,7 @@ def test_fine_grid_and_general_model():
 
     with Solver(0) as s:
         s.solve(_abi.MODEL_F, c3_draws(6, na=2400), fetch=False)  # fine-grid solver (lines in global memory)
-        check(s, s.fetch_compact(), 0.53)
+        check(s, s.fetch_compact(), 0.36)
         rng = np.random.default_rng(3)
         pg = []
         for _ in range(40):
@@ -71,7 +71,7 @@ def test_fine_grid_and_general_model():
             d["lambda"] = float(10 ** rng.uniform(np.log10(2e-7), 0))
             pg.append(Param(par=d))
         cl = s.solve_compact(_abi.MODEL_G, pg)
-        check(s, cl, 0.56)
+        check(s, cl, 0.50)
         # bequest variant: terminal lines on the full grid
         s.solve(_abi.MODEL_G, [Param(par=dict(na=100, nu=2.0))], fetch=False)
-        check(s, s.fetch_compact(), 0.60)
+        check(s, s.fetch_compact(), 0.55)
