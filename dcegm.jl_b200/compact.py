@@ -104,7 +104,9 @@ def encode_reference(lines_c, lines_v, grid):
         I = np.ascontiguousarray(y, float).view(np.uint64)
         with np.errstate(over="ignore"):
             head = [I[0]] + ([I[1:2] - I[0:1]][0].tolist() if n > 1 else [])
-            R = (I[2:] - 2 * I[1:-1] + I[:-2]).astype(np.uint64) if n > 2 else np.zeros(0, np.uint64)
+            R = np.zeros(n, np.uint64)  # blocks cover k = 32 b .. 32 b + 31; R_0 = R_1 = 0 (raw words in front)
+            if n > 2:
+                R[2:] = I[2:] - 2 * I[1:-1] + I[:-2]
         widths, payload = [], bytearray()
         for b0 in range(0, len(R), 32):
             blk = R[b0:b0 + 32].view(np.int64)

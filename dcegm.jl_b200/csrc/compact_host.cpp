@@ -20,10 +20,10 @@ inline uint64_t word_bits(double w) {
 }
 
 // The ordinate section (compact_lines.cu): I_0 | I_1 - I_0 | width bytes | payload of second differences of the
-// 64-bit patterns, blocks of 32.  Writes the n ordinates to out[2 k + 1].  false when the section is inconsistent.
+// 64-bit patterns, blocks of 32 points.  Writes the n ordinates to out[2 k + 1].  false when the section is inconsistent.
 bool decode_y(const double* sec, int yw, int n, double* out) {
     if (n <= 0) return yw == 0;
-    const int m = n > 2 ? n - 2 : 0, nblk = (m + 31) / 32;
+    const int nblk = (n + 31) / 32;  // block b: k = 32 b .. 32 b + 31; the residuals of k = 0, 1 are zero place-holders
     const int head = (n < 2 ? n : 2) + (nblk + 7) / 8;
     if (yw < head) return false;
     uint64_t i0 = word_bits(sec[0]), i1 = n > 1 ? i0 + word_bits(sec[1]) : 0;
@@ -36,7 +36,7 @@ bool decode_y(const double* sec, int yw, int n, double* out) {
     uint64_t a = i0, b = i1;  // I_(k-2), I_(k-1)
     for (int blk = 0; blk < nblk; blk++) {
         const int w = wb[blk];
-        const int cnt = m - blk * 32 < 32 ? m - blk * 32 : 32;
+        const int cnt = n - blk * 32 < 32 ? n - blk * 32 : 32;
         if (w > 8 || at + (size_t)w * cnt > pay_cap) return false;
         for (int j = 0; j < cnt; j++) {
             uint64_t r = 0;
@@ -45,8 +45,9 @@ bool decode_y(const double* sec, int yw, int n, double* out) {
                 if (w < 8 && (r >> (8 * w - 1)) & 1) r |= ~uint64_t(0) << (8 * w);  // sign extension
                 at += w;
             }
+            const int k = blk * 32 + j;
+            if (k < 2) continue;  // raw words
             const uint64_t c = r + 2 * b - a;
-            const int k = 2 + blk * 32 + j;
             memcpy(&out[2 * k + 1], &c, 8);
             a = b;
             b = c;

@@ -33,9 +33,9 @@ cudaError_t launch_pack_lines(const DeviceBatch& B, int first, int count, const 
                               cudaStream_t stream);
 cudaError_t launch_chunk_offsets(const int32_t* lens, size_t nsl, int cap, long long* d_off, long long* h_off_mapped,
                                  cudaStream_t stream);
-cudaError_t launch_compact_count(const DeviceBatch& B, int first, int count, int32_t* aux, int32_t* wsize, unsigned* codes,
+cudaError_t launch_compact_count(const DeviceBatch& B, int first, int count, int32_t* aux, int32_t* yws, int32_t* wsize, unsigned* codes,
                                  int32_t* aux_host, int32_t* lens_host, cudaStream_t stream);
-cudaError_t launch_compact_write(const DeviceBatch& B, int first, int count, const int32_t* aux, const unsigned* codes,
+cudaError_t launch_compact_write(const DeviceBatch& B, int first, int count, const int32_t* aux, const int32_t* yws, const unsigned* codes,
                                  const long long* off, double* dst, cudaStream_t stream);
 cudaError_t launch_sweep_records(const dcegm_summary* summ, const double* mom, const int32_t* sim_status, int nmodels, int nT,
                                  int nT_pad, size_t rec_bytes, unsigned char* dst, cudaStream_t stream);
@@ -65,7 +65,7 @@ struct dcegm_ctx {
     long long* pin_off = nullptr;
     int32_t* pin_aux = nullptr;   // compact delivery: per-slot run/explicit counts and lengths of a chunk (host-mapped)
     size_t pin_slots = 0;
-    DevBuf cmp_aux, cmp_wsize, cmp_codes;
+    DevBuf cmp_aux, cmp_wsize, cmp_codes, cmp_yw;
     DevBuf order;         // launch order of whole-batch solves (costliest models first)
     // host tables of the last upload, page-locked in place (cudaHostRegister) so that their H2D copies run at full
     // PCIe rate instead of through the driver's staging buffer; re-registered only when a vector moved or grew
@@ -368,6 +368,7 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     if (compact) {
         if ((rc = ensure(h, h->cmp_aux, sizeof(int32_t) * cslots, false))) return rc;
         if ((rc = ensure(h, h->cmp_wsize, sizeof(int32_t) * cslots, false))) return rc;
+        if ((rc = ensure(h, h->cmp_yw, sizeof(int32_t) * cslots, false))) return rc;
         if ((rc = ensure(h, h->cmp_codes, sizeof(unsigned) * cslots * l.cap, false))) return rc;
     }
     // compact records never exceed 2 n + n / 256 + 4 words (full-width ordinates, one explicit run), packed lines 2 n
@@ -417,7 +418,7 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
         if (c >= 1) CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * (c - 1) + 1], 0));  // pack_off still read by pack c-1
         cudaError_t e;
         if (compact) {
-            e = launch_compact_count(B, c0, cnt, (int32_t*)h->cmp_aux.p, (int32_t*)h->cmp_wsize.p, (unsigned*)h->cmp_codes.p,
+            e = launch_compact_count(B, c0, cnt, (int32_t*)h->cmp_aux.p, (int32_t*)h->cmp_yw.p, (int32_t*)h->cmp_wsize.p, (unsigned*)h->cmp_codes.p,
                                      pin_aux_dev, pin_aux_dev + cslots, h->s_pack);
             if (e != cudaSuccess) return cuda_fail(h, e, "compact count kernel");
             e = launch_chunk_offsets((const int32_t*)h->cmp_wsize.p, nsl, 0x7fffffff, (long long*)h->pack_off.p, pin_off_dev, h->s_pack);
@@ -441,7 +442,7 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
         double2* buf = (double2*)((c & 1) ? h->pack_xy2.p : h->pack_xy.p);
         if (c >= 2) CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * (c - 2) + 2], 0));  // buffer free again
         if (compact)
-            e = launch_compact_write(B, c0, cnt, (const int32_t*)h->cmp_aux.p, (const unsigned*)h->cmp_codes.p,
+            e = launch_compact_write(B, c0, cnt, (const int32_t*)h->cmp_aux.p, (const int32_t*)h->cmp_yw.p, (const unsigned*)h->cmp_codes.p,
                                      (const long long*)h->pack_off.p, (double*)buf, h->s_pack);
         else
             e = launch_pack_lines(B, c0, cnt, (const long long*)h->pack_off.p, buf, h->s_pack);
@@ -558,7 +559,7 @@ int dcegm_destroy(dcegm_handle h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     DevBuf* bufs[] = {&h->models, &h->grids, &h->off, &h->wgt, &h->lines, &h->lens, &h->vbound, &h->meta, &h->isects,
-                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2, &h->big_scratch, &h->cmp_aux, &h->cmp_wsize, &h->cmp_codes, &h->order,
+                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2, &h->big_scratch, &h->cmp_aux, &h->cmp_wsize, &h->cmp_codes, &h->cmp_yw, &h->order,
                       &h->simm, &h->yvec, &h->mom, &h->rhist, &h->sstat, &h->pan_d, &h->pan_i, &h->pan_ret,
                       &h->sh_w, &h->sh_d, &h->sh_r, &h->sh_w0, &h->sh_y0};
     for (DevBuf* b : bufs)
@@ -778,7 +779,8 @@ int dcegm_fetch_compact(dcegm_handle h, int first, int count, double* words, siz
     if ((rc = ensure(h, h->cmp_wsize, sizeof(int32_t) * nsl, false))) return rc;
     if ((rc = ensure(h, h->pack_off, sizeof(long long) * (nsl + 1), false))) return rc;
     if ((rc = ensure(h, h->cmp_codes, sizeof(unsigned) * nsl * l.cap, false))) return rc;
-    cudaError_t e = launch_compact_count(h->batch, first, count, (int32_t*)h->cmp_aux.p, (int32_t*)h->cmp_wsize.p,
+    if ((rc = ensure(h, h->cmp_yw, sizeof(int32_t) * nsl, false))) return rc;
+    cudaError_t e = launch_compact_count(h->batch, first, count, (int32_t*)h->cmp_aux.p, (int32_t*)h->cmp_yw.p, (int32_t*)h->cmp_wsize.p,
                                          (unsigned*)h->cmp_codes.p, nullptr, nullptr, h->stream);
     if (e != cudaSuccess) return cuda_fail(h, e, "compact count kernel");
     std::vector<int32_t> wsize(nsl);
@@ -795,7 +797,7 @@ int dcegm_fetch_compact(dcegm_handle h, int first, int count, double* words, siz
     if ((size_t)*nwords > cap_words) return fail(h, DCEGM_E_CAPACITY, "dcegm_fetch_compact: destination too small");
     if ((rc = ensure(h, h->pack_xy, sizeof(double) * (size_t)*nwords, false))) return rc;
     CK(cudaMemcpyAsync(h->pack_off.p, woffsets, sizeof(int64_t) * (nsl + 1), cudaMemcpyHostToDevice, h->stream));
-    e = launch_compact_write(h->batch, first, count, (const int32_t*)h->cmp_aux.p, (const unsigned*)h->cmp_codes.p,
+    e = launch_compact_write(h->batch, first, count, (const int32_t*)h->cmp_aux.p, (const int32_t*)h->cmp_yw.p, (const unsigned*)h->cmp_codes.p,
                              (const long long*)h->pack_off.p, (double*)h->pack_xy.p, h->stream);
     if (e != cudaSuccess) return cuda_fail(h, e, "compact write kernel");
     CK(cudaMemcpyAsync(words, h->pack_xy.p, sizeof(double) * (size_t)*nwords, cudaMemcpyDeviceToHost, h->stream));

@@ -260,9 +260,10 @@ int  dcegm_fetch_packed(dcegm_handle h, int first, int count, double* xy, size_t
  * arithmetic modulo 2^64, exactly invertible), byte-packed in blocks of 32.  Record of one line slot (slots in layout
  * order [model][it][iy][id][kind]; an empty slot has no record), in 8-byte words:
  *     head | ysec[yw] | run[nrun] | xs[nx]     head = yw; n = lens[slot], nrun = aux[slot] & 0xffff, nx = aux[slot] >> 16
- *     ysec = I_0 | I_1 - I_0 | width bytes w_b of the ceil((n-2)/32) blocks, zero-padded to 8 | payload, zero-padded to 8
- *       I_k = bit pattern of y_k; block b holds R_k = I_k - 2 I_(k-1) + I_(k-2), k = 2 + 32 b .., as little-endian
- *       two's-complement integers of w_b bytes each (w_b = 0: all zero, 8: raw); n = 1: I_0 only
+ *     ysec = I_0 | I_1 - I_0 | width bytes w_b of the ceil(n/32) blocks, zero-padded to 8 | payload, zero-padded to 8
+ *       I_k = bit pattern of y_k; block b holds R_k = I_k - 2 I_(k-1) + I_(k-2) for k = 32 b .. 32 b + 31 (R_0 = R_1 = 0
+ *       are place-holders) as little-endian two's-complement integers of w_b bytes each (w_b = 0: all zero, 8: raw);
+ *       n = 1: I_0 only
  *     run (64-bit integer) = pos | src << 16 | kind << 32; it covers points pos .. (next run's pos, or n) - 1:
  *       kind 0  x[pos + j] = a[src + j] + y[pos + j]     (a: the model's savings grid, dcegm_get_grid; one IEEE add)
  *       kind 1  x[pos + j] = x of point src + j of the POLICY line of the same (model, it, iy, id)   (value lines only)

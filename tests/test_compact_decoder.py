@@ -58,7 +58,7 @@ def test_run_kinds_and_rejection():
     rc, ac, rv, av = encode_reference(Lc, Lv, grid)
     assert (ac & 0xFFFF, ac >> 16) == (3, 1) and (av & 0xFFFF, av >> 16) == (3, 1)
     ywc, ywv = int(rc[:1].view(np.uint64)[0]), int(rv[:1].view(np.uint64)[0])  # head word: size of the ordinate section
-    assert ywc == 2 + 1 + 2 and ywv == 2 + 1 + 2  # I_0, I_1 - I_0, one word of width bytes, 2 residuals of 8 bytes
+    assert ywc == 2 + 1 + 4 and ywv == 2 + 1 + 4  # I_0, I_1 - I_0, one word of width bytes, one block of 4 x 8 bytes
     runs_c = rc[1 + ywc:1 + ywc + 3].view(np.uint64)
     assert [(int(v & 0xFFFF), int(v >> 16 & 0xFFFF), int(v >> 32)) for v in runs_c] == [(0, 0, KIND_GRID), (2, 0, KIND_EXPLICIT), (3, 3, KIND_GRID)]
     runs_v = rv[1 + ywv:1 + ywv + 3].view(np.uint64)
