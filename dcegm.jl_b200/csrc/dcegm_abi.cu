@@ -1,6 +1,7 @@
 // dcegm_abi.cu — the C ABI of libdcegm_cuda.so (include/dcegm.h): handle, device memory, streams,
 // uploads, kernel launches and result transfers.  No solver arithmetic lives here and there is no
 // CPU path: every solve runs the sm_100a kernels of solver_*.cu.
+#include <cuda.h>  // types of the stream memory operation fetched through cudaGetDriverEntryPoint (libcuda is not linked)
 #include <cuda_runtime.h>
 
 #include <sys/syscall.h>
@@ -60,6 +61,7 @@ struct dcegm_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t s_pack = nullptr, s_copy = nullptr;  // pipelined solve-to-host: packing and D2H streams
+    cudaStream_t s_pack_lo = nullptr, s_pack_hi = nullptr;  // ... the packing stream at default / highest priority
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     std::vector<cudaEvent_t> ev_pool;                 // per-chunk events of the pipelined solve
     long long* pin_off = nullptr;
@@ -67,6 +69,8 @@ struct dcegm_ctx {
     size_t pin_slots = 0;
     DevBuf cmp_aux, cmp_wsize, cmp_codes, cmp_yw;
     DevBuf order;         // launch order of whole-batch solves (costliest models first)
+    DevBuf chunk_done, model_chunk;  // one-launch pipelined solve: per-chunk completion counters, chunk of every model
+    int wait_value_state = 0;        // 0 untested, 1 cuStreamWaitValue32 works, -1 unavailable (chunked launches instead)
     // host tables of the last upload, page-locked in place (cudaHostRegister) so that their H2D copies run at full
     // PCIe rate instead of through the driver's staging buffer; re-registered only when a vector moved or grew
     struct Pinned { const void* p = nullptr; size_t bytes = 0; };
@@ -236,6 +240,8 @@ int upload(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels, unsi
     B.status = (int32_t*)h->status.p;
     B.summaries = (dcegm_summary*)h->summaries.p;
     B.order = nullptr;
+    B.chunk_done = nullptr;
+    B.model_chunk = nullptr;
     // Whole-batch solves start the costliest models first (longest-processing-time order): one CTA solves one model, and
     // the envelope makes small-lambda models several times dearer than smooth ones, so the last wave should be cheap ones.
     // The taste-shock scale is the predictor.  Chunked solves (dcegm_solve_*_packed/_compact) keep the batch order.
@@ -315,15 +321,31 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     const size_t nstates = (size_t)nmodels * l.nT * l.nstate;
     // chunks of whole waves (2 CTAs x 148 SMs): one wave first, so that the first transfer starts early, then
     // two waves each, at most 16 chunks
+    // ONE launch for the whole batch when the driver offers stream memory operations: finished models count up their
+    // chunk's counter and the packing stream (highest priority: its CTAs take the SM slots solver CTAs free) waits for
+    // the counter instead of for a per-chunk kernel — the GPU never drains at a chunk boundary, and chunks can be small.
+    // DCEGM_ONE_LAUNCH=0 keeps one launch per chunk (also the fine-grid solvers' way).
+    typedef CUresult (*wait_value_fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+    static wait_value_fn wait_value = [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &fn, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) fn = nullptr;
+        cudaGetLastError();
+        return (wait_value_fn)fn;
+    }();
+    const char* ol = getenv("DCEGM_ONE_LAUNCH");
+    const bool want_one = !h->big && (model == DCEGM_MODEL_F || model == DCEGM_MODEL_G) && wait_value && h->wait_value_state >= 0 &&
+                          !(ol && atoi(ol) == 0) && nmodels > 296;
     const int wave = 296;
     std::vector<int> cstart, ccount;
     {
-        int per_chunk = 2 * wave;
-        while ((nmodels - wave + per_chunk - 1) / per_chunk + 2 > 16) per_chunk += wave;
+        int per_chunk = want_one ? wave : 2 * wave;
+        while ((nmodels - wave + per_chunk - 1) / per_chunk + 2 > (want_one ? 32 : 16)) per_chunk += wave;
         int c0 = 0;
         while (c0 < nmodels) {
             // half a wave first (one CTA per SM: the shortest time to the first transfer), then one wave, then per_chunk
             int cnt = nmodels > 2 * wave ? (cstart.empty() ? wave / 2 : cstart.size() == 1 ? wave : per_chunk) : per_chunk;
+            if (want_one && nmodels - c0 <= per_chunk + wave / 2 && nmodels - c0 > wave / 2) cnt = nmodels - c0 - wave / 2;  // short last chunk
             if (h->big) cnt = 148 * ((nmodels + 148 * 16 - 1) / (148 * 16));  // fine-grid solver: one envelope CTA per SM
             cnt = cnt < nmodels - c0 ? cnt : nmodels - c0;
             cstart.push_back(c0);
@@ -334,14 +356,21 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     const int nchunks = (int)cstart.size();
     int chunk = 0;
     for (int c : ccount) chunk = c > chunk ? c : chunk;
-    if (!h->s_pack) {
-        // DCEGM_PACK_PRIO=1 runs the packing kernels at the highest stream priority (measured slower: they take SM slots
-        // from the solver, which then feeds the copy engine late — profiles/r2_e2e_pipeline.md)
+    if (!h->s_pack_lo) {
         int prio_lo = 0, prio_hi = 0;
         CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
-        const char* pp = getenv("DCEGM_PACK_PRIO");
-        CK(cudaStreamCreateWithPriority(&h->s_pack, cudaStreamNonBlocking, pp && atoi(pp) ? prio_hi : prio_lo));
+        CK(cudaStreamCreateWithPriority(&h->s_pack_lo, cudaStreamNonBlocking, prio_lo));
+        CK(cudaStreamCreateWithPriority(&h->s_pack_hi, cudaStreamNonBlocking, prio_hi));
         CK(cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking));
+    }
+    {
+        // Priority of the packing kernels.  One launch: highest, or they would wait for the solver grid's last pending
+        // CTA (measured: first chunk encoded at 18.8 ms instead of 5.3 ms).  One launch per chunk: default — at the
+        // highest priority they take SM slots from the solver, which then feeds the copy engine late (133.7 k vs
+        // 116.4 k models/s end to end).  DCEGM_PACK_PRIO=0/1 overrides.
+        const char* pp = getenv("DCEGM_PACK_PRIO");
+        const bool hi = pp ? atoi(pp) != 0 : want_one;
+        h->s_pack = hi ? h->s_pack_hi : h->s_pack_lo;
     }
     while (h->ev_pool.size() < (size_t)3 * nchunks) {
         cudaEvent_t e;
@@ -400,11 +429,39 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
         Bc.order = (const int32_t*)h->order.p;
         h->batch.order = Bc.order;  // still a permutation of the batch: later whole-batch runs may use it
     }
-    for (int c = 0; c < nchunks; c++) {
-        cudaError_t e = launch_range(h, Bc, cstart[c], ccount[c], h->stream);
+    // ONE launch for the whole batch when the driver offers stream memory operations: finished models count up their
+    // chunk's counter and the packing stream waits for the counter instead of for a per-chunk kernel — no drain of the
+    // GPU at every chunk boundary.  DCEGM_ONE_LAUNCH=0 keeps one launch per chunk.
+    bool one_launch = want_one && Bc.order != nullptr;
+    if (one_launch) {
+        std::vector<uint16_t> mc(nmodels);
+        for (int c = 0; c < nchunks; c++)
+            for (int i = 0; i < ccount[c]; i++) mc[cstart[c] + i] = (uint16_t)c;  // chunks are model ranges
+        if ((rc = ensure(h, h->model_chunk, sizeof(uint16_t) * nmodels, false))) return rc;
+        if ((rc = ensure(h, h->chunk_done, sizeof(int32_t) * nchunks, false))) return rc;
+        CK(cudaMemcpyAsync(h->model_chunk.p, mc.data(), sizeof(uint16_t) * nmodels, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemsetAsync(h->chunk_done.p, 0, sizeof(int32_t) * nchunks, h->stream));
+        CK(cudaStreamSynchronize(h->stream));  // mc goes out of scope; the counters are zero before anybody waits
+        if (h->wait_value_state == 0) {  // first use: does the wait work on this device / driver?
+            const CUresult r = wait_value((CUstream)h->s_pack, (CUdeviceptr)h->chunk_done.p, 0u, CU_STREAM_WAIT_VALUE_GEQ);
+            h->wait_value_state = (r == CUDA_SUCCESS && cudaStreamSynchronize(h->s_pack) == cudaSuccess) ? 1 : -1;
+            cudaGetLastError();
+            one_launch = h->wait_value_state == 1;
+        }
+    }
+    if (one_launch) {
+        Bc.chunk_done = (int32_t*)h->chunk_done.p;
+        Bc.model_chunk = (const uint16_t*)h->model_chunk.p;
+        cudaError_t e = launch_range(h, Bc, 0, nmodels, h->stream);
         if (e != cudaSuccess) return cuda_fail(h, e, "kernel launch");
         launches += h->launches_last;
-        CK(cudaEventRecord(h->ev_pool[3 * c], h->stream));
+    } else {
+        for (int c = 0; c < nchunks; c++) {
+            cudaError_t e = launch_range(h, Bc, cstart[c], ccount[c], h->stream);
+            if (e != cudaSuccess) return cuda_fail(h, e, "kernel launch");
+            launches += h->launches_last;
+            CK(cudaEventRecord(h->ev_pool[3 * c], h->stream));
+        }
     }
     CK(cudaEventRecord(h->ev[3], h->stream));
 
@@ -414,7 +471,12 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
     for (int c = 0; c < nchunks && err == DCEGM_OK; c++) {
         const int c0 = cstart[c], cnt = ccount[c];
         const size_t nsl = per * cnt;
-        CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * c], 0));
+        if (one_launch) {
+            if (wait_value((CUstream)h->s_pack, (CUdeviceptr)((int32_t*)h->chunk_done.p + c), (cuuint32_t)cnt, CU_STREAM_WAIT_VALUE_GEQ) != CUDA_SUCCESS)
+                return fail(h, DCEGM_E_CUDA, "cuStreamWaitValue32 failed");
+        } else {
+            CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * c], 0));
+        }
         if (c >= 1) CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * (c - 1) + 1], 0));  // pack_off still read by pack c-1
         cudaError_t e;
         if (compact) {
@@ -559,7 +621,7 @@ int dcegm_destroy(dcegm_handle h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     DevBuf* bufs[] = {&h->models, &h->grids, &h->off, &h->wgt, &h->lines, &h->lens, &h->vbound, &h->meta, &h->isects,
-                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2, &h->big_scratch, &h->cmp_aux, &h->cmp_wsize, &h->cmp_codes, &h->cmp_yw, &h->order,
+                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2, &h->big_scratch, &h->cmp_aux, &h->cmp_wsize, &h->cmp_codes, &h->cmp_yw, &h->chunk_done, &h->model_chunk, &h->order,
                       &h->simm, &h->yvec, &h->mom, &h->rhist, &h->sstat, &h->pan_d, &h->pan_i, &h->pan_ret,
                       &h->sh_w, &h->sh_d, &h->sh_r, &h->sh_w0, &h->sh_y0};
     for (DevBuf* b : bufs)
@@ -571,7 +633,8 @@ int dcegm_destroy(dcegm_handle h) {
     if (h->pin_aux) cudaFreeHost(h->pin_aux);
     for (auto& r : h->pin_tab)
         if (r.p) cudaHostUnregister(const_cast<void*>(r.p));
-    if (h->s_pack) cudaStreamDestroy(h->s_pack);
+    if (h->s_pack_lo) cudaStreamDestroy(h->s_pack_lo);
+    if (h->s_pack_hi) cudaStreamDestroy(h->s_pack_hi);
     if (h->s_copy) cudaStreamDestroy(h->s_copy);
     cudaStreamDestroy(h->stream);
     delete h;

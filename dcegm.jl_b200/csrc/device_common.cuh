@@ -65,6 +65,10 @@ struct DeviceBatch {
     dcegm_summary* summaries;  // [nmodels]
     int first;               // first model of this launch (grid = number of models of the launch)
     const int32_t* order;    // launch order of a whole-batch solve: CTA b solves model order[b] (null: model first + b)
+    // pipelined solve-to-host in ONE launch: a finished model adds 1 to chunk_done[model_chunk[m]] (after a fence), the
+    // packing stream waits for a chunk's counter to reach the chunk's size (stream memory operation); null otherwise
+    int32_t* chunk_done;
+    const uint16_t* model_chunk;
 };
 
 // inputs / outputs of the forward simulator (solver_sim.cu)
@@ -330,6 +334,16 @@ __device__ __forceinline__ int count_le_indexed_at(const unsigned short* __restr
 }
 __device__ __forceinline__ int count_le_indexed(const KnotIndex& K, const double* __restrict__ x, int n, double q) {
     return count_le_indexed_at(reinterpret_cast<const unsigned short*>(dc_smem + K.tab), K, x, n, q);
+}
+
+// last statement of a per-model solver kernel: publish "this model's lines are in HBM" to the packing stream
+__device__ __forceinline__ void signal_model_done(const DeviceBatch& B, int m) {
+    if (!B.chunk_done) return;
+    __syncthreads();  // every thread's stores of this model are issued
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(&B.chunk_done[B.model_chunk[m]], 1);
+    }
 }
 
 // status bit of a knot pair x0, x1 (consecutive abscissae of a stored line) the previous period's interpolate()

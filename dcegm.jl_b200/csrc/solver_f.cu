@@ -337,6 +337,7 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_f_kernel(DeviceBat
         B.summaries[m] = sm;
         B.status[m] = s_status;
     }
+    signal_model_done(B, m);
 #ifdef DCEGM_PHASE_CLOCKS
     DC_CLK(14);
     if (tid == 0)

@@ -328,6 +328,7 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBat
         B.summaries[m] = sm;
         B.status[m] = s_status;
     }
+    signal_model_done(B, m);
 }
 
 cudaError_t launch_solve_g(const DeviceBatch& B0, int first, int count, cudaStream_t stream) {
