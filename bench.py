@@ -336,6 +336,7 @@ def main():
 
     e2e_xy_value, d2h_xy, _ = timed_e2e(e2e_xy_step, min(args.steps, 3))
     e2e_value, d2h, d2h_gbs = timed_e2e(e2e_step, args.steps)
+    e2e_launches = int(solver.timing().n_launches)  # kernels of one end-to-end step: solver + encoder passes per chunk
     clocks = sampler.stop() if rank == 0 else None  # sampled over both timed regions (device-resident and e2e)
     gbs_all = None
     if dist:  # per-rank device-to-host rates (the host side limits e2e on a multi-GPU box)
@@ -409,7 +410,7 @@ def main():
                               "source": "achieved = FP64-pipe warp instructions per model (sm__inst_executed_pipe_fp64.sum; " + ctr_src +
                                         ") x models / kernel time; peak = dcegm_debug_dfma_rate measured in this run"},
             "e2e": {"value": e2e_value, "unit": "models/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "d2h_gbs": d2h_gbs, "d2h_gbs_per_rank": gbs_all,
+                    "d2h_gbs": d2h_gbs, "d2h_gbs_per_rank": gbs_all, "gpu_launches_per_step": e2e_launches,
                     "format": "compact lines (include/dcegm.h): ordinates + abscissa runs, lossless; expanded lazily per line by the host mirror",
                     "expand_all_on_host": expand,
                     "full_xy": {"value": e2e_xy_value, "unit": "models/s", "d2h_bytes_per_step": int(d2h_xy),
