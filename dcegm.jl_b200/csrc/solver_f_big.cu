@@ -8,9 +8,12 @@
 //                        code solve_f_kernel runs) reading the next-period lines of the model from its
 //                        region of global memory (L2-resident: 4 lines x 16 B x na per model)
 //   big_env_kernel       one CTA per model: secondary upper envelope + policy repair (envelope.cuh,
-//                        instantiated on global-memory scratch), credit-constraint point, checks, the one
-//                        store of the finished lines, and the knot index of the new lines
-// Two launches per period; every period's lines are written to the solution buffers once, the working
+//                        instantiated on global-memory scratch), credit-constraint point
+//   big_post_kernel      CTA per (model, 256-point / 256-bucket tile): everything of the period's tail that is per-point
+//                        work — the one store of the finished lines, the retiree line's checks, and the knot index of
+//                        the new lines (one binary search per bucket) — which took a third of big_env_kernel's time
+//                        when its single CTA per model did it (profiles/r1g_big_env_by_source_line.txt)
+// Three launches per period; every period's lines are written to the solution buffers once, the working
 // copies (SoA, two period sets) live in a per-model scratch region.
 #include <math_constants.h>
 
@@ -36,8 +39,9 @@ struct BigState {
     int n_wc[2], n_wv[2], n_r[2];  // by line set
     double vb_w[2], vb_r[2];
     KnotIndex Kr, Kc, Kv;           // index over the lines of the set built last
-    int idx_ok;                     // the three tables are valid
+    int idx_ok;                     // the three tables were built (lines of at least two points)
     int status;
+    int now;                        // status bits raised by the lines of the period built last
     double ev0[2];
     int sum_envp, sum_seg, sum_is, sum_rm, sum_maxlen;
     long long sum_pts;
@@ -227,6 +231,7 @@ __global__ void __launch_bounds__(kThreads) big_terminal_kernel(DeviceBatch B, u
         st->n_wc[w] = 2; st->n_wv[w] = nv; st->n_r[w] = 2;
         st->vb_w[w] = 0.0; st->vb_r[w] = 0.0;
         st->status = 0;
+        st->now = 0;
         st->ev0[0] = st->ev0[1] = 0.0;
         st->sum_envp = st->sum_seg = st->sum_is = st->sum_rm = st->sum_maxlen = 0;
         st->sum_pts = 4 + 2 * nv;
@@ -274,7 +279,8 @@ __global__ void __launch_bounds__(kThreads, DCEGM_BIG_EGM_MINBLOCKS) big_egm_ker
     const bool next_terminal = (t + 1 == nT - 1);
     const bool beq = (t == nT - 2) && p.nu > 0;
     const double scale = beq ? p.betaRnu : p.betaR;
-    bool fast = model_fast && !beq && st->idx_ok;
+    // the bucket index (and with it the straight-line node) needs the next-period lines strictly increasing and finite
+    bool fast = model_fast && !beq && st->idx_ok && !(st->now & kStatusNoIndex);
     const KnotIndex Kr = st->Kr, Kc = st->Kc, Kv = st->Kv;
     const unsigned short* __restrict__ Tr = P.tab(g, 0);
     const unsigned short* __restrict__ Tc = P.tab(g, 1);
@@ -350,15 +356,12 @@ __global__ void __launch_bounds__(kEnvThreads) big_env_kernel(DeviceBatch B, uns
     BIG_CLK_BEGIN();
     __shared__ DevModel s_p;
     __shared__ int s_n[2];
-    __shared__ int s_status, s_now;  // status word of the model so far; bits raised by this period's lines
+    __shared__ int s_status;  // status word of the model so far
     if (tid == 0) s_p = B.models[m];
     const BigPlan P(B.lay.cap, B.lay.isec_cap);
     unsigned char* g = scratch + (size_t)blockIdx.x * stride;
     BigState* st = P.state(g);
-    if (tid == 0) {
-        s_status = st->status;
-        s_now = 0;
-    }
+    if (tid == 0) s_status = st->status;
     __syncthreads();
     const DevModel& p = s_p;
     const int na = p.na;
@@ -394,66 +397,131 @@ __global__ void __launch_bounds__(kEnvThreads) big_env_kernel(DeviceBatch B, uns
     C.vb_w = ev0w;
     DC_CLK(12);
 
-    // retiree: credit-constraint point and checks (dc_algo.jl:90-101)
+    // retiree: credit-constraint point (dc_algo.jl:90-101); its checks, all stores and the knot index are
+    // big_post_kernel's (per-point work, spread over the GPU)
+    __syncthreads();
     if (tid == 0) {
         C.r_x()[0] = a0;
         C.rc_y()[0] = 0.0;
         C.rv_y()[0] = ev0r;
-    }
-    C.n_r = na + 1;
-    C.vb_r = ev0r;
-    __syncthreads();
-    int flag = 0;
-    for (int k = tid; k < na + 1; k += kEnvThreads) {
-        if (k + 1 < na + 1) flag |= knot_pair_flag(C.r_x()[k], C.r_x()[k + 1], first_period);
-        if (!isfinite(C.r_x()[k]) || !isfinite(C.rc_y()[k]) || !isfinite(C.rv_y()[k])) flag |= DCEGM_ST_NONFINITE;
-    }
-    if (flag) {
-        atomicOr(&s_status, flag);
-        atomicOr(&s_now, flag);
-    }
-    if (tid == 0 && S.cnt()[2]) {
-        atomicOr(&s_status, S.cnt()[2]);
-        atomicOr(&s_now, S.cnt()[2]);
-    }
-
-    store_line<kEnvThreads>(B, m, t, 0, 0, DCEGM_KIND_C, C.wc_x(), C.wc_y(), C.n_wc);
-    store_line<kEnvThreads>(B, m, t, 0, 0, DCEGM_KIND_V, C.wv_x(), C.wv_y(), C.n_wv);
-    store_line<kEnvThreads>(B, m, t, 0, 1, DCEGM_KIND_C, C.r_x(), C.rc_y(), C.n_r);
-    store_line<kEnvThreads>(B, m, t, 0, 1, DCEGM_KIND_V, C.r_x(), C.rv_y(), C.n_r);
-    __syncthreads();
-    const int status = s_status;
-    if (tid == 0) {
+        const int wf = S.cnt()[2];  // bits raised by the worker's envelope
         B.vbound[ss * 2 + 0] = ev0w;
         B.vbound[ss * 2 + 1] = ev0r;
         const dcegm_env_meta mt = B.meta[ss];
+        const int n_r = na + 1;
         st->sum_envp += mt.n_removed > 0;
         st->sum_seg += mt.n_segments;
         st->sum_is += mt.n_isects;
         st->sum_rm += mt.n_removed;
         int ml = C.n_wc > C.n_wv ? C.n_wc : C.n_wv;
-        ml = ml > C.n_r ? ml : C.n_r;
+        ml = ml > n_r ? ml : n_r;
         st->sum_maxlen = st->sum_maxlen > ml ? st->sum_maxlen : ml;
-        st->sum_pts += C.n_wc + C.n_wv + 2 * C.n_r;
+        st->sum_pts += C.n_wc + C.n_wv + 2 * n_r;
         st->n_wc[w] = C.n_wc;
         st->n_wv[w] = C.n_wv;
-        st->n_r[w] = C.n_r;
+        st->n_r[w] = n_r;
         st->vb_w[w] = C.vb_w;
-        st->vb_r[w] = C.vb_r;
-        st->status = status;
+        st->vb_r[w] = ev0r;
+        st->now = wf;
+        st->status = s_status | wf;
     }
-    DC_CLK(13);
-    if (t > 0) {
-        // The bucket index (and with it the straight-line EGM node) needs THIS period's lines strictly increasing and
-        // finite; a model flagged in an earlier period uses it again as soon as its lines are regular (both node
-        // paths give the same bits on regular lines).
-        big_build_index<kEnvThreads>(P, g, st, C, s_now);
-        BIG_CLK_END();
-        return;
-    }
-
-    big_summary(B, m, p, C, st, status);
     BIG_CLK_END();
+}
+
+// ---- the per-point tail of period t: stores, retiree checks, knot index -------------------------------------------
+__global__ void __launch_bounds__(kThreads) big_post_kernel(DeviceBatch B, unsigned char* scratch, size_t stride, int t) {
+    const int lm = blockIdx.y;
+    const int m = B.first + lm;
+    const int tid = threadIdx.x;
+    const BigPlan P(B.lay.cap, B.lay.isec_cap);
+    unsigned char* g = scratch + (size_t)lm * stride;
+    BigState* st = P.state(g);
+    const int w = t & 1;
+    const LineSetG C = big_set(P, g, st, w);
+    const int n_wc = C.n_wc, n_wv = C.n_wv, n_r = C.n_r;
+    const bool first_period = t == 0;
+    const int k = blockIdx.x * kThreads + tid;
+    // ---- the one store of the finished lines (interleaved x, y) ----
+    {
+        const size_t s0 = line_slot(B.lay, m, t, 0, 0, 0);  // slots: worker c, worker v, retiree c, retiree v
+        if (k == 0) {
+            B.lens[s0 + 0] = n_wc;
+            B.lens[s0 + 1] = n_wv;
+            B.lens[s0 + 2] = n_r;
+            B.lens[s0 + 3] = n_r;
+        }
+        if (B.lines) {
+            const int cap = B.lay.cap;
+            double2* d = B.lines + s0 * (size_t)cap;
+            if (k < n_wc && k < cap) d[k] = make_double2(C.wc_x()[k], C.wc_y()[k]);
+            if (k < n_wv && k < cap) d[(size_t)cap + k] = make_double2(C.wv_x()[k], C.wv_y()[k]);
+            if (k < n_r && k < cap) {
+                const double x = C.r_x()[k];
+                d[(size_t)2 * cap + k] = make_double2(x, C.rc_y()[k]);
+                d[(size_t)3 * cap + k] = make_double2(x, C.rv_y()[k]);
+            }
+        }
+    }
+    // ---- retiree line: strictly increasing, finite ----
+    {
+        int flag = 0;
+        if (k < n_r) {
+            if (k + 1 < n_r) flag |= knot_pair_flag(C.r_x()[k], C.r_x()[k + 1], first_period);
+            if (!isfinite(C.r_x()[k]) || !isfinite(C.rc_y()[k]) || !isfinite(C.rv_y()[k])) flag |= DCEGM_ST_NONFINITE;
+        }
+        flag = __reduce_or_sync(0xffffffffu, flag);
+        if (flag && (tid & 31) == 0) {
+            atomicOr(&st->status, flag);
+            atomicOr(&st->now, flag);
+        }
+    }
+    if (first_period) return;  // period 1 is read by nobody: no index
+    // ---- knot index of the three knot vectors: entry b = first knot whose bucket is >= b, one search per entry ----
+    const bool ok = n_wc >= 2 && n_wv >= 2 && n_r >= 2;
+    const int nb = P.nbuck;
+    KnotIndex K[3];
+    const double* X[3] = {C.r_x(), C.wc_x(), C.wv_x()};
+    const int N[3] = {n_r, n_wc, n_wv};
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+        K[j].tab = 0;
+        K[j].lo = K[j].inv = 0.0;
+        K[j].topi = 0;
+        if (ok) knot_index_range(K[j], X[j], N[j], nb);
+    }
+    if (k == 0) {
+        st->Kr = K[0];
+        st->Kc = K[1];
+        st->Kv = K[2];
+        st->idx_ok = ok ? 1 : 0;
+    }
+    if (ok && k <= nb) {
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            int lo = 0, hi = N[j];  // knot_bucket is non-decreasing along an increasing knot vector
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (knot_bucket(K[j], X[j][mid]) >= k)
+                    hi = mid;
+                else
+                    lo = mid + 1;
+            }
+            P.tab(g, j)[k] = (unsigned short)lo;
+        }
+    }
+}
+
+// ---- per-model summary after the first period --------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) big_summary_kernel(DeviceBatch B, unsigned char* scratch, size_t stride) {
+    const int m = B.first + blockIdx.x;
+    __shared__ DevModel s_p;
+    if (threadIdx.x == 0) s_p = B.models[m];
+    __syncthreads();
+    const BigPlan P(B.lay.cap, B.lay.isec_cap);
+    unsigned char* g = scratch + (size_t)blockIdx.x * stride;
+    BigState* st = P.state(g);
+    const LineSetG C = big_set(P, g, st, 0);  // period 1 (t = 0) lives in set 0
+    big_summary(B, m, s_p, C, st, st->status);
 }
 
 // Launches the whole backward recursion for models [first, first+count).  `scratch` holds `count` regions of
@@ -467,6 +535,7 @@ cudaError_t launch_solve_f_big(const DeviceBatch& B0, int first, int count, unsi
     constexpr int kMaxParts = 8;
     const size_t stride = BigPlan(B0.lay.cap, B0.lay.isec_cap).bytes;
     const int nT = B0.lay.nT, na = B0.lay.na;
+    const int nbuck_plus1 = BigPlan(B0.lay.cap, B0.lay.isec_cap).nbuck + 1;
     static const int parts_wanted = [] {
         const char* e = getenv("DCEGM_BIG_PARTS");  // 1 = one stream
         const int v = e ? atoi(e) : 4;
@@ -504,8 +573,14 @@ cudaError_t launch_solve_f_big(const DeviceBatch& B0, int first, int count, unsi
             unsigned char* scr = scratch + (size_t)beg[h] * stride;
             big_egm_kernel<<<ggrid, kThreads, 0, st[h]>>>(Bh[h], scr, stride, t);
             big_env_kernel<<<cnt[h], kEnvThreads, 0, st[h]>>>(Bh[h], scr, stride, t);
-            nl += 2;
+            const int ptiles = (B0.lay.cap > nbuck_plus1 ? B0.lay.cap : nbuck_plus1);
+            big_post_kernel<<<dim3((ptiles + kThreads - 1) / kThreads, cnt[h]), kThreads, 0, st[h]>>>(Bh[h], scr, stride, t);
+            nl += 3;
         }
+    }
+    for (int h = 0; h < np; h++) {
+        big_summary_kernel<<<cnt[h], kThreads, 0, st[h]>>>(Bh[h], scratch + (size_t)beg[h] * stride, stride);
+        nl++;
     }
     if (np > 1) {
         for (int h = 1; h < np; h++) {
