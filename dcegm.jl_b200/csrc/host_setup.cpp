@@ -284,17 +284,19 @@ bool build_tables(int model, const dcegm_param* params, int nmodels, HostTables&
 
     const size_t off_per = minimal ? (size_t)ny : (size_t)(nT - 1) * 2 * ny;
     const size_t wgt_per = model == DCEGM_MODEL_G ? (size_t)ny * ny : (size_t)ny;
-    out.sim.assign(nmodels, SimModel{});
-    out.yvec.assign((size_t)ny * nmodels, 0.0);
-    out.off.assign(off_per * nmodels, 0.0);
-    out.wgt.assign(wgt_per * nmodels, 0.0);
+    // every element below is written by one(m): no zero fill (7.9 MB of offsets at 4096 C3 models)
+    out.sim.resize(nmodels);
+    out.yvec.resize((size_t)ny * nmodels);
+    out.off.resize(off_per * nmodels);
+    out.wgt.resize(wgt_per * nmodels);
 
     auto one = [&](int m) {
         const dcegm_param& p = params[m];
         double* off = out.off.data() + off_per * m;
         double* wgt = out.wgt.data() + wgt_per * m;
-        std::vector<double> yvec(ny);
+        double* yvec = out.yvec.data() + (size_t)ny * m;
         SimModel& sm = out.sim[m];
+        sm = SimModel{};
         sm.inc0 = p.inc0;
         sm.inc1 = p.inc1;
         sm.inc2 = p.inc2;
@@ -321,8 +323,9 @@ bool build_tables(int model, const dcegm_param* params, int nmodels, HostTables&
                 for (int iy = 0; iy < ny; iy++)
                     for (int jy = 0; jy < ny; jy++) wgt[(size_t)iy * ny + jy] = ghw[jy] * inv_sqrt_pi;
             } else {  // param.jl:284
-                std::vector<double> P;
-                rouwenhorst(p.rho, 0.0, p.sigma, ny, yvec, P);
+                std::vector<double> z, P;
+                rouwenhorst(p.rho, 0.0, p.sigma, ny, z, P);
+                std::copy(z.begin(), z.end(), yvec);
                 std::copy(P.begin(), P.end(), wgt);
             }
             for (int it = 1; it <= nT - 1; it++)  // m1[it+1][iid][jy,:]  param.jl:301
@@ -337,7 +340,6 @@ bool build_tables(int model, const dcegm_param* params, int nmodels, HostTables&
                 off[i] = 0.0 + std::exp(yvec[i]);             // minimal_EGM.jl:21
             }
         }
-        std::copy(yvec.begin(), yvec.end(), out.yvec.begin() + (size_t)ny * m);
     };
     unsigned hw = std::thread::hardware_concurrency();
     int nt = (int)std::min<unsigned>(hw ? hw : 1, 16);
