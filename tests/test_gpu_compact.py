@@ -75,3 +75,20 @@ def test_fine_grid_and_general_model():
         # bequest variant: terminal lines on the full grid
         s.solve(_abi.MODEL_G, [Param(par=dict(na=100, nu=2.0))], fetch=False)
         check(s, s.fetch_compact(), 0.55)
+
+
+def test_minimal_models_and_small_batches():
+    """slots without a value line (minimal EGM stores (m, c) only), batches below one chunk, a batch of one"""
+    from dcegm_jl_b200 import Param, _abi
+    from dcegm_jl_b200.solver import Solver
+
+    with Solver(0) as s:
+        s.solve(_abi.MODEL_MINIMAL, [Param(par=dict(beta=b)) for b in (0.9, 0.95, 0.99)], fetch=False)
+        check(s, s.fetch_compact(), 0.80)  # 101-point lines: the per-slot words weigh more
+        cl = s.solve_compact(_abi.MODEL_F, c3_draws(1, na=60))
+        check(s, cl, 0.60)
+        cl = s.solve_compact(_abi.MODEL_F, c3_draws(300, na=60), keep_dirty=True)  # 300 models: two chunks, one launch
+        check(s, cl, 0.60)
+        with pytest.raises(Exception):
+            s.solve(_abi.MODEL_F, c3_draws(2, na=60), summary_only=True)
+            s.fetch_compact()

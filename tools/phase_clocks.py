@@ -10,7 +10,7 @@ sys.path.insert(0, ROOT)
 from dcegm_jl_b200 import _lib  # noqa: E402
 
 _lib.LIB_PATH = os.path.join(ROOT, "dcegm.jl_b200", "csrc", "libdcegm_cuda_prof.so")
-from bench import c3_params  # noqa: E402
+from bench_configs import c3_params  # noqa: E402
 from dcegm_jl_b200 import _abi  # noqa: E402
 from dcegm_jl_b200.solver import Solver  # noqa: E402
 
