@@ -22,7 +22,7 @@ EXPORTS = [
     "dcegm_simulate", "dcegm_fetch_sim_moments", "dcegm_fetch_sim_panel", "dcegm_sim_moments_to_device", "dcegm_solve_minimal_borrow", "dcegm_solve_minimal_bequest",
     "dcegm_sweep_record_bytes", "dcegm_sweep_records_to_device",
     "dcegm_solve_f_compact", "dcegm_solve_g_compact", "dcegm_fetch_compact", "dcegm_expand_compact",
-    "dcegm_decode_compact_pair", "dcegm_get_grid", "dcegm_debug_host_table",
+    "dcegm_decode_compact_pair", "dcegm_get_grid", "dcegm_debug_host_table", "dcegm_debug_check_guards",
 ]
 
 
@@ -65,6 +65,7 @@ def load():
     lib.dcegm_expand_compact.argtypes = [H, C.c_int, C.c_int, dp, lp, ip, ip, dp, C.c_size_t, lp, lp, C.c_int]
     lib.dcegm_decode_compact_pair.argtypes = [dp, C.c_int, dp, C.c_int, C.c_int, dp, C.c_int, C.c_int, dp, dp]
     lib.dcegm_get_grid.argtypes = [H, C.c_int, dp, C.c_int, C.POINTER(C.c_int)]
+    lib.dcegm_debug_check_guards.argtypes = [H, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.dcegm_debug_host_table.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, dp, dp]
     lib.dcegm_simulate.argtypes = [H, C.c_uint, C.POINTER(_abi.dcegm_sim_shocks)]
     lib.dcegm_fetch_sim_moments.argtypes = [H, C.c_int, C.c_int, dp, ip, ip]

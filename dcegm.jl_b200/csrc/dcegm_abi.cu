@@ -109,14 +109,19 @@ int cuda_fail(dcegm_ctx* h, cudaError_t e, const char* what) {
         if (e_ != cudaSuccess) return cuda_fail(h, e_, #call);  \
     } while (0)
 
+// Every device buffer ends in a guard band of kGuardBytes filled with 0xA5 when it is allocated: a kernel that writes
+// past the end of a buffer changes it, and dcegm_debug_check_guards() finds out (compute-sanitizer is not available on
+// this GPU pool; tests/test_gpu_guards.py runs every solver and checks the bands).
+constexpr size_t kGuardBytes = 4096;
 int ensure(dcegm_ctx* h, DevBuf& b, size_t bytes, bool zero_new) {
     if (bytes <= b.cap) return DCEGM_OK;
     if (b.p) CK(cudaFree(b.p));
     b.p = nullptr;
     b.cap = 0;
-    CK(cudaMalloc(&b.p, bytes));
+    CK(cudaMalloc(&b.p, bytes + kGuardBytes));
     b.cap = bytes;
     if (zero_new) CK(cudaMemsetAsync(b.p, 0, bytes, h->stream));
+    CK(cudaMemsetAsync((char*)b.p + bytes, 0xA5, kGuardBytes, h->stream));
     return DCEGM_OK;
 }
 
@@ -897,6 +902,31 @@ int dcegm_get_grid(dcegm_handle h, int model, double* grid, int cap, int* na) {
     if (!grid) return DCEGM_OK;
     if (cap < p.na) return fail(h, DCEGM_E_CAPACITY, "dcegm_get_grid: destination too small");
     memcpy(grid, h->tab.grids.data() + (size_t)p.grid * p.na, sizeof(double) * p.na);
+    return DCEGM_OK;
+}
+
+// ---- diagnostics: guard bands behind every device buffer of the handle -----------------------------------------
+int dcegm_debug_check_guards(dcegm_handle h, int* nbuffers, int* nbad) {
+    if (!h || !nbuffers || !nbad) return DCEGM_E_INVALID;
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    DevBuf* bufs[] = {&h->models, &h->grids, &h->off, &h->wgt, &h->lines, &h->lens, &h->vbound, &h->meta, &h->isects,
+                      &h->removed, &h->dirty, &h->status, &h->summaries, &h->pack_off, &h->pack_xy, &h->pack_xy2, &h->big_scratch,
+                      &h->cmp_aux, &h->cmp_wsize, &h->cmp_codes, &h->cmp_yw, &h->chunk_done, &h->model_chunk, &h->order,
+                      &h->simm, &h->yvec, &h->mom, &h->rhist, &h->sstat, &h->pan_d, &h->pan_i, &h->pan_ret,
+                      &h->sh_w, &h->sh_d, &h->sh_r, &h->sh_w0, &h->sh_y0};
+    std::vector<unsigned char> g(kGuardBytes);
+    *nbuffers = *nbad = 0;
+    for (DevBuf* b : bufs) {
+        if (!b->p) continue;
+        ++*nbuffers;
+        CK(cudaMemcpy(g.data(), (const char*)b->p + b->cap, kGuardBytes, cudaMemcpyDeviceToHost));
+        for (unsigned char c : g)
+            if (c != 0xA5) {
+                ++*nbad;
+                break;
+            }
+    }
     return DCEGM_OK;
 }
 

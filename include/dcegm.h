@@ -372,6 +372,10 @@ int  dcegm_fetch_sim_panel(dcegm_handle h, int model, double* w0, double* w1, do
 int  dcegm_debug_math_check(unsigned long long n, unsigned long long seed, int emin, int emax,
                             unsigned long long* mismatches2);
 
+/* Every device buffer of a handle ends in a 4 KB guard band written at allocation; *nbad counts the buffers whose band
+ * was overwritten since (a kernel wrote past the end of the buffer), *nbuffers the buffers checked. */
+int  dcegm_debug_check_guards(dcegm_handle h, int* nbuffers, int* nbad);
+
 /* The host-side model constructors of the library (csrc/host_setup.cpp), callable without a device, so that the
  * tables the kernels receive can be checked against independent implementations (tests/test_host_setup_tables.py):
  * which = 0 range(p0, stop=p1, length=n) -> out0[n] (param.jl:199);  1 quadpoints(n,0,1) -> nodes out0[n], weights
