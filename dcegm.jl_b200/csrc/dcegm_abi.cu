@@ -351,7 +351,10 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
             // half a wave first (one CTA per SM: the shortest time to the first transfer), then one wave, then per_chunk
             int cnt = nmodels > 2 * wave ? (cstart.empty() ? wave / 2 : cstart.size() == 1 ? wave : per_chunk) : per_chunk;
             if (want_one && nmodels - c0 <= per_chunk + wave / 2 && nmodels - c0 > wave / 2) cnt = nmodels - c0 - wave / 2;  // short last chunk
-            if (h->big) cnt = 148 * ((nmodels + 148 * 16 - 1) / (148 * 16));  // fine-grid solver: one envelope CTA per SM
+            // fine-grid solvers: one envelope CTA per SM and chunk.  (Splitting the last chunk to shorten the one transfer
+            // nothing can hide was measured slower — 148 + 65 + 43 models: 426 ms against 401 ms for 148 + 108: small
+            // chunks solve inefficiently, and the compact records of 108 models are a 26 ms copy.)
+            if (h->big) cnt = 148 * ((nmodels + 148 * 16 - 1) / (148 * 16));
             cnt = cnt < nmodels - c0 ? cnt : nmodels - c0;
             cstart.push_back(c0);
             ccount.push_back(cnt);
@@ -460,15 +463,24 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
         cudaError_t e = launch_range(h, Bc, 0, nmodels, h->stream);
         if (e != cudaSuccess) return cuda_fail(h, e, "kernel launch");
         launches += h->launches_last;
-    } else {
-        for (int c = 0; c < nchunks; c++) {
-            cudaError_t e = launch_range(h, Bc, cstart[c], ccount[c], h->stream);
-            if (e != cudaSuccess) return cuda_fail(h, e, "kernel launch");
-            launches += h->launches_last;
-            CK(cudaEventRecord(h->ev_pool[3 * c], h->stream));
-        }
     }
-    CK(cudaEventRecord(h->ev[3], h->stream));
+    // one launch per chunk: the fine-grid solvers issue hundreds of launches per chunk, and more than ~1000 pending
+    // launches make the host block in cudaLaunchKernel (it then sees a finished chunk's offsets late): only two chunks
+    // are in the launch queue at a time there
+    int launched = one_launch ? nchunks : 0;
+    const int lookahead = h->big ? 2 : nchunks;
+    auto launch_next = [&]() -> int {
+        const int c = launched;
+        cudaError_t e = launch_range(h, Bc, cstart[c], ccount[c], h->stream);
+        if (e != cudaSuccess) return cuda_fail(h, e, "kernel launch");
+        launches += h->launches_last;
+        CK(cudaEventRecord(h->ev_pool[3 * c], h->stream));
+        if (++launched == nchunks) CK(cudaEventRecord(h->ev[3], h->stream));
+        return DCEGM_OK;
+    };
+    if (one_launch) CK(cudaEventRecord(h->ev[3], h->stream));
+    while (launched < nchunks && launched < lookahead)
+        if ((rc = launch_next())) return rc;
 
     int64_t base = 0;
     offsets[0] = 0;
@@ -520,6 +532,7 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
         CK(cudaMemcpyAsync((char*)xy + unit * (size_t)base, buf, unit * (size_t)run_, cudaMemcpyDeviceToHost, h->s_copy));
         CK(cudaEventRecord(h->ev_pool[3 * c + 2], h->s_copy));
         base += run_;
+        if (launched < nchunks && (rc = launch_next())) return rc;
     }
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaStreamSynchronize(h->s_pack));
