@@ -109,9 +109,37 @@ def run_c4(solver, n=256, reps=3):
     ok, bits = status_counts(solver.status())
     t = float(np.median(ms))
     algo = 2 * 2 * 49 * 20001 * 16 * n
-    return {"workload": f"C4: fine-grid retirement model x{n} (na=20000, nT=50, ny=32)", "models": n, "solved": ok,
-            "status_bits": bits, "kernel_ms": t, "reps": reps, "models_per_s": ok / (t * 1e-3),
-            "launches_per_rep": solver.timing().n_launches, "algorithmic_gbs": algo / (t * 1e-3) / 1e9}
+    out = {"workload": f"C4: fine-grid retirement model x{n} (na=20000, nT=50, ny=32)", "models": n, "solved": ok,
+           "status_bits": bits, "kernel_ms": t, "reps": reps, "models_per_s": ok / (t * 1e-3),
+           "launches_per_rep": solver.timing().n_launches, "algorithmic_gbs": algo / (t * 1e-3) / 1e9}
+    # end to end through dcegm_solve_f_compact: host Param array in, every stored polyline in pinned host memory out
+    lib, h = solver.lib, solver.h
+    lay = solver.layout()
+    nslots = n * lay.nT * lay.nstate * 4
+    woff = np.zeros(nslots + 1, np.int64)
+    lens = np.zeros(nslots, np.int32)
+    aux = np.zeros(nslots, np.int32)
+    nw = C.c_int64()
+    lp, ip = C.POINTER(C.c_int64), C.POINTER(C.c_int32)
+    args = (woff.ctypes.data_as(lp), lens.ctypes.data_as(ip), aux.ctypes.data_as(ip), C.byref(nw))
+    if lib.dcegm_fetch_compact(h, 0, n, None, 0, *args) == 0:
+        cap_words = int(nw.value * 1.05) + 4096
+        pinned = C.c_void_p()
+        if lib.dcegm_host_alloc(C.byref(pinned), cap_words * 8) == 0:
+            ts = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                rc = lib.dcegm_solve_f_compact(h, arr, n, 0, C.cast(pinned, C.POINTER(C.c_double)), cap_words, *args)
+                ts.append(time.perf_counter() - t0)
+                if rc != 0:
+                    break
+            lib.dcegm_host_free(pinned)
+            if rc == 0:
+                out["e2e_ms"] = min(ts[1:]) * 1e3
+                out["e2e_d2h_bytes"] = int(nw.value * 8 + woff.nbytes + lens.nbytes + aux.nbytes)
+                out["e2e_solved_models_per_s"] = ok / min(ts[1:])
+                out["e2e_xy_bytes"] = int(lens.astype(np.int64).sum() * 16)
+    return out
 
 
 def run_c5(solver, local, world, rank, dist, per=8192, nsims=100000, reps=3):
