@@ -353,13 +353,15 @@ def main():
         off = np.zeros(nslots + 1, np.int64)
         npts = C.c_int64()
         threads = os.cpu_count() or 1
-        t0 = time.perf_counter()
-        rc = lib.dcegm_expand_compact(h, 0, nper, pin_d, wp, lnp, axp, xy.ctypes.data_as(C.POINTER(C.c_double)), npts_total,
-                                      off.ctypes.data_as(lp), C.byref(npts), threads)
-        t_exp = time.perf_counter() - t0
-        assert rc == 0, lib.dcegm_last_error(h)
+        t_exp = []
+        for _ in range(2):  # the first pass also faults in the 3.15 GB destination; the second is the decoder alone
+            t0 = time.perf_counter()
+            rc = lib.dcegm_expand_compact(h, 0, nper, pin_d, wp, lnp, axp, xy.ctypes.data_as(C.POINTER(C.c_double)), npts_total,
+                                          off.ctypes.data_as(lp), C.byref(npts), threads)
+            t_exp.append(time.perf_counter() - t0)
+            assert rc == 0, lib.dcegm_last_error(h)
         ref_xy, ref_off = solver.fetch_packed()
-        expand = {"ms": t_exp * 1e3, "threads": threads, "points": int(npts.value),
+        expand = {"ms": t_exp[1] * 1e3, "ms_first_touch": t_exp[0] * 1e3, "threads": threads, "points": int(npts.value),
                   "equals_packed_points_bitwise": bool(xy.tobytes() == ref_xy.tobytes() and np.array_equal(off, ref_off))}
         del xy, ref_xy
     lib.dcegm_host_free(pinned)

@@ -38,20 +38,47 @@ bool decode_y(const double* sec, int yw, int n, double* out) {
         const int w = wb[blk];
         const int cnt = n - blk * 32 < 32 ? n - blk * 32 : 32;
         if (w > 8 || at + (size_t)w * cnt > pay_cap) return false;
-        for (int j = 0; j < cnt; j++) {
-            uint64_t r = 0;
-            if (w) {
-                memcpy(&r, pay + at, w);  // little-endian host
-                if (w < 8 && (r >> (8 * w - 1)) & 1) r |= ~uint64_t(0) << (8 * w);  // sign extension
-                at += w;
-            }
-            const int k = blk * 32 + j;
-            if (k < 2) continue;  // raw words
-            const uint64_t c = r + 2 * b - a;
-            memcpy(&out[2 * k + 1], &c, 8);
-            a = b;
-            b = c;
+        const int k0 = blk * 32;
+        const int j0 = k0 < 2 ? 2 - k0 : 0;  // the residuals of k = 0, 1 are place-holders (raw words in front)
+        const unsigned char* src = pay + at + (size_t)j0 * w;
+        double* dst = out + 2 * (size_t)(k0 + j0) + 1;
+        // width-specialised inner loops: one unaligned 8-byte load per residual (the record's run words follow the
+        // payload, so the load never leaves the record), sign extension by a shift pair, the integer recurrence
+        switch (w) {
+#define DC_BLOCK(W)                                                                                  \
+    case W:                                                                                          \
+        for (int j = j0; j < cnt; j++, src += W, dst += 2) {                                         \
+            uint64_t raw;                                                                            \
+            memcpy(&raw, src, 8);                                                                    \
+            const uint64_t r = (uint64_t)((int64_t)(raw << (64 - 8 * W)) >> (64 - 8 * W));           \
+            const uint64_t c = r + 2 * b - a;                                                        \
+            memcpy(dst, &c, 8);                                                                      \
+            a = b;                                                                                   \
+            b = c;                                                                                   \
+        }                                                                                            \
+        break;
+            case 0:
+                for (int j = j0; j < cnt; j++, dst += 2) {
+                    const uint64_t c = 2 * b - a;
+                    memcpy(dst, &c, 8);
+                    a = b;
+                    b = c;
+                }
+                break;
+                DC_BLOCK(1) DC_BLOCK(2) DC_BLOCK(3) DC_BLOCK(4) DC_BLOCK(5) DC_BLOCK(6) DC_BLOCK(7)
+            case 8:
+                for (int j = j0; j < cnt; j++, src += 8, dst += 2) {
+                    uint64_t r;
+                    memcpy(&r, src, 8);
+                    const uint64_t c = r + 2 * b - a;
+                    memcpy(dst, &c, 8);
+                    a = b;
+                    b = c;
+                }
+                break;
+#undef DC_BLOCK
         }
+        at += (size_t)w * cnt;
     }
     return (at + 7) / 8 == (size_t)(yw - head);
 }
