@@ -40,7 +40,10 @@ def kernel_source_hash():
     h = hashlib.sha256()
     for f in KERNEL_SOURCES:
         with open(os.path.join(ROOT, "dcegm.jl_b200", "csrc", f), "rb") as fh:
-            h.update(fh.read())
+            data = fh.read()
+        if f == "Makefile":  # only what decides how a kernel is compiled, not the list of files linked into the library
+            data = b"".join(ln for ln in data.splitlines(True) if ln.split(b":=")[0].split(b"?=")[0].strip() in (b"NVCC", b"ARCH", b"NVFLAGS"))
+        h.update(data)
     return h.hexdigest()[:16]
 
 
