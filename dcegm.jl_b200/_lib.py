@@ -23,6 +23,7 @@ EXPORTS = [
     "dcegm_sweep_record_bytes", "dcegm_sweep_records_to_device",
     "dcegm_solve_f_compact", "dcegm_solve_g_compact", "dcegm_fetch_compact", "dcegm_expand_compact",
     "dcegm_decode_compact_pair", "dcegm_get_grid", "dcegm_debug_host_table", "dcegm_debug_check_guards",
+    "dcegm_pack_lines_noalloc",
 ]
 
 
@@ -66,6 +67,9 @@ def load():
     lib.dcegm_decode_compact_pair.argtypes = [dp, C.c_int, dp, C.c_int, C.c_int, dp, C.c_int, C.c_int, dp, dp]
     lib.dcegm_get_grid.argtypes = [H, C.c_int, dp, C.c_int, C.POINTER(C.c_int)]
     lib.dcegm_debug_check_guards.argtypes = [H, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    # device pointers travel as plain integers (torch data_ptr())
+    lib.dcegm_pack_lines_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_size_t,
+                                             C.c_void_p, C.POINTER(C.c_int64), C.c_void_p, C.c_char_p, C.c_size_t]
     lib.dcegm_debug_host_table.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, dp, dp]
     lib.dcegm_simulate.argtypes = [H, C.c_uint, C.POINTER(_abi.dcegm_sim_shocks)]
     lib.dcegm_fetch_sim_moments.argtypes = [H, C.c_int, C.c_int, dp, ip, ip]

@@ -250,6 +250,29 @@ int  dcegm_fetch_dirty(dcegm_handle h, int first, int count, double* dirty);
  * query npoints/offsets only. */
 int  dcegm_fetch_packed(dcegm_handle h, int first, int count, double* xy, size_t cap_points,
                         int64_t* offsets, int64_t* npoints);
+/* ---- packing without allocation ---------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  It is dcegm_fetch_packed's
+ * device work — prefix offsets of min(lens, cap), then every line slot's points copied behind those of the slots before
+ * it — on caller-provided DEVICE memory, with the offsets scratch in a file-scope static device array of the library
+ * (csrc/no_alloc.cu) instead of a buffer grown with cudaMalloc.  The call allocates nothing (no cudaMalloc / cudaFree /
+ * allocating library routine); the array (8 MiB + 512 B) is held by every GPU that loads the library until the process
+ * exits, and bounds the call: nslots > DCEGM_NOALLOC_MAX_SLOTS is rejected with DCEGM_E_INVALID (a C3 batch of 4096
+ * models has 409 600 slots).
+ *   lines_dev   double [nslots][cap][2] (the `lines` layout above), lens_dev int32 [nslots]          device, inputs
+ *   xy_dev      double [cap_points][2]: the packed points                                            device, output
+ *   offsets_dev int64 [nslots + 1] prefix offsets in points, or NULL                                 device, output
+ *   npoints     HOST, or NULL.  Non-NULL: the call waits for `stream`, stores the total and returns DCEGM_E_CAPACITY if
+ *               it exceeds cap_points.  NULL: the call only enqueues work (one memset, two kernels) and returns.
+ *               Either way a slot that would end beyond cap_points is left out, never written past the end.
+ *   stream      a cudaStream_t (NULL: the default stream) of device_ordinal, on which all work is enqueued
+ *   errbuf      receives the message of a non-zero return (may be NULL)
+ * All calls on one device share the array, which keeps the last call's contents (the call clears the words that must
+ * start at zero): calls whose GPU work overlaps — different streams, or unordered host threads — race; serialise them. */
+#define DCEGM_NOALLOC_MAX_SLOTS (1 << 20)
+int  dcegm_pack_lines_noalloc(int device_ordinal, const double* lines_dev, const int32_t* lens_dev, int64_t nslots, int cap,
+                              double* xy_dev, size_t cap_points, int64_t* offsets_dev, int64_t* npoints, void* stream,
+                              char* errbuf, size_t errbuf_bytes);
 /* ---- compact lines: the same polylines in half the bytes --------------------------------------------
  * A stored line is a Vector{Point} (line.jl:1-4), 16 B per point, but nearly every abscissa is redundant: a
  * policy line is (avec + c0, c0) (dc_algo.jl:65), so x = a[i] + y for the savings grid point i a point came from,
