@@ -340,6 +340,13 @@ def main():
     e2e_xy_value, d2h_xy, _ = timed_e2e(e2e_xy_step, min(args.steps, 3))
     e2e_value, d2h, d2h_gbs = timed_e2e(e2e_step, args.steps)
     e2e_launches = int(solver.timing().n_launches)  # kernels of one end-to-end step: solver + encoder passes per chunk
+    # slots delivered as a reference to an identical line of their chunk's first model (no record of their own)
+    idx_ = np.flatnonzero(lens_h > 0)
+    _, first_ = np.unique(woff[:-1][idx_], return_index=True)  # the first slot at an offset owns the record
+    own_ = np.zeros(len(idx_), bool)
+    own_[first_] = True
+    shared_slots = int((~own_).sum())
+    shared_points = int(lens_h[idx_[~own_]].sum())
     clocks = sampler.stop() if rank == 0 else None  # sampled over both timed regions (device-resident and e2e)
     gbs_all = None
     if dist:  # per-rank device-to-host rates (the host side limits e2e on a multi-GPU box)
@@ -416,11 +423,15 @@ def main():
                                         ") x models / kernel time; peak = dcegm_debug_dfma_rate measured in this run"},
             "e2e": {"value": e2e_value, "unit": "models/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "d2h_gbs": d2h_gbs, "d2h_gbs_per_rank": gbs_all, "gpu_launches_per_step": e2e_launches,
-                    "format": "compact lines (include/dcegm.h): ordinates + abscissa runs, lossless; expanded lazily per line by the host mirror",
+                    "format": "compact lines (include/dcegm.h): ordinates + abscissa runs, lossless; a line bit-identical to the same "
+                              "slot of its chunk's first model travels once; expanded lazily per line by the host mirror",
+                    "lines_delivered_by_reference": {"slots": shared_slots, "of_slots": int((lens_h > 0).sum()), "points": shared_points,
+                                                     "note": "the retiree's lines do not depend on (lambda, sigma), the two swept "
+                                                             "parameters of C3; DCEGM_COMPACT_ALIAS=0 ships every line on its own"},
                     "expand_all_on_host": expand,
                     "full_xy": {"value": e2e_xy_value, "unit": "models/s", "d2h_bytes_per_step": int(d2h_xy),
                                 "note": "the same call delivering every point as an (x, y) pair (dcegm_solve_f_packed)"},
-                    "note": "bound by the device-to-host transfer of the stored polylines over PCIe"},
+                    "note": "the solver kernel with the encoder running beside it, plus upload and the last chunk's encode + copy"},
             "gpu_launches": args.steps * 1,
             "clocks": clocks,
         }

@@ -17,7 +17,9 @@ _lp = C.POINTER(C.c_int64)
 
 class CompactLines:
     """words [nwords] float64 (8-byte words), woffsets [nslots + 1], lens [nslots], aux [nslots]; slots in layout
-    order [model][it][iy][id][kind].  `solver` (optional) lets `expand` use the library's threaded decoder and
+    order [model][it][iy][id][kind].  woffsets[slot] is where the slot's record starts; a slot whose line is bit-identical
+    to the same slot of its delivery chunk's first model has that model's offset (no record of its own), so sizes are
+    never differences of offsets.  `solver` (optional) lets `expand` use the library's threaded decoder and
     `grid` fetch the savings grids; without it pass `grids` = {model: avec}."""
 
     def __init__(self, lay_nT, lay_nstate, nmodels, words, woffsets, lens, aux, solver=None, first=0, grids=None):

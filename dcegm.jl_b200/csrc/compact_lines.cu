@@ -36,6 +36,7 @@ constexpr int kCT = 256;  // threads per CTA of the two kernels
 constexpr int kPairsPerCta = kCT / 32;
 constexpr unsigned kKindGrid = 0, kKindRef = 1, kKindExplicit = 2;
 constexpr unsigned kNoCode = 0xffffffffu;
+constexpr int32_t kAliasMark = -1;  // aux / yws of a slot without a record of its own (nrun = nx = 65535 cannot occur)
 
 __device__ __forceinline__ bool same_bits(double a, double b) { return __double_as_longlong(a) == __double_as_longlong(b); }
 
@@ -213,15 +214,36 @@ __device__ LineSizes encode_line(const double2* __restrict__ L, int n, bool valu
     return z;
 }
 
+// all n points of A and R bit-identical? (one warp; 32 points per step, leaves at the first difference)
+__device__ __forceinline__ bool same_line(const double2* __restrict__ A, const double2* __restrict__ R, int n) {
+    const int lane = threadIdx.x & 31;
+    const ulonglong2* a = reinterpret_cast<const ulonglong2*>(A);
+    const ulonglong2* r = reinterpret_cast<const ulonglong2*>(R);
+    for (int k0 = 0; k0 < n; k0 += 32) {
+        const int k = k0 + lane;
+        bool ne = false;
+        if (k < n) {
+            const ulonglong2 u = a[k], v = r[k];
+            ne = u.x != v.x || u.y != v.y;
+        }
+        if (__any_sync(0xffffffffu, ne)) return false;
+    }
+    return true;
+}
+
 }  // namespace
 
 // sizes of the compact records of the slot pairs [first_pair, first_pair + npairs) and the per-point codes:
 // aux[slot] = nrun | nx << 16, yws[slot] = words of the ordinate section, wsize[slot] = 1 + yw + nrun + nx (words; 0 for
-// an empty slot), codes[slot][cap]
-__global__ void __launch_bounds__(kCT) compact_count_kernel(DeviceBatch B, size_t first_pair, size_t npairs, int32_t* __restrict__ aux,
-                                                            int32_t* __restrict__ yws, int32_t* __restrict__ wsize,
-                                                            unsigned* __restrict__ codes, int32_t* __restrict__ aux_host,
-                                                            int32_t* __restrict__ lens_host) {
+// an empty slot), codes[slot][cap].
+// alias_pairs > 0 (= slot pairs per model): a pair of a later model whose two lines are bit-identical to the same
+// (it, iy, id) pair of the range's FIRST model gets no record — aux = yws = kAliasMark, wsize = 0 — and the host points
+// its offsets at the first model's records.  In a sweep over (lambda, sigma) every retiree line is such a line: the
+// retiree has no income draw (param.jl:212) and no taste-shocked choice (dc_algo.jl:44).
+__global__ void __launch_bounds__(kCT) compact_count_kernel(DeviceBatch B, size_t first_pair, size_t npairs, size_t alias_pairs,
+                                                            int32_t* __restrict__ aux, int32_t* __restrict__ yws,
+                                                            int32_t* __restrict__ wsize, unsigned* __restrict__ codes,
+                                                            int32_t* __restrict__ aux_host, int32_t* __restrict__ lens_host) {
     __shared__ double s_xc[kPairsPerCta][kStageCap];
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const size_t lq = (size_t)blockIdx.x * kPairsPerCta + wid;
@@ -234,6 +256,26 @@ __global__ void __launch_bounds__(kCT) compact_count_kernel(DeviceBatch B, size_
     int nc = B.lens[sc], nv = B.lens[sv];
     nc = nc < cap ? nc : cap;
     nv = nv < cap ? nv : cap;
+    if (alias_pairs && lq >= alias_pairs && nc + nv > 0) {
+        const size_t rc = 2 * (first_pair + lq % alias_pairs), rv = rc + 1;  // the first model's slots
+        int rnc = B.lens[rc], rnv = B.lens[rv];
+        rnc = rnc < cap ? rnc : cap;
+        rnv = rnv < cap ? rnv : cap;
+        if (rnc == nc && rnv == nv && same_line(B.lines + sc * (size_t)cap, B.lines + rc * (size_t)cap, nc) &&
+            same_line(B.lines + sv * (size_t)cap, B.lines + rv * (size_t)cap, nv)) {
+            if (lane < 2) {
+                const size_t s = sc + lane - 2 * first_pair;
+                aux[s] = kAliasMark;
+                yws[s] = kAliasMark;
+                wsize[s] = 0;
+                if (aux_host) {
+                    aux_host[s] = kAliasMark;
+                    lens_host[s] = lane ? nv : nc;
+                }
+            }
+            return;  // warp-uniform
+        }
+    }
     ClassifyCtx cx;
     cx.a = B.grids + (size_t)p.grid * p.na;
     cx.na = p.na;
@@ -282,6 +324,7 @@ __global__ void __launch_bounds__(kCT) compact_write_kernel(DeviceBatch B, size_
     int nc = B.lens[sc], nv = B.lens[sv];
     nc = nc < cap ? nc : cap;
     nv = nv < cap ? nv : cap;
+    if (yws[sc - 2 * first_pair] == kAliasMark) return;  // no record of its own (compact_count_kernel)
     ClassifyCtx cx{};
     const double2* Lc = B.lines + sc * (size_t)cap;
     const double2* Lv = B.lines + sv * (size_t)cap;
@@ -299,13 +342,13 @@ __global__ void __launch_bounds__(kCT) compact_write_kernel(DeviceBatch B, size_
     }
 }
 
-cudaError_t launch_compact_count(const DeviceBatch& B, int first, int count, int32_t* aux, int32_t* yws, int32_t* wsize, unsigned* codes,
-                                 int32_t* aux_host, int32_t* lens_host, cudaStream_t stream) {
+cudaError_t launch_compact_count(const DeviceBatch& B, int first, int count, bool alias, int32_t* aux, int32_t* yws, int32_t* wsize,
+                                 unsigned* codes, int32_t* aux_host, int32_t* lens_host, cudaStream_t stream) {
     const size_t pairs_per = (size_t)B.lay.nT * B.lay.nstate * 2;
     if (count <= 0) return cudaSuccess;
     const size_t np = pairs_per * count;
-    compact_count_kernel<<<(unsigned)((np + kPairsPerCta - 1) / kPairsPerCta), kCT, 0, stream>>>(B, pairs_per * first, np, aux, yws, wsize, codes,
-                                                                                              aux_host, lens_host);
+    compact_count_kernel<<<(unsigned)((np + kPairsPerCta - 1) / kPairsPerCta), kCT, 0, stream>>>(B, pairs_per * first, np, alias ? pairs_per : 0,
+                                                                                              aux, yws, wsize, codes, aux_host, lens_host);
     return cudaGetLastError();
 }
 cudaError_t launch_compact_write(const DeviceBatch& B, int first, int count, const int32_t* aux, const int32_t* yws, const unsigned* codes,

@@ -34,7 +34,7 @@ cudaError_t launch_pack_lines(const DeviceBatch& B, int first, int count, const 
                               cudaStream_t stream);
 cudaError_t launch_chunk_offsets(const int32_t* lens, size_t nsl, int cap, long long* d_off, long long* h_off_mapped,
                                  cudaStream_t stream);
-cudaError_t launch_compact_count(const DeviceBatch& B, int first, int count, int32_t* aux, int32_t* yws, int32_t* wsize, unsigned* codes,
+cudaError_t launch_compact_count(const DeviceBatch& B, int first, int count, bool alias, int32_t* aux, int32_t* yws, int32_t* wsize, unsigned* codes,
                                  int32_t* aux_host, int32_t* lens_host, cudaStream_t stream);
 cudaError_t launch_compact_write(const DeviceBatch& B, int first, int count, const int32_t* aux, const int32_t* yws, const unsigned* codes,
                                  const long long* off, double* dst, cudaStream_t stream);
@@ -300,6 +300,22 @@ int run(dcegm_ctx* h) {
     return DCEGM_OK;
 }
 
+// Compact delivery: slot pairs whose lines are bit-identical to the same pair of the first model of their chunk carry
+// no record (compact_count_kernel marks them aux = -1).  off[0 .. nsl] / aux[0 .. nsl): the chunk's word offsets and run
+// counts, `per` slots per model; marked slots take over the first model's offset and run counts.  DCEGM_COMPACT_ALIAS=0
+// switches the detection off (every slot then has its own record).
+bool compact_alias() {
+    const char* e = getenv("DCEGM_COMPACT_ALIAS");
+    return !(e && atoi(e) == 0);
+}
+void resolve_aliases(int64_t* off, int32_t* aux, size_t per, size_t nsl) {
+    for (size_t s = per; s < nsl; s++)
+        if (aux[s] == -1) {
+            off[s] = off[s % per];
+            aux[s] = aux[s % per];
+        }
+}
+
 // Pipelined solve-to-host: the batch is solved in chunks on the compute stream while finished chunks
 // are packed densely (s_pack) and copied to the caller's buffer (s_copy), so that the D2H transfer of
 // chunk c overlaps the kernels of chunk c+1...  The only host round trip per chunk is its line lengths
@@ -497,7 +513,7 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
         if (c >= 1) CK(cudaStreamWaitEvent(h->s_pack, h->ev_pool[3 * (c - 1) + 1], 0));  // pack_off still read by pack c-1
         cudaError_t e;
         if (compact) {
-            e = launch_compact_count(B, c0, cnt, (int32_t*)h->cmp_aux.p, (int32_t*)h->cmp_yw.p, (int32_t*)h->cmp_wsize.p, (unsigned*)h->cmp_codes.p,
+            e = launch_compact_count(B, c0, cnt, compact_alias(), (int32_t*)h->cmp_aux.p, (int32_t*)h->cmp_yw.p, (int32_t*)h->cmp_wsize.p, (unsigned*)h->cmp_codes.p,
                                      pin_aux_dev, pin_aux_dev + cslots, h->s_pack);
             if (e != cudaSuccess) return cuda_fail(h, e, "compact count kernel");
             e = launch_chunk_offsets((const int32_t*)h->cmp_wsize.p, nsl, 0x7fffffff, (long long*)h->pack_off.p, pin_off_dev, h->s_pack);
@@ -513,6 +529,7 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
         if (compact) {
             memcpy(aux_out + per * c0, h->pin_aux, sizeof(int32_t) * nsl);
             memcpy(lens_out + per * c0, h->pin_aux + cslots, sizeof(int32_t) * nsl);
+            resolve_aliases(go, aux_out + per * c0, per, nsl);
         }
         if ((size_t)(base + run_) > cap_points) {
             err = fail(h, DCEGM_E_CAPACITY, "dcegm_solve_*_packed: destination too small");
@@ -861,7 +878,7 @@ int dcegm_fetch_compact(dcegm_handle h, int first, int count, double* words, siz
     if ((rc = ensure(h, h->pack_off, sizeof(long long) * (nsl + 1), false))) return rc;
     if ((rc = ensure(h, h->cmp_codes, sizeof(unsigned) * nsl * l.cap, false))) return rc;
     if ((rc = ensure(h, h->cmp_yw, sizeof(int32_t) * nsl, false))) return rc;
-    cudaError_t e = launch_compact_count(h->batch, first, count, (int32_t*)h->cmp_aux.p, (int32_t*)h->cmp_yw.p, (int32_t*)h->cmp_wsize.p,
+    cudaError_t e = launch_compact_count(h->batch, first, count, compact_alias(), (int32_t*)h->cmp_aux.p, (int32_t*)h->cmp_yw.p, (int32_t*)h->cmp_wsize.p,
                                          (unsigned*)h->cmp_codes.p, nullptr, nullptr, h->stream);
     if (e != cudaSuccess) return cuda_fail(h, e, "compact count kernel");
     std::vector<int32_t> wsize(nsl);
@@ -874,10 +891,14 @@ int dcegm_fetch_compact(dcegm_handle h, int first, int count, double* words, siz
         woffsets[s + 1] = woffsets[s] + wsize[s];
     }
     *nwords = woffsets[nsl];
+    if (words) {  // device copy of the prefix offsets (aliased slots are skipped by the write kernel)
+        if ((size_t)*nwords > cap_words) return fail(h, DCEGM_E_CAPACITY, "dcegm_fetch_compact: destination too small");
+        CK(cudaMemcpyAsync(h->pack_off.p, woffsets, sizeof(int64_t) * (nsl + 1), cudaMemcpyHostToDevice, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    resolve_aliases(woffsets, aux, per, nsl);
     if (!words) return DCEGM_OK;
-    if ((size_t)*nwords > cap_words) return fail(h, DCEGM_E_CAPACITY, "dcegm_fetch_compact: destination too small");
     if ((rc = ensure(h, h->pack_xy, sizeof(double) * (size_t)*nwords, false))) return rc;
-    CK(cudaMemcpyAsync(h->pack_off.p, woffsets, sizeof(int64_t) * (nsl + 1), cudaMemcpyHostToDevice, h->stream));
     e = launch_compact_write(h->batch, first, count, (const int32_t*)h->cmp_aux.p, (const int32_t*)h->cmp_yw.p, (const unsigned*)h->cmp_codes.p,
                              (const long long*)h->pack_off.p, (double*)h->pack_xy.p, h->stream);
     if (e != cudaSuccess) return cuda_fail(h, e, "compact write kernel");

@@ -291,7 +291,14 @@ int  dcegm_pack_lines_noalloc(int device_ordinal, const double* lines_dev, const
  *       kind 0  x[pos + j] = a[src + j] + y[pos + j]     (a: the model's savings grid, dcegm_get_grid; one IEEE add)
  *       kind 1  x[pos + j] = x of point src + j of the POLICY line of the same (model, it, iy, id)   (value lines only)
  *       kind 2  x[pos + j] = next unread word of xs
- * woffsets[nslots + 1] are prefix offsets in words into `words`.  dcegm_solve_*_compact is dcegm_solve_*_packed with
+ * woffsets[s] is the word offset of slot s's record in `words`, woffsets[nslots] the total (*nwords).  IDENTICAL LINES
+ * TRAVEL ONCE: a (policy, value) slot pair whose two lines are bit-identical to the same (it, iy, id) pair of the FIRST
+ * model of its delivery chunk (dcegm_fetch_compact: of model `first`) has no record of its own — its woffsets entries
+ * are that model's, its aux / lens equal that model's — so woffsets is not monotone, and the size of a record follows
+ * from lens, aux and the record's head, never from differences of woffsets.  In a sweep over (lambda, sigma) all retiree
+ * lines are of this kind (a retiree has no income draw, param.jl:212, and no taste-shocked choice, dc_algo.jl:44): 44 % of a C3
+ * batch's bytes.  Decoders need no special case.  DCEGM_COMPACT_ALIAS=0 (environment) switches the detection off.
+ * dcegm_solve_*_compact is dcegm_solve_*_packed with
  * this delivery format (same chunked pipeline; `words` from dcegm_host_alloc makes the copies asynchronous);
  * cap_words = nslots * (2 * cap + cap / 256 + 4) always fits (a C3 batch needs 0.49 words per point).  dcegm_fetch_compact encodes models [first, first + count) of the
  * resident solution (words == NULL: sizes only).  dcegm_expand_compact rebuilds the densely packed points of

@@ -188,7 +188,8 @@ function solve_batch(ps::Vector{Param}; model = :f)
 end
 
 # ---- the same sweep in the compact line format (include/dcegm.h "compact lines"): half the bytes over PCIe; lines are
-# rebuilt lazily, one Envelope pair at a time, by the handle-free decoder ------------------------------------------
+# rebuilt lazily, one Envelope pair at a time, by the handle-free decoder.  woff[slot] is the START of a slot's record;
+# lines shared bit for bit with the chunk's first model (retirees in a (lambda, sigma) sweep) point at its records ----
 struct CompactBatch
     words::Vector{Float64}; woff::Vector{Int64}; lens::Vector{Int32}; aux::Vector{Int32}
     grids::Vector{Vector{Float64}}   # savings grid of every model (dcegm_get_grid)

@@ -1,6 +1,8 @@
 """Compact line delivery (dcegm_solve_*_compact / dcegm_fetch_compact): expanding the compact records on the host
 gives the densely packed points of dcegm_fetch_packed BIT FOR BIT — retirement model incl. envelope-heavy and
 status-flagged draws, fine-grid solver, general model — in about a third of the bytes."""
+import os
+
 import numpy as np
 import pytest
 
@@ -21,6 +23,16 @@ def c3_draws(n, na=500):
     return ps
 
 
+def aliased(cl):
+    """slots without a record of their own: non-empty, and an earlier non-empty slot starts at the same offset"""
+    idx = np.flatnonzero(cl.lens > 0)
+    _, first = np.unique(cl.woffsets[:-1][idx], return_index=True)
+    al = np.zeros(len(cl.lens), bool)
+    al[idx] = True
+    al[idx[first]] = False
+    return al
+
+
 def check(s, cl, ratio_max):
     xy, off = s.fetch_packed()
     exy, eoff = cl.expand(nthreads=4)
@@ -39,11 +51,31 @@ def test_retirement_batch_pipeline_equals_packed():
     with Solver(0) as s:
         cl = s.solve_compact(_abi.MODEL_F, ps)
         assert int(s.status()[91]) == _abi.ST_DUP_KNOT
-        r = check(s, cl, 0.36)
-        # the non-pipelined encoder of the resident solution gives the same stream
+        r = check(s, cl, 0.22)
+        # identical lines travel once: every retiree pair (id 1) and the worker's terminal pair of a chunk's later models
+        # point at the chunk's first model (lambda and sigma enter neither), and nothing else does
+        al = aliased(cl)
+        per = 25 * 4
+        assert al.reshape(700, 25, 2, 2)[:, :24, 0, :].sum() == 0
+        roots = np.flatnonzero(~al.reshape(700, per)[:, 2])  # models that carry their own retiree records
+        assert roots[0] == 0 and 2 <= len(roots) <= 8, roots
+        assert al.sum() == (700 - len(roots)) * 52
+        # the non-pipelined encoder of the resident solution: one root (model 0), same lines
         cl2 = s.fetch_compact()
-        assert cl2.words.tobytes() == cl.words.tobytes() and np.array_equal(cl2.woffsets, cl.woffsets)
+        check(s, cl2, 0.22)
+        assert aliased(cl2).sum() == 699 * 52
         assert np.array_equal(cl2.aux, cl.aux) and np.array_equal(cl2.lens, cl.lens)
+        # without the detection both encoders give the same stream, in slot order
+        os.environ["DCEGM_COMPACT_ALIAS"] = "0"
+        try:
+            cl_na = s.solve_compact(_abi.MODEL_F, ps)
+            check(s, cl_na, 0.36)
+            cl2_na = s.fetch_compact()
+            assert cl2_na.words.tobytes() == cl_na.words.tobytes() and np.array_equal(cl2_na.woffsets, cl_na.woffsets)
+            assert aliased(cl_na).sum() == 0 and (np.diff(cl_na.woffsets) >= 0).all()
+            assert np.array_equal(cl_na.aux, cl.aux) and np.array_equal(cl_na.lens, cl.lens)
+        finally:
+            os.environ.pop("DCEGM_COMPACT_ALIAS")
         # a sub-range, and single lines through the handle-free decoder
         cl3 = s.fetch_compact(first=90, count=3)
         sol = s.fetch(first=90, count=3)
@@ -72,6 +104,10 @@ def test_fine_grid_and_general_model():
             pg.append(Param(par=d))
         cl = s.solve_compact(_abi.MODEL_G, pg)
         check(s, cl, 0.50)
+        # five identical general models: everything behind the first one is a reference to it
+        cl = s.solve_compact(_abi.MODEL_G, [Param(par=dict(na=100, rho=0.5))] * 5)
+        check(s, cl, 0.20)
+        assert aliased(cl).reshape(5, -1)[1:].sum() == (cl.lens.reshape(5, -1)[1:] > 0).sum() and aliased(cl).reshape(5, -1)[0].sum() == 0
         # bequest variant: terminal lines on the full grid
         s.solve(_abi.MODEL_G, [Param(par=dict(na=100, nu=2.0))], fetch=False)
         check(s, s.fetch_compact(), 0.55)

@@ -87,7 +87,9 @@ def test_results_do_not_depend_on_schedule_or_repetition():
                 os.environ["DCEGM_ONE_LAUNCH"] = "0"
                 cl2 = s.solve_compact(_abi.MODEL_F, ps)  # one launch per chunk
                 os.environ.pop("DCEGM_ONE_LAUNCH")
-                assert cl2.words.tobytes() == cl.words.tobytes() and np.array_equal(cl2.woffsets, cl.woffsets)
+                # other chunk boundaries, so other models carry the shared retiree records: same lines all the same
+                assert cl2.expand()[0].tobytes() == cl.expand()[0].tobytes()
+                assert np.array_equal(cl2.aux, cl.aux) and np.array_equal(cl2.lens, cl.lens)
     finally:
         os.environ.pop("DCEGM_ONE_LAUNCH", None)
         if old is None:
