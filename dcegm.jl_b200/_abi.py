@@ -1,7 +1,7 @@
 """ctypes mirror of include/dcegm.h (structures and constants only; no library is loaded here)."""
 import ctypes as C
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 # error codes
 OK, E_INVALID, E_CUDA, E_NOSOLUTION, E_NODEVICE, E_CAPACITY = 0, -1, -2, -3, -4, -5

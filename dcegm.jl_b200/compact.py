@@ -99,31 +99,45 @@ def encode_reference(lines_c, lines_v, grid):
     (rec_c, aux_c, rec_v, aux_v)."""
 
     def enc_y(y):
-        """ordinate section: I_0 | I_1 - I_0 | width bytes | payload of second differences (blocks of 32)"""
+        """ordinate section: I_0 | I_1 - I_0 | control bytes | payload; blocks of 8 points hold the second or the third
+        differences of the bit patterns (whichever is narrower), w four-bit units per residual"""
         n = len(y)
         if n == 0:
             return np.zeros(0)
-        I = np.ascontiguousarray(y, float).view(np.uint64)
-        with np.errstate(over="ignore"):
-            head = [I[0]] + ([I[1:2] - I[0:1]][0].tolist() if n > 1 else [])
-            R = np.zeros(n, np.uint64)  # blocks cover k = 32 b .. 32 b + 31; R_0 = R_1 = 0 (raw words in front)
-            if n > 2:
-                R[2:] = I[2:] - 2 * I[1:-1] + I[:-2]
-        widths, payload = [], bytearray()
-        for b0 in range(0, len(R), 32):
-            blk = R[b0:b0 + 32].view(np.int64)
-            w = 0
-            for r in blk:
-                r = int(r)
-                if r:
-                    bits = (r if r >= 0 else ~r).bit_length() + 1
-                    w = max(w, (bits + 7) // 8)
-            widths.append(w)
-            for r in blk:
-                payload += int(r).to_bytes(8, "little", signed=True)[:w]
-        wb = bytes(widths) + bytes(-len(widths) % 8)
+        M = (1 << 64) - 1
+        I = [int(v) for v in np.ascontiguousarray(y, float).view(np.uint64)]
+        head = [I[0]] + ([(I[1] - I[0]) & M] if n > 1 else [])
+        R2 = [0] * n  # R2_0 = R2_1 = 0 (raw words in front)
+        for k in range(2, n):
+            R2[k] = (I[k] - 2 * I[k - 1] + I[k - 2]) & M
+        R3 = [0] * n
+        for k in range(2, n):
+            R3[k] = (R2[k] - R2[k - 1]) & M
+
+        def signed(u):
+            return u - (1 << 64) if u >> 63 else u
+
+        def nibbles(u):
+            r = signed(u)
+            return 0 if r == 0 else ((r if r >= 0 else ~r).bit_length() + 1 + 3) // 4
+
+        ctl, payload = [], bytearray()
+        for b0 in range(0, n, 8):
+            cnt = min(8, n - b0)
+            w2 = max(nibbles(u) for u in R2[b0:b0 + cnt])
+            w3 = max(nibbles(u) for u in R3[b0:b0 + cnt])
+            third = w3 < w2
+            w, R = (w3, R3) if third else (w2, R2)
+            ctl.append(w | (32 if third else 0))
+            hb = w >> 1
+            for u in R[b0:b0 + cnt]:
+                payload += u.to_bytes(8, "little")[:hb]
+            if w & 1:
+                tops = [(u >> (8 * hb)) & 15 for u in R[b0:b0 + cnt]] + [0]
+                payload += bytes(tops[2 * i] | (tops[2 * i + 1] << 4) for i in range((cnt + 1) // 2))
+        cb = bytes(ctl) + bytes(-len(ctl) % 8)
         payload += bytes(-len(payload) % 8)
-        return np.concatenate([np.array(head, np.uint64), np.frombuffer(wb + bytes(payload), np.uint64)]).view(np.float64)
+        return np.concatenate([np.array(head, np.uint64), np.frombuffer(cb + bytes(payload), np.uint64)]).view(np.float64)
 
     def enc(L, codes):
         n = len(L)

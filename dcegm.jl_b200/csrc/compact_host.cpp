@@ -19,66 +19,67 @@ inline uint64_t word_bits(double w) {
     return b;
 }
 
-// The ordinate section (compact_lines.cu): I_0 | I_1 - I_0 | width bytes | payload of second differences of the
-// 64-bit patterns, blocks of 32 points.  Writes the n ordinates to out[2 k + 1].  false when the section is inconsistent.
+// The ordinate section (compact_lines.cu): I_0 | I_1 - I_0 | control bytes | payload; blocks of 8 points hold second or
+// third differences of the 64-bit patterns, w four-bit units each.  Writes the n ordinates to out[2 k + 1].  false when
+// the section is inconsistent.
+template <int HB, bool ODD>
+inline void decode_block(const unsigned char* src, const unsigned char* top, int j0, int cnt, bool third, uint64_t& i1,
+                         uint64_t& d1, uint64_t& d2, double* dst) {
+    constexpr int bits = 8 * HB + (ODD ? 4 : 0);  // width of a residual, 0 .. 64
+    for (int j = j0; j < cnt; j++, dst += 2) {
+        uint64_t r = 0;
+        if constexpr (bits > 0) {
+            uint64_t v = 0;
+            // one unaligned 8-byte load per residual: the record's run words follow the payload, so the load never
+            // leaves the record; bytes beyond the residual's own are shifted out below
+            if constexpr (HB > 0) memcpy(&v, src + (size_t)j * HB, 8);
+            if constexpr (ODD) v = (v & ((1ULL << (8 * HB)) - 1)) | ((uint64_t)((top[j >> 1] >> (4 * (j & 1))) & 15) << (8 * HB));
+            r = (uint64_t)((int64_t)(v << (64 - bits)) >> (64 - bits));  // sign extension
+        }
+        d2 = third ? d2 + r : r;
+        d1 += d2;
+        i1 += d1;
+        memcpy(dst, &i1, 8);
+    }
+}
+
 bool decode_y(const double* sec, int yw, int n, double* out) {
     if (n <= 0) return yw == 0;
-    const int nblk = (n + 31) / 32;  // block b: k = 32 b .. 32 b + 31; the residuals of k = 0, 1 are zero place-holders
+    const int nblk = (n + 7) / 8;  // block b: k = 8 b .. 8 b + 7; the residuals of k = 0, 1 are zero place-holders
     const int head = (n < 2 ? n : 2) + (nblk + 7) / 8;
     if (yw < head) return false;
-    uint64_t i0 = word_bits(sec[0]), i1 = n > 1 ? i0 + word_bits(sec[1]) : 0;
-    memcpy(&out[1], &i0, 8);
-    if (n > 1) memcpy(&out[3], &i1, 8);
-    const unsigned char* wb = reinterpret_cast<const unsigned char*>(sec + (n < 2 ? n : 2));
+    uint64_t i1 = word_bits(sec[0]), d1 = 0, d2 = 0;  // I_(k-1), I_(k-1) - I_(k-2), R2_(k-1)
+    memcpy(&out[1], &i1, 8);
+    if (n > 1) {
+        d1 = word_bits(sec[1]);
+        i1 += d1;
+        memcpy(&out[3], &i1, 8);
+    }
+    const unsigned char* ctl = reinterpret_cast<const unsigned char*>(sec + (n < 2 ? n : 2));
     const unsigned char* pay = reinterpret_cast<const unsigned char*>(sec + head);
     const size_t pay_cap = (size_t)(yw - head) * 8;
     size_t at = 0;
-    uint64_t a = i0, b = i1;  // I_(k-2), I_(k-1)
     for (int blk = 0; blk < nblk; blk++) {
-        const int w = wb[blk];
-        const int cnt = n - blk * 32 < 32 ? n - blk * 32 : 32;
-        if (w > 8 || at + (size_t)w * cnt > pay_cap) return false;
-        const int k0 = blk * 32;
+        const int c = ctl[blk], w = c & 31, hb = w >> 1;
+        const bool third = (c & 32) != 0;
+        const int cnt = n - blk * 8 < 8 ? n - blk * 8 : 8;
+        const size_t bytes = (size_t)cnt * hb + ((w & 1) ? (cnt + 1) / 2 : 0);
+        if (w > 16 || (c & 0xc0) || at + bytes > pay_cap) return false;
+        const int k0 = blk * 8;
         const int j0 = k0 < 2 ? 2 - k0 : 0;  // the residuals of k = 0, 1 are place-holders (raw words in front)
-        const unsigned char* src = pay + at + (size_t)j0 * w;
+        const unsigned char* src = pay + at;
+        const unsigned char* top = src + (size_t)cnt * hb;
         double* dst = out + 2 * (size_t)(k0 + j0) + 1;
-        // width-specialised inner loops: one unaligned 8-byte load per residual (the record's run words follow the
-        // payload, so the load never leaves the record), sign extension by a shift pair, the integer recurrence
         switch (w) {
-#define DC_BLOCK(W)                                                                                  \
-    case W:                                                                                          \
-        for (int j = j0; j < cnt; j++, src += W, dst += 2) {                                         \
-            uint64_t raw;                                                                            \
-            memcpy(&raw, src, 8);                                                                    \
-            const uint64_t r = (uint64_t)((int64_t)(raw << (64 - 8 * W)) >> (64 - 8 * W));           \
-            const uint64_t c = r + 2 * b - a;                                                        \
-            memcpy(dst, &c, 8);                                                                      \
-            a = b;                                                                                   \
-            b = c;                                                                                   \
-        }                                                                                            \
+#define DC_W(W)                                                                                   \
+    case W:                                                                                       \
+        decode_block<(W) / 2, ((W) & 1) != 0>(src, top, j0, cnt, third, i1, d1, d2, dst);         \
         break;
-            case 0:
-                for (int j = j0; j < cnt; j++, dst += 2) {
-                    const uint64_t c = 2 * b - a;
-                    memcpy(dst, &c, 8);
-                    a = b;
-                    b = c;
-                }
-                break;
-                DC_BLOCK(1) DC_BLOCK(2) DC_BLOCK(3) DC_BLOCK(4) DC_BLOCK(5) DC_BLOCK(6) DC_BLOCK(7)
-            case 8:
-                for (int j = j0; j < cnt; j++, src += 8, dst += 2) {
-                    uint64_t r;
-                    memcpy(&r, src, 8);
-                    const uint64_t c = r + 2 * b - a;
-                    memcpy(dst, &c, 8);
-                    a = b;
-                    b = c;
-                }
-                break;
-#undef DC_BLOCK
+            DC_W(0) DC_W(1) DC_W(2) DC_W(3) DC_W(4) DC_W(5) DC_W(6) DC_W(7) DC_W(8) DC_W(9) DC_W(10) DC_W(11) DC_W(12)
+            DC_W(13) DC_W(14) DC_W(15) DC_W(16)
+#undef DC_W
         }
-        at += (size_t)w * cnt;
+        at += bytes;
     }
     return (at + 7) / 8 == (size_t)(yw - head);
 }
@@ -90,7 +91,7 @@ bool decode_slot(const double* rec, int n, int nrun, int nx, const double* a, in
     if (n == 0) return nrun == 0 && nx == 0;
     if (nrun < 1) return false;
     const uint64_t yw64 = word_bits(rec[0]);
-    if (yw64 > (uint64_t)n + (uint64_t)n / 256 + 4) return false;
+    if (yw64 > (uint64_t)n + (uint64_t)n / 64 + 4) return false;
     const int yw = (int)yw64;
     if (!decode_y(rec + 1, yw, n, out)) return false;
     const double* runs = rec + 1 + yw;

@@ -10,22 +10,26 @@
 // bend-back points of the value line, ...) carry an explicit x.  The rules are verified per point on the device, so
 // the encoding is lossless whatever the solver produced (non-monotone or non-finite lines included).
 //
-// The ordinates themselves are smooth along a line, so they travel as the SECOND DIFFERENCES of their 64-bit patterns
-// (integer arithmetic modulo 2^64: exactly invertible), packed in blocks of 32 values with one byte width per block.
+// The ordinates themselves are smooth along a line, so they travel as SECOND (or third) DIFFERENCES of their 64-bit
+// patterns (integer arithmetic modulo 2^64: exactly invertible), packed in blocks of 8 values with one control byte
+// per block: the width of the block's residuals in 4-bit units and which of the two differences it holds.
 //
 // Record of one line slot, in 8-byte words (include/dcegm.h, "compact lines"):
 //     head | ysec[yw] | run[nrun] | xs[nx]          head = yw (words of the ordinate section)
-//     ysec = I_0 | I_1 - I_0 | width bytes w_b of the ceil(n/32) blocks, padded to 8 | payload, padded to 8
-//       I_k = bit pattern of y_k; block b holds R_k = I_k - 2 I_(k-1) + I_(k-2) for k = 32 b .. 32 b + 31 (R_0 = R_1 = 0:
-//       the first two ordinates are the raw words in front) as little-endian two's-complement integers of w_b bytes
-//       (w_b = 0: all zero)
+//     ysec = I_0 | I_1 - I_0 | control bytes c_b of the ceil(n/8) blocks, padded to 8 | payload, padded to 8
+//       I_k = bit pattern of y_k; R2_k = I_k - 2 I_(k-1) + I_(k-2) for k >= 2, R2_0 = R2_1 = 0 (the first two ordinates
+//       are the raw words in front); R3_k = R2_k - R2_(k-1).  Block b covers k = 8 b .. 8 b + 7 (cnt = 8, or what is left
+//       of the line) and holds R2 (c_b bit 5 clear) or R3 (bit 5 set) as two's-complement integers of w = c_b & 31
+//       four-bit units (0: all zero ... 16: raw), whichever is narrower: first cnt x (w >> 1) bytes, the low bytes of
+//       residual j little-endian at byte j (w >> 1); then, for odd w, ceil(cnt / 2) bytes with the top four bits of the
+//       residuals 2 i (low half) and 2 i + 1 (high half) in byte i
 //     run = pos | src << 16 | kind << 32 : points pos .. (next run's pos or n) - 1 take their abscissae from
 //       kind 0 (GRID)     x[pos + j] = a[src + j] + y[pos + j]          (one IEEE addition, as the kernels did)
 //       kind 1 (REF)      x[pos + j] = x of point src + j of the policy line of the same (model, it, iy, id)
 //       kind 2 (EXPLICIT) x[pos + j] = the next unread word of xs
 // Two passes per chunk: compact_count_kernel (per-point codes, sizes) -> chunk_offsets_kernel (prefix offsets,
 // solver_misc.cu) -> compact_write_kernel (streams lines + codes into the records).  One WARP per (policy, value) slot
-// pair, 32 points per step = one block of the ordinate section: ballots and shuffles only, no block-wide barrier.
+// pair, 32 points per step = four blocks of the ordinate section: ballots and shuffles only, no block-wide barrier.
 #include "device_common.cuh"
 
 namespace dcegm {
@@ -60,7 +64,7 @@ __device__ __forceinline__ int count_le_strided(const double* __restrict__ x, in
 constexpr int kStageCap = 640;  // doubles per warp: 8 x 5 KB of shared memory per CTA
 __device__ __forceinline__ unsigned classify(double2 pt, bool value_line, const double* __restrict__ a, int na, double a0,
                                              double inv_da, const double2* __restrict__ Lc, int nc,
-                                             const double* __restrict__ xs_c) {
+                                             const double* __restrict__ xs_c, int hint) {
     if (!value_line) {
         const double d = pt.x - pt.y;
         const double t = (d - a0) * inv_da;
@@ -79,6 +83,8 @@ __device__ __forceinline__ unsigned classify(double2 pt, bool value_line, const 
             if (i >= 0 && i < na && same_bits(a[i] + pt.y, pt.x)) return (kKindGrid << 16) | (unsigned)i;
         }
     } else if (xs_c) {
+        // value points mostly sit at a constant offset from their policy points: try where the previous step ended
+        if (hint >= 0 && hint < nc && same_bits(xs_c[hint], pt.x)) return (kKindRef << 16) | (unsigned)hint;
         const int j = count_le_strided(xs_c, 1, nc, pt.x) - 1;
         if (j >= 0 && same_bits(xs_c[j], pt.x)) return (kKindRef << 16) | (unsigned)j;
     } else {
@@ -102,14 +108,14 @@ struct ClassifyCtx {
     const double* xs_c;  // shared-memory copy of the policy line's abscissae or null
 };
 
-// bytes of the shortest two's-complement form of r (0 for r == 0)
-__device__ __forceinline__ int signed_bytes(long long r) {
+// four-bit units of the shortest two's-complement form of r (0 for r == 0, at most 16)
+__device__ __forceinline__ int signed_nibbles(long long r) {
     if (r == 0) return 0;
     const int bits = 65 - __clzll(r ^ (r >> 63));  // magnitude bits + sign bit
-    return (bits + 7) >> 3;
+    return (bits + 3) >> 2;
 }
-__host__ __device__ inline int ysec_head_words(int n) {  // raw words + width bytes, in words
-    const int nblk = (n + 31) / 32;
+__host__ __device__ inline int ysec_head_words(int n) {  // raw words + control bytes, in words
+    const int nblk = (n + 7) / 8;
     return (n < 2 ? n : 2) + (nblk + 7) / 8;
 }
 
@@ -129,25 +135,28 @@ __device__ LineSizes encode_line(const double2* __restrict__ L, int n, bool valu
     if (n == 0) return z;
     const int head = ysec_head_words(n);
     double* sec = rec + 1;
-    unsigned char* wbytes = WRITE ? reinterpret_cast<unsigned char*>(sec + (n < 2 ? n : 2)) : nullptr;
+    unsigned char* ctl = WRITE ? reinterpret_cast<unsigned char*>(sec + (n < 2 ? n : 2)) : nullptr;
     unsigned char* payload = WRITE ? reinterpret_cast<unsigned char*>(sec + head) : nullptr;
     double* rec_runs = WRITE ? rec + 1 + known.yw : nullptr;
     double* rec_xs = WRITE ? rec_runs + known.nrun : nullptr;
     int run_base = 0, x_base = 0, pay = 0;
     unsigned carry = kNoCode;
     unsigned long long ym1 = 0, ym2 = 0;  // bit patterns of the two ordinates before this step
+    long long r2m1 = 0;                   // second difference of the ordinate before this step
+    int ref_delta = 0;                    // count pass, value lines: policy index minus own index at the end of the last step
     for (int k0 = 0; k0 < n; k0 += 32) {
         const int k = k0 + lane;
         const bool in = k < n;
         double2 pt = make_double2(0.0, 0.0);
         unsigned code = kNoCode;
+        unsigned stash = 0;  // the count pass's word of this point: abscissa code | control byte of its block << 24
         if (in) {
             pt = L[k];
             if (WRITE) {
-                code = force_explicit ? (kKindExplicit << 16) : codes[k];
+                stash = codes[k];
+                code = force_explicit ? (kKindExplicit << 16) : (stash & 0x3ffffu);
             } else {
-                code = classify(pt, value_line, cx.a, cx.na, cx.a0, cx.inv_da, cx.Lc, cx.nc, cx.xs_c);
-                codes[k] = code;
+                code = classify(pt, value_line, cx.a, cx.na, cx.a0, cx.inv_da, cx.Lc, cx.nc, cx.xs_c, k + ref_delta);
             }
         }
         // ---- abscissa runs ----
@@ -169,7 +178,8 @@ __device__ LineSizes encode_line(const double2* __restrict__ L, int n, bool valu
         x_base += __popc(mx);
         const int last = (n - k0 < 32 ? n - k0 : 32) - 1;
         carry = __shfl_sync(0xffffffffu, code, last);
-        // ---- ordinates: second differences of the bit patterns, one block per step ----
+        if (!WRITE && (carry >> 16) == kKindRef) ref_delta = (int)(carry & 0xffffu) - (k0 + last);
+        // ---- ordinates: second / third differences of the bit patterns, four blocks of 8 per step ----
         const unsigned long long iy = (unsigned long long)__double_as_longlong(pt.y);
         unsigned long long p1 = __shfl_up_sync(0xffffffffu, iy, 1), p2 = __shfl_up_sync(0xffffffffu, iy, 2);
         if (lane == 0) {
@@ -178,35 +188,64 @@ __device__ LineSizes encode_line(const double2* __restrict__ L, int n, bool valu
         } else if (lane == 1) {
             p2 = ym1;
         }
-        const long long r = (in && k >= 2) ? (long long)(iy - 2ULL * p1 + p2) : 0LL;
-        const int w = __reduce_max_sync(0xffffffffu, signed_bytes(r));
-        const int cnt = last + 1;
+        const long long r2 = (in && k >= 2) ? (long long)(iy - 2ULL * p1 + p2) : 0LL;
+        long long r2p = __shfl_up_sync(0xffffffffu, r2, 1);
+        if (lane == 0) r2p = r2m1;
+        const long long r3 = (in && k >= 2) ? (long long)((unsigned long long)r2 - (unsigned long long)r2p) : 0LL;
+        const int j = lane & 7, g = lane >> 3;
+        int w;
+        bool third;
+        if (WRITE) {  // chosen by the count pass
+            w = (int)(stash >> 24) & 31;
+            third = ((stash >> 24) & 32u) != 0;
+        } else {
+            // maxima of both widths over the aligned groups of 8 lanes: bytewise maximum of the packed pair
+            unsigned ww = (unsigned)signed_nibbles(r2) | ((unsigned)signed_nibbles(r3) << 8);
+#pragma unroll
+            for (int o = 1; o < 8; o <<= 1) ww = __vmaxu4(ww, __shfl_xor_sync(0xffffffffu, ww, o));
+            const int w2 = (int)(ww & 0xffu), w3 = (int)(ww >> 8);
+            third = w3 < w2;
+            w = third ? w3 : w2;
+            if (in) codes[k] = code | ((unsigned)(w | (third ? 32 : 0)) << 24);
+        }
+        const int hb = w >> 1;
+        const long long r = third ? r3 : r2;
+        int cntg = n - (k0 + 8 * g);
+        cntg = cntg < 0 ? 0 : cntg > 8 ? 8 : cntg;
+        const int gbytes = cntg * hb + ((w & 1) ? (cntg + 1) >> 1 : 0);  // at most 68
+        // the four blocks' sizes packed into one word (byte g = block g), gathered by one OR reduction
+        const unsigned gb4 = __reduce_or_sync(0xffffffffu, j == 0 ? (unsigned)gbytes << (8 * g) : 0u);
+        const int goff = (int)__vsadu4(gb4 & ((1u << (8 * g)) - 1u), 0u);
         if (WRITE) {
-            if (lane == 0) wbytes[k0 >> 5] = (unsigned char)w;
+            const int nib = (w & 1) ? (int)(((unsigned long long)r >> (8 * hb)) & 0xfULL) : 0;
+            const int nib_next = __shfl_down_sync(0xffffffffu, nib, 1);
             if (in) {
-                unsigned char* dst = payload + pay + lane * w;
+                if (j == 0) ctl[(k0 >> 3) + g] = (unsigned char)(w | (third ? 32 : 0));
+                unsigned char* dst = payload + pay + goff;
                 unsigned long long u = (unsigned long long)r;
-                for (int i = 0; i < w; i++) {
-                    dst[i] = (unsigned char)(u & 0xffu);
+                for (int i = 0; i < hb; i++) {
+                    dst[j * hb + i] = (unsigned char)(u & 0xffu);
                     u >>= 8;
                 }
+                if ((w & 1) && !(j & 1)) dst[cntg * hb + (j >> 1)] = (unsigned char)(nib | ((j + 1 < cntg ? nib_next : 0) << 4));
             }
         }
-        pay += w * cnt;
+        pay += (int)__vsadu4(gb4, 0u);
         ym1 = __shfl_sync(0xffffffffu, iy, last);
         ym2 = last >= 1 ? __shfl_sync(0xffffffffu, iy, last - 1) : ym1;  // (a one-point tail only ends a line)
+        r2m1 = __shfl_sync(0xffffffffu, r2, last);
     }
     if (WRITE) {
-        const int nblk = (n + 31) / 32;
+        const int nblk = (n + 7) / 8;
         if (lane == 0) {
             rec[0] = __longlong_as_double((long long)known.yw);
             const unsigned long long i0 = (unsigned long long)__double_as_longlong(L[0].y);
             sec[0] = __longlong_as_double((long long)i0);
             if (n > 1) sec[1] = __longlong_as_double((long long)((unsigned long long)__double_as_longlong(L[1].y) - i0));
         }
-        if (lane < 8 && nblk + lane < ((nblk + 7) / 8) * 8) wbytes[nblk + lane] = 0;  // padding of the width bytes
+        if (lane < 8 && nblk + lane < ((nblk + 7) / 8) * 8) ctl[nblk + lane] = 0;  // padding of the control bytes
         const int pad = ((pay + 7) & ~7) - pay;
-        if (lane < pad) payload[pay + lane] = 0;                                      // ... and of the payload
+        if (lane < pad) payload[pay + lane] = 0;                                   // ... and of the payload
     }
     z.nrun = run_base;
     z.nx = x_base;

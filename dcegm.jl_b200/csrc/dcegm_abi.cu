@@ -424,8 +424,8 @@ int solve_packed(dcegm_ctx* h, int model, const dcegm_param* params, int nmodels
         if ((rc = ensure(h, h->cmp_yw, sizeof(int32_t) * cslots, false))) return rc;
         if ((rc = ensure(h, h->cmp_codes, sizeof(unsigned) * cslots * l.cap, false))) return rc;
     }
-    // compact records never exceed 2 n + n / 256 + 4 words (full-width ordinates, one explicit run), packed lines 2 n
-    const size_t pack_bytes = compact ? sizeof(double) * cslots * (2 * (size_t)l.cap + l.cap / 256 + 4) : sizeof(double2) * cslots * l.cap;
+    // compact records never exceed 2 n + n / 64 + 8 words (full-width ordinates, one explicit run), packed lines 2 n
+    const size_t pack_bytes = compact ? sizeof(double) * cslots * (2 * (size_t)l.cap + l.cap / 64 + 8) : sizeof(double2) * cslots * l.cap;
     if ((rc = ensure(h, h->pack_xy, pack_bytes, false))) return rc;
     if (nchunks > 1)
         if ((rc = ensure(h, h->pack_xy2, pack_bytes, false))) return rc;

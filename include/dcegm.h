@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define DCEGM_ABI_VERSION 1
+#define DCEGM_ABI_VERSION 2
 
 /* ---- error codes (function return values) --------------------------------- */
 #define DCEGM_OK            0
@@ -279,13 +279,18 @@ int  dcegm_pack_lines_noalloc(int device_ordinal, const double* lines_dev, const
  * and the value line of the same (period, state, choice) shares the policy line's abscissae (dc_algo.jl:78, :482,
  * :486-492).  The compact form ships the ordinates plus a few RUNS naming the source of each stretch of abscissae;
  * points for which neither rule reproduces the stored x bit for bit (verified per point on the device) carry an
- * explicit x.  The ordinates, smooth along a line, travel as the second differences of their 64-bit patterns (integer
- * arithmetic modulo 2^64, exactly invertible), byte-packed in blocks of 32.  Record of one line slot (slots in layout
- * order [model][it][iy][id][kind]; an empty slot has no record), in 8-byte words:
+ * explicit x.  The ordinates, smooth along a line, travel as second or third differences of their 64-bit patterns
+ * (integer arithmetic modulo 2^64, exactly invertible), packed in blocks of 8 with a width in four-bit units per block.
+ * Record of one line slot (slots in layout order [model][it][iy][id][kind]; an empty slot has no record), in 8-byte words:
  *     head | ysec[yw] | run[nrun] | xs[nx]     head = yw; n = lens[slot], nrun = aux[slot] & 0xffff, nx = aux[slot] >> 16
- *     ysec = I_0 | I_1 - I_0 | width bytes w_b of the ceil(n/32) blocks, zero-padded to 8 | payload, zero-padded to 8
- *       I_k = bit pattern of y_k; block b holds R_k = I_k - 2 I_(k-1) + I_(k-2) for k = 32 b .. 32 b + 31 (R_0 = R_1 = 0
- *       are place-holders) as little-endian two's-complement integers of w_b bytes each (w_b = 0: all zero, 8: raw);
+ *     ysec = I_0 | I_1 - I_0 | control bytes c_b of the ceil(n/8) blocks, zero-padded to 8 | payload, zero-padded to 8
+ *       I_k = bit pattern of y_k; R2_k = I_k - 2 I_(k-1) + I_(k-2) for k >= 2 and R2_0 = R2_1 = 0 (place-holders: the
+ *       first two ordinates are the raw words in front); R3_k = R2_k - R2_(k-1).  Block b covers k = 8 b .. 8 b + 7
+ *       (cnt = 8, or what is left of the line) and holds R2 (c_b bit 5 clear) or R3 (bit 5 set), whichever is narrower,
+ *       as two's-complement integers of w = c_b & 31 four-bit units (0: all zero ... 16: raw; bits 6-7 zero): first
+ *       cnt x (w >> 1) bytes — the low w >> 1 bytes of residual j, little-endian, at byte j (w >> 1) — then, for odd w,
+ *       ceil(cnt / 2) bytes holding the top four bits of residuals 2 i (low half) and 2 i + 1 (high half) in byte i.
+ *       Decoding: R2_k = residual, or R2_(k-1) + residual; D_k = D_(k-1) + R2_k with D_1 = I_1 - I_0; I_k = I_(k-1) + D_k.
  *       n = 1: I_0 only
  *     run (64-bit integer) = pos | src << 16 | kind << 32; it covers points pos .. (next run's pos, or n) - 1:
  *       kind 0  x[pos + j] = a[src + j] + y[pos + j]     (a: the model's savings grid, dcegm_get_grid; one IEEE add)
@@ -300,7 +305,7 @@ int  dcegm_pack_lines_noalloc(int device_ordinal, const double* lines_dev, const
  * batch's bytes.  Decoders need no special case.  DCEGM_COMPACT_ALIAS=0 (environment) switches the detection off.
  * dcegm_solve_*_compact is dcegm_solve_*_packed with
  * this delivery format (same chunked pipeline; `words` from dcegm_host_alloc makes the copies asynchronous);
- * cap_words = nslots * (2 * cap + cap / 256 + 4) always fits (a C3 batch needs 0.49 words per point).  dcegm_fetch_compact encodes models [first, first + count) of the
+ * cap_words = nslots * (2 * cap + cap / 64 + 8) always fits (a C3 batch needs 0.24 words per point).  dcegm_fetch_compact encodes models [first, first + count) of the
  * resident solution (words == NULL: sizes only).  dcegm_expand_compact rebuilds the densely packed points of
  * dcegm_fetch_packed (bit-identical: tests/test_gpu_compact.py) on `nthreads` host threads, for the batch of the
  * handle's last solve; woffsets / lens / aux point at the first slot of model `first`, woffsets values are relative

@@ -201,7 +201,7 @@ function solve_batch_compact(ps::Vector{Param}; model = :f)
     nstate = model == :g ? l0.ny : 1
     nslot = length(ps) * l0.nT * nstate * 4
     cap = 8 * cld(l0.na + l0.na ÷ 10 + 2 * max(l0.na ÷ 16, 32) + 2, 8)
-    words = Vector{Float64}(undef, nslot * (2 * cap + cap ÷ 256 + 4)); woff = Vector{Int64}(undef, nslot + 1)
+    words = Vector{Float64}(undef, nslot * (2 * cap + cap ÷ 64 + 8)); woff = Vector{Int64}(undef, nslot + 1)
     lens = Vector{Int32}(undef, nslot); aux = Vector{Int32}(undef, nslot); nw = Ref{Int64}(0)
     f = model == :g ? :dcegm_solve_g_compact : :dcegm_solve_f_compact
     check(ccall((f, LIB), Cint, (Ptr{Cvoid}, Ptr{CParam}, Cint, Cuint, Ptr{Float64}, Csize_t, Ptr{Int64}, Ptr{Int32}, Ptr{Int32}, Ref{Int64}),

@@ -58,7 +58,8 @@ def test_run_kinds_and_rejection():
     rc, ac, rv, av = encode_reference(Lc, Lv, grid)
     assert (ac & 0xFFFF, ac >> 16) == (3, 1) and (av & 0xFFFF, av >> 16) == (3, 1)
     ywc, ywv = int(rc[:1].view(np.uint64)[0]), int(rv[:1].view(np.uint64)[0])  # head word: size of the ordinate section
-    assert ywc == 2 + 1 + 4 and ywv == 2 + 1 + 4  # I_0, I_1 - I_0, one word of width bytes, one block of 4 x 8 bytes
+    # I_0, I_1 - I_0, one word of control bytes, one block of 4 residuals (at most 8 bytes each)
+    assert 2 + 1 < ywc <= 2 + 1 + 4 and 2 + 1 < ywv <= 2 + 1 + 4
     runs_c = rc[1 + ywc:1 + ywc + 3].view(np.uint64)
     assert [(int(v & 0xFFFF), int(v >> 16 & 0xFFFF), int(v >> 32)) for v in runs_c] == [(0, 0, KIND_GRID), (2, 0, KIND_EXPLICIT), (3, 3, KIND_GRID)]
     runs_v = rv[1 + ywv:1 + ywv + 3].view(np.uint64)
@@ -74,23 +75,25 @@ def test_run_kinds_and_rejection():
     bad = rc.copy()
     bad[r0:r0 + 1] = np.array([1 | (0 << 16) | (KIND_GRID << 32)], np.uint64).view(np.float64)
     assert decode(grid, bad, 4, ac, rv, 4, av)[0] == _abi.E_INVALID
-    # an ordinate section that claims more words than the line can need, a block width above 8
+    # an ordinate section that claims more words than the line can need, a residual width above 16 four-bit units
     bad = rc.copy()
     bad[0:1] = np.array([1000], np.uint64).view(np.float64)
     assert decode(grid, bad, 4, ac, rv, 4, av)[0] == _abi.E_INVALID
     bad = rc.copy()
     wb = bad[3:4].view(np.uint8)
-    wb[0] = 9
+    wb[0] = 17
+    assert decode(grid, bad, 4, ac, rv, 4, av)[0] == _abi.E_INVALID
+    wb[0] = 0x40 | 4  # unknown control bit
     assert decode(grid, bad, 4, ac, rv, 4, av)[0] == _abi.E_INVALID
     # empty slots
     assert decode(grid, np.zeros(1), 0, 0, np.zeros(1), 0, 0)[0] == 0
 
 
 def test_ordinate_packing_roundtrip_on_hostile_values():
-    """second differences of the bit patterns wrap modulo 2^64: any doubles survive, whatever their order of magnitude"""
+    """differences of the bit patterns wrap modulo 2^64: any doubles survive, whatever their order of magnitude"""
     rng = np.random.default_rng(5)
     grid = np.array([0.0, 1.0])
-    for n in (1, 2, 3, 33, 34, 35, 70, 300):
+    for n in (1, 2, 3, 4, 7, 8, 9, 10, 15, 16, 17, 33, 34, 35, 70, 300):
         y = rng.standard_normal(n) * 10.0 ** rng.integers(-300, 300, n)
         y[rng.integers(0, n, 2)] = [np.inf, -0.0]
         if n > 5:
@@ -103,7 +106,24 @@ def test_ordinate_packing_roundtrip_on_hostile_values():
     smooth = np.stack([np.linspace(1, 2, 500) + 100, np.sqrt(np.linspace(1, 2, 500))], axis=1)
     rc, ac, _, _ = encode_reference(smooth, smooth[:0], grid)
     yw = int(rc[:1].view(np.uint64)[0])
-    assert yw <= 0.65 * 500  # smooth ordinates: 5 bytes per value instead of 8
+    assert yw <= 0.5 * 500  # smooth ordinates: under 4 bytes per value instead of 8
+    # every residual width 0 .. 16 and both difference orders occur and decode: y_k built from chosen residuals
+    for order3 in (False, True):
+        for w in range(0, 17):
+            n = 29
+            I = [0x3FF0000000000000, 0x3FF0000000000000 + 12345]
+            d1, d2 = I[1] - I[0], 0
+            for k in range(2, n):
+                mag = 0 if w == 0 else (1 << (4 * w - 2)) + k  # needs exactly w four-bit units with its sign
+                r = -mag if k & 1 else mag
+                d2 = d2 + r if order3 else r
+                d1 += d2
+                I.append((I[-1] + d1) & ((1 << 64) - 1))
+            y = np.array(I, np.uint64).view(np.float64)
+            L = np.stack([np.arange(n) * 3.0 + 50.0, y], axis=1)
+            rc, ac, _, _ = encode_reference(L, L[:0], grid)
+            code, xc, _ = decode(grid, rc, n, ac, np.zeros(1), 0, 0)
+            assert code == 0 and xc.tobytes() == L.tobytes(), (order3, w)
 
 
 def test_negative_zero_and_nan_abscissae_survive():
