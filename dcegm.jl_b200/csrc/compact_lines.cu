@@ -144,16 +144,24 @@ __device__ LineSizes encode_line(const double2* __restrict__ L, int n, bool valu
     unsigned long long ym1 = 0, ym2 = 0;  // bit patterns of the two ordinates before this step
     long long r2m1 = 0;                   // second difference of the ordinate before this step
     int ref_delta = 0;                    // count pass, value lines: policy index minus own index at the end of the last step
+    // the loads of the next step are issued before this step's work (one warp has nothing else to hide them behind)
+    double2 pt_next = lane < n ? L[lane] : make_double2(0.0, 0.0);
+    unsigned stash_next = (WRITE && lane < n) ? codes[lane] : 0u;
     for (int k0 = 0; k0 < n; k0 += 32) {
         const int k = k0 + lane;
         const bool in = k < n;
-        double2 pt = make_double2(0.0, 0.0);
+        const double2 pt = pt_next;
         unsigned code = kNoCode;
-        unsigned stash = 0;  // the count pass's word of this point: abscissa code | control byte of its block << 24
+        const unsigned stash = stash_next;  // the count pass's word of this point: abscissa code | control byte of its block << 24
+        if (k + 32 < n) {
+            pt_next = L[k + 32];
+            if (WRITE) stash_next = codes[k + 32];
+        } else {
+            pt_next = make_double2(0.0, 0.0);
+            stash_next = 0u;
+        }
         if (in) {
-            pt = L[k];
             if (WRITE) {
-                stash = codes[k];
                 code = force_explicit ? (kKindExplicit << 16) : (stash & 0x3ffffu);
             } else {
                 code = classify(pt, value_line, cx.a, cx.na, cx.a0, cx.inv_da, cx.Lc, cx.nc, cx.xs_c, k + ref_delta);
@@ -253,18 +261,27 @@ __device__ LineSizes encode_line(const double2* __restrict__ L, int n, bool valu
     return z;
 }
 
-// all n points of A and R bit-identical? (one warp; 32 points per step, leaves at the first difference)
+// all n points of A and R bit-identical? (one warp; four 32-point steps in flight per vote, leaves at the first
+// vote that saw a difference)
 __device__ __forceinline__ bool same_line(const double2* __restrict__ A, const double2* __restrict__ R, int n) {
     const int lane = threadIdx.x & 31;
     const ulonglong2* a = reinterpret_cast<const ulonglong2*>(A);
     const ulonglong2* r = reinterpret_cast<const ulonglong2*>(R);
-    for (int k0 = 0; k0 < n; k0 += 32) {
-        const int k = k0 + lane;
+    for (int k0 = 0; k0 < n; k0 += 128) {
         bool ne = false;
-        if (k < n) {
-            const ulonglong2 u = a[k], v = r[k];
-            ne = u.x != v.x || u.y != v.y;
+        ulonglong2 u[4], v[4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const int k = k0 + 32 * q + lane;
+            if (k < n) {
+                u[q] = a[k];
+                v[q] = r[k];
+            } else {
+                u[q] = v[q] = make_ulonglong2(0ULL, 0ULL);
+            }
         }
+#pragma unroll
+        for (int q = 0; q < 4; q++) ne |= u[q].x != v[q].x || u[q].y != v[q].y;
         if (__any_sync(0xffffffffu, ne)) return false;
     }
     return true;
