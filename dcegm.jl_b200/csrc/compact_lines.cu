@@ -106,6 +106,7 @@ struct ClassifyCtx {
     const double2* Lc;
     int nc;
     const double* xs_c;  // shared-memory copy of the policy line's abscissae or null
+    double* stage;       // count pass over the policy line: where that copy is written (same memory), or null
 };
 
 // four-bit units of the shortest two's-complement form of r (0 for r == 0, at most 16)
@@ -161,6 +162,7 @@ __device__ LineSizes encode_line(const double2* __restrict__ L, int n, bool valu
             stash_next = 0u;
         }
         if (in) {
+            if (!WRITE && !value_line && cx.stage) cx.stage[k] = pt.x;  // read by the value line's pass that follows
             if (WRITE) {
                 code = force_explicit ? (kKindExplicit << 16) : (stash & 0x3ffffu);
             } else {
@@ -340,12 +342,9 @@ __global__ void __launch_bounds__(kCT) compact_count_kernel(DeviceBatch B, size_
     cx.Lc = B.lines + sc * (size_t)cap;
     cx.nc = nc;
     cx.xs_c = nullptr;
+    cx.stage = nullptr;
     const double2* Lv = B.lines + sv * (size_t)cap;
-    if (nc <= kStageCap && nv > 0) {
-        for (int k = lane; k < nc; k += 32) s_xc[wid][k] = cx.Lc[k].x;
-        cx.xs_c = s_xc[wid];
-        __syncwarp();
-    }
+    if (nc <= kStageCap && nv > 0) cx.xs_c = cx.stage = s_xc[wid];  // filled while the policy line is encoded
     for (int which = 0; which < 2; which++) {
         const int n = which ? nv : nc;
         const size_t s = (which ? sv : sc) - 2 * first_pair;
@@ -364,6 +363,7 @@ __global__ void __launch_bounds__(kCT) compact_count_kernel(DeviceBatch B, size_
                 lens_host[s] = n;
             }
         }
+        __syncwarp();  // the staged abscissae are complete before the value line looks them up
     }
 }
 
@@ -381,7 +381,7 @@ __global__ void __launch_bounds__(kCT) compact_write_kernel(DeviceBatch B, size_
     nc = nc < cap ? nc : cap;
     nv = nv < cap ? nv : cap;
     if (yws[sc - 2 * first_pair] == kAliasMark) return;  // no record of its own (compact_count_kernel)
-    ClassifyCtx cx{};
+    ClassifyCtx cx{};  // the write pass classifies nothing
     const double2* Lc = B.lines + sc * (size_t)cap;
     const double2* Lv = B.lines + sv * (size_t)cap;
     for (int which = 0; which < 2; which++) {

@@ -1,6 +1,6 @@
 """Timeline of one end-to-end C3 call (dcegm_solve_f_compact, host Param array in -> compact lines in pinned host
 memory): the library's DCEGM_TRACE host timestamps of the last of several calls, plus wall time of each call.
-usage: e2e_trace.py [nmodels]"""
+usage: e2e_trace.py [nmodels] [packed]     packed: dcegm_solve_f_packed (every point as an (x, y) pair) instead"""
 import ctypes as C
 import os
 import sys
@@ -33,11 +33,19 @@ with Solver(0) as s:
     cap_words = int(nw.value * 1.05) + 4096
     pinned = C.c_void_p()
     assert lib.dcegm_host_alloc(C.byref(pinned), cap_words * 8) == 0
+    packed = len(sys.argv) > 2 and sys.argv[2] == "packed"
+    if packed:
+        npts_total = int(lens.astype(np.int64).sum())
+        lib.dcegm_host_free(pinned)
+        assert lib.dcegm_host_alloc(C.byref(pinned), (npts_total + 256) * 16) == 0
     for rep in range(6):
         if rep == 5:
             os.environ["DCEGM_TRACE"] = "1"
         t0 = time.perf_counter()
-        rc = lib.dcegm_solve_f_compact(h, arr, n, 0, C.cast(pinned, C.POINTER(C.c_double)), cap_words, *args)
+        if packed:
+            rc = lib.dcegm_solve_f_packed(h, arr, n, 0, C.cast(pinned, C.POINTER(C.c_double)), npts_total + 256, args[0], C.byref(nw))
+        else:
+            rc = lib.dcegm_solve_f_compact(h, arr, n, 0, C.cast(pinned, C.POINTER(C.c_double)), cap_words, *args)
         dt = time.perf_counter() - t0
         assert rc == 0, lib.dcegm_last_error(h)
         t = s.timing()
