@@ -407,10 +407,30 @@ __device__ __forceinline__ double iup(double u, const DevModel& p) {  // utils.j
 // ---------------------------------------------------------------------------------------------
 // block helpers (kThreads threads)
 // ---------------------------------------------------------------------------------------------
+// The cooperative routines below and worker_envelope (envelope.cuh) run on a THREAD GROUP of NT threads (their template
+// parameter): the whole CTA by default.  A .cu file that defines DC_GROUPED 1 before including this header runs them on
+// groups of NT consecutive threads of a wider CTA (NT a multiple of 32, at most 15 groups), every group on its own named
+// barrier, so that several groups work through independent envelopes at their own pace (solver_g.cu: one income state
+// per group).
+#ifndef DC_GROUPED
+#define DC_GROUPED 0
+#endif
+template <int NT>
+__device__ __forceinline__ int dc_gtid() {
+    return DC_GROUPED ? (int)(threadIdx.x % NT) : (int)threadIdx.x;
+}
+template <int NT>
+__device__ __forceinline__ void dc_gsync() {
+#if DC_GROUPED
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + (int)(threadIdx.x / NT)), "n"(NT) : "memory");
+#else
+    __syncthreads();
+#endif
+}
 // exclusive prefix sum of data[0..n) in place; returns the total.  red: (NT / 32)+1 ints of scratch.
 template <int NT = kThreads>
 __device__ inline int block_scan_excl(int* data, int n, int* red) {
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int tid = dc_gtid<NT>(), lane = tid & 31, wid = tid >> 5;
     const int per = (n + NT - 1) / NT;
     const int b = tid * per;
     int local = 0;
@@ -426,7 +446,7 @@ __device__ inline int block_scan_excl(int* data, int n, int* red) {
         if (lane >= o) inc += t;
     }
     if (lane == 31) red[wid] = inc;
-    __syncthreads();
+    dc_gsync<NT>();
     if (wid == 0) {
         int v = lane < (NT / 32) ? red[lane] : 0;
         int vi = v;
@@ -438,7 +458,7 @@ __device__ inline int block_scan_excl(int* data, int n, int* red) {
         if (lane < (NT / 32)) red[lane] = vi - v;
         if (lane == (NT / 32) - 1) red[(NT / 32)] = vi;
     }
-    __syncthreads();
+    dc_gsync<NT>();
     int run = red[wid] + inc - local;
     const int total = red[(NT / 32)];
 #pragma unroll (NT > 256 ? 4 : 1)
@@ -450,47 +470,47 @@ __device__ inline int block_scan_excl(int* data, int n, int* red) {
             run += v;
         }
     }
-    __syncthreads();
+    dc_gsync<NT>();
     return total;
 }
 
 template <int NT = kThreads>
 __device__ inline double block_min(double v, double* red) {
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int lane = dc_gtid<NT>() & 31, wid = dc_gtid<NT>() >> 5;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
     if (lane == 0) red[wid] = v;
-    __syncthreads();
+    dc_gsync<NT>();
     double r = red[0];
 #pragma unroll
     for (int w = 1; w < (NT / 32); w++) r = fmin(r, red[w]);
-    __syncthreads();
+    dc_gsync<NT>();
     return r;
 }
 template <int NT = kThreads>
 __device__ inline int block_sum(int v, int* red) {
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int lane = dc_gtid<NT>() & 31, wid = dc_gtid<NT>() >> 5;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     if (lane == 0) red[wid] = v;
-    __syncthreads();
+    dc_gsync<NT>();
     int r = 0;
 #pragma unroll
     for (int w = 0; w < (NT / 32); w++) r += red[w];
-    __syncthreads();
+    dc_gsync<NT>();
     return r;
 }
 template <int NT = kThreads>
 __device__ inline int block_min_int(int v, int* red) {
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int lane = dc_gtid<NT>() & 31, wid = dc_gtid<NT>() >> 5;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
     if (lane == 0) red[wid] = v;
-    __syncthreads();
+    dc_gsync<NT>();
     int r = red[0];
 #pragma unroll
     for (int w = 1; w < (NT / 32); w++) r = min(r, red[w]);
-    __syncthreads();
+    dc_gsync<NT>();
     return r;
 }
 

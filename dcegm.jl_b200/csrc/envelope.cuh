@@ -232,7 +232,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                                        double* Vx, double* Vy, int* nV, double* Cx, double* Cy, int* nC,
                                        dcegm_env_meta* meta_out, double2* isects_out, uint32_t* removed_out,
                                        int rem_words, bool first_period = false) {
-    const int tid = threadIdx.x;
+    const int tid = dc_gtid<NT>();  // index inside the thread group (the CTA unless DC_GROUPED)
     unsigned status = 0;
 
     // ---- bend-back guard (dc_algo.jl:394-418) ------------------------------------------------
@@ -266,7 +266,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         S.cnt()[1] = 0;
         S.cnt()[2] = 0;
     }
-    __syncthreads();
+    dc_gsync<NT>();
 
     // ---- splitLine: direction changes (envelope.jl:84-110) -----------------------------------
     DC_ENV_UNROLL
@@ -276,7 +276,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         S.scan()[k] = isb;
         S.fknot()[k] = (unsigned char)isb;
     }
-    __syncthreads();
+    dc_gsync<NT>();
     const int nb = block_scan_excl<NT>(S.scan(), n, S.red());
     int nseg = nb + 1;
     const bool first_rising = X[1] > X[0];
@@ -309,12 +309,12 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             S.segb()[0] = 0;
             S.segb()[nseg] = n - 1;
         }
-        __syncthreads();
+        dc_gsync<NT>();
         DC_ENV_UNROLL
         for (int s = tid; s < nseg; s += NT) S.segrise()[s] = X[S.segb()[s] + 1] > X[S.segb()[s]];
         DC_ENV_UNROLL
         for (int k = tid; k < n; k += NT) S.order()[k] = 0;
-        __syncthreads();
+        dc_gsync<NT>();
 
         DC_CLK(5);
         // ---- every point: sorted position, winning section, top Point (envelope.jl:154-164) ----
@@ -339,7 +339,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 t_hi[s] = xa > xb ? xa : xb;
                 t_own[s] = e1 - e0 + (s == 0 ? 1 : 0);
             }
-            __syncthreads();
+            dc_gsync<NT>();
             for (int gi = tid; gi * 32 + 32 <= ntile; gi += NT) {
                 double lo = CUDART_INF, hi = -CUDART_INF;
                 int own = 0;
@@ -353,7 +353,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 g_hi[gi] = hi;
                 g_own[gi] = own;
             }
-            __syncthreads();
+            dc_gsync<NT>();
         }
         DC_ENV_UNROLL
         for (int k = tid; k < n; k += NT) {
@@ -438,11 +438,11 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             S.Ty()[k] = best;
             S.fknot()[k] = knot;
         }
-        __syncthreads();
+        dc_gsync<NT>();
         DC_CLK(6);
         DC_ENV_UNROLL
         for (int k = tid; k < n; k += NT) S.order()[S.pos()[k]] = (unsigned short)k;
-        __syncthreads();
+        dc_gsync<NT>();
         // unique(xx)
         DC_ENV_UNROLL
         for (int q = tid; q < n; q += NT) {
@@ -450,7 +450,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             S.fuq()[q] = (unsigned char)uq;
             S.scan()[q] = uq;
         }
-        __syncthreads();
+        dc_gsync<NT>();
         const int nu = block_scan_excl<NT>(S.scan(), n, S.red());
         DC_ENV_UNROLL
         for (int q = tid; q < n; q += NT)
@@ -460,7 +460,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             int q = S.pos()[k];
             S.pos()[k] = (unsigned short)(S.fuq()[q] ? S.scan()[q] : S.scan()[q] - 1);  // index into the unique grid
         }
-        __syncthreads();
+        dc_gsync<NT>();
 
         DC_CLK(7);
         // ---- changes of winner (envelope.jl:173-243) ---------------------------------------------
@@ -472,7 +472,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 S.swj()[slot] = (unsigned short)j;
             }
         }
-        __syncthreads();
+        dc_gsync<NT>();
         const int nsw = S.cnt()[0];
         for (int t = tid >> 5; t < nsw; t += (NT / 32)) {  // warp per change of winner
             const int j = S.swj()[t];
@@ -492,7 +492,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 S.cntI()[j] = (unsigned char)c;
             }
         }
-        __syncthreads();
+        dc_gsync<NT>();
         DC_CLK(8);
         nis = S.cnt()[1];
         if (nis > S.isec_cap) {
@@ -515,7 +515,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             int reg = (j == 0) || S.fknot()[k] || (j == nu - 1);
             S.scan()[j] = (j == 0 ? 0 : (int)S.cntI()[j]) + reg;
         }
-        __syncthreads();
+        dc_gsync<NT>();
         ne = block_scan_excl<NT>(S.scan(), nu, S.red());
         const int room = S.cap - 1;
         if (ne > room) status |= DCEGM_ST_LINE_OVERFLOW;
@@ -548,7 +548,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             for (int t = 0; t < nis && !kept; t++) kept = (S.isl2x()[t] == X[k]) && (S.isl2y()[t] == V[k]);
             S.frem()[k] = kept ? 0 : 1;
         }
-        __syncthreads();
+        dc_gsync<NT>();
     }
     DC_CLK(9);
     {
@@ -611,7 +611,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         // deleteat!(cout, rmidx)  (dc_algo.jl:482)
         DC_ENV_UNROLL
         for (int k = tid; k < n; k += NT) S.scan()[k] = S.frem()[k] ? 0 : 1;
-        __syncthreads();
+        dc_gsync<NT>();
         // compact the two insertion lists (push! order)
         if (tid == 0) {
             int nl = 0, nr = 0;
@@ -637,7 +637,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 Cx[1 + S.scan()[k]] = X[k];
                 Cy[1 + S.scan()[k]] = Cc[k];
             }
-        __syncthreads();
+        dc_gsync<NT>();
         const int nl = S.cnt()[0], nr = S.cnt()[1];
         // the reference's loop runs over insert_left and indexes insert_right with it (dc_algo.jl:486-492): a shorter
         // insert_right is a BoundsError, a longer one is silently ignored
@@ -695,14 +695,14 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 S.Dx()[at + 1] = S.insRx()[i];
                 S.Dv()[at + 1] = S.insRy()[i];
             }
-            __syncthreads();
+            dc_gsync<NT>();
             ncur += 2 * nl;
             DC_ENV_UNROLL
             for (int k = tid; k < ncur; k += NT) {
                 Cx[1 + k] = S.Dx()[k];
                 Cy[1 + k] = S.Dv()[k];
             }
-            __syncthreads();
+            dc_gsync<NT>();
         }
         for (int i = 0; i < nl && !merged; i++) {
             const double lx = S.insLx()[i];
@@ -730,12 +730,12 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                     vx = Cx[1 + k];
                     vy = Cy[1 + k];
                 }
-                __syncthreads();
+                dc_gsync<NT>();
                 if (k >= j) {
                     Cx[1 + k + 2] = vx;
                     Cy[1 + k + 2] = vy;
                 }
-                __syncthreads();
+                dc_gsync<NT>();
             }
             if (tid == 0) {
                 Cx[1 + j] = lx;
@@ -744,7 +744,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 Cy[1 + j + 1] = S.insRy()[i];
             }
             ncur += 2;
-            __syncthreads();
+            dc_gsync<NT>();
         }
     } else {
         DC_ENV_UNROLL
@@ -763,7 +763,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         Cx[0] = a0;
         Cy[0] = 0.0;
     }
-    __syncthreads();
+    dc_gsync<NT>();
     const int lenV = ne + 1, lenC = ncur + 1;
     // sortx!(c): stable sort on x.  The repaired policy is already ascending except in degenerate
     // cases; detect, and only then rank-sort through the (now free) D arrays.
@@ -778,17 +778,17 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         // run boundaries in segb (room for cap + 1 entries in this variant), scan as temporary.
         DC_ENV_UNROLL
         for (int k = tid; k < lenC; k += NT) S.scan()[k] = (k == 0) || (Cx[k] < Cx[k - 1]);
-        __syncthreads();
+        dc_gsync<NT>();
         DC_ENV_UNROLL
         for (int k = tid; k < lenC; k += NT) S.fuq()[k] = (unsigned char)S.scan()[k];
-        __syncthreads();
+        dc_gsync<NT>();
         int nr = block_scan_excl<NT>(S.scan(), lenC, S.red());
         int* rb = S.segb();
         DC_ENV_UNROLL
         for (int k = tid; k < lenC; k += NT)
             if (S.fuq()[k]) rb[S.scan()[k]] = k;
         if (tid == 0) rb[nr] = lenC;
-        __syncthreads();
+        dc_gsync<NT>();
         double *sx = Cx, *sy = Cy, *dx = S.Dx(), *dy = S.Dv();
         while (nr > 1) {
             DC_ENV_UNROLL
@@ -832,11 +832,11 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             const int nr2 = (nr + 1) >> 1;
             DC_ENV_UNROLL
             for (int i = tid; i < nr2; i += NT) S.scan()[i] = rb[2 * i];
-            __syncthreads();
+            dc_gsync<NT>();
             DC_ENV_UNROLL
             for (int i = tid; i < nr2; i += NT) rb[i] = S.scan()[i];
             if (tid == 0) rb[nr2] = lenC;
-            __syncthreads();
+            dc_gsync<NT>();
             nr = nr2;
             double* t = sx; sx = dx; dx = t;
             t = sy; sy = dy; dy = t;
@@ -847,7 +847,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                 Cx[k] = sx[k];
                 Cy[k] = sy[k];
             }
-            __syncthreads();
+            dc_gsync<NT>();
         }
     } else if (bad) {
         DC_ENV_UNROLL
@@ -861,13 +861,13 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
             S.Dx()[r] = xk;
             S.Dv()[r] = Cy[k];
         }
-        __syncthreads();
+        dc_gsync<NT>();
         DC_ENV_UNROLL
         for (int k = tid; k < lenC; k += NT) {
             Cx[k] = S.Dx()[k];
             Cy[k] = S.Dv()[k];
         }
-        __syncthreads();
+        dc_gsync<NT>();
     }
     // status: knot vectors the previous period's interpolate() would reject (knot_pair_flag), non-finite entries
     int flag = 0;
@@ -882,7 +882,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         if (!isfinite(Vx[k]) || !isfinite(Vy[k])) flag |= DCEGM_ST_NONFINITE;
     }
     if (flag || status) atomicOr(&S.cnt()[2], flag | (int)status);
-    __syncthreads();
+    dc_gsync<NT>();
     if (tid == 0) {
         *nV = lenV;
         *nC = lenC;
@@ -891,7 +891,7 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
         meta_out->n_removed = nrem;
         meta_out->n_prepended = npre;
     }
-    __syncthreads();
+    dc_gsync<NT>();
 }
 
 }  // namespace dcegm

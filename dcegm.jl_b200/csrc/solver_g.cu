@@ -7,37 +7,51 @@
 // written to HBM once.  Per period:
 //   A. thread per (current state iy, future choice iid, grid point ia): loop over the future state
 //      jy, accumulate pr*vfun and pr*u'(c') in index order (dc_algo.jl:142-157)
-//   B. thread per (iy, current choice id, ia): ccp / logsum on the integrated values, Euler
+//   B. thread per (current choice id, ia) of one state: ccp / logsum on the integrated values, Euler
 //      inversion, value (dc_algo.jl:159-182)
-//   C. per iy: worker envelope + policy repair (envelope.cuh), credit-constraint point, store.
+//   C. worker envelope + policy repair (envelope.cuh), credit-constraint point, store.
+// B and C run per income state on THREAD GROUPS (kGroups groups of kGroupThreads threads, each with its own envelope
+// scratch and named barrier): the envelopes of a period — short lines, many barriers, stretches where one warp works —
+// proceed side by side instead of one after the other on the whole CTA.
 #include <math_constants.h>
 
 #define DC_SEG_INTERP_ATTR static __device__ __noinline__  // envelope.cuh
+#define DC_GROUPED 1  // block_* and worker_envelope run on groups of NT threads (device_common.cuh)
 #include "device_common.cuh"
 #include "envelope.cuh"
 
 namespace dcegm {
 
-// shared-memory map: ny x 7 double[cap] line arrays | vmat,cmat double[ny][2][na] each | D arrays of
-// every state 3 x double[ny][na+koff] | envelope scratch
+#ifndef DCEGM_G_GROUPS
+#define DCEGM_G_GROUPS 2
+#endif
+constexpr int kGroups = DCEGM_G_GROUPS;            // income states in flight through phases B and C
+constexpr int kGroupThreads = kThreads / kGroups;  // 128
+static_assert(kGroupThreads % 32 == 0 && kGroups * kGroupThreads == kThreads && kGroups <= 8, "thread groups");
+
+// shared-memory map: ny x 7 double[cap] line arrays | vmat,cmat double[ny][2][na] each | per-state words |
+// kGroups envelope scratch regions (the dirty worker line of a state is written straight into its group's region)
 struct GPlan {
-    int cap8, na8, d8, ny;
-    int o_mat, o_d, o_meta;
-    EnvScratch env;
+    int cap8, na8, ny;
+    int o_mat, o_meta, env_stride;
+    EnvScratch env;  // region of group 0
     __host__ __device__ GPlan(int cap, int isec_cap, int na, int ny_) {
         ny = ny_;
         cap8 = EnvScratch::align16(cap * 8);
         na8 = EnvScratch::align16(na * 8);
-        const int koff = na / 10 - 1 > 0 ? na / 10 - 1 : 0;
-        d8 = EnvScratch::align16((na + koff) * 8);
         o_mat = ny * 7 * cap8;
-        o_d = o_mat + ny * 4 * na8;
-        o_meta = o_d + ny * 3 * d8;
+        o_meta = o_mat + ny * 4 * na8;
         env.off = o_meta + EnvScratch::align16(ny * 5 * 8) + EnvScratch::align16(ny * 3 * 4);
         env.cap = cap;
         env.isec_cap = isec_cap;
+        env_stride = EnvScratch::align16(env.bytes());
     }
-    __host__ __device__ size_t bytes() const { return (size_t)env.off + env.bytes(); }
+    __host__ __device__ size_t bytes() const { return (size_t)env.off + (size_t)kGroups * env_stride; }
+    __device__ __forceinline__ EnvScratch scratch(int g) const {
+        EnvScratch S = env;
+        S.off += g * env_stride;
+        return S;
+    }
     // line arrays of income state iy: 0 wc_x, 1 wc_y, 2 wv_x, 3 wv_y, 4 r_x, 5 rc_y, 6 rv_y
     __device__ __forceinline__ double* line(int iy, int a) const {
         return reinterpret_cast<double*>(dc_smem + (iy * 7 + a) * cap8);
@@ -45,9 +59,6 @@ struct GPlan {
     // 0 vmat[iid=0], 1 vmat[iid=1], 2 cmat[0], 3 cmat[1]
     __device__ __forceinline__ double* mat(int iy, int a) const {
         return reinterpret_cast<double*>(dc_smem + o_mat + (iy * 4 + a) * na8);
-    }
-    __device__ __forceinline__ double* dirty(int iy, int a) const {
-        return reinterpret_cast<double*>(dc_smem + o_d + (iy * 3 + a) * d8);
     }
     // per state: vbound worker, vbound retiree, ev0 worker, ev0 retiree (doubles); n_wc, n_wv, n_r (ints)
     __device__ __forceinline__ double* vb(int iy) const { return reinterpret_cast<double*>(dc_smem + o_meta) + iy * 5; }
@@ -58,14 +69,15 @@ struct GPlan {
 
 size_t solver_g_smem_bytes(int cap, int isec_cap, int na, int ny) { return GPlan(cap, isec_cap, na, ny).bytes(); }
 
+// stored by the nt threads t = 0 .. nt - 1 of the CTA or of one thread group
 __device__ inline void store_line_g(const DeviceBatch& B, int m, int it, int iy, int id, int kind, const double* x,
-                                    const double* y, int n) {
+                                    const double* y, int n, int t = threadIdx.x, int nt = kThreads) {
     const size_t slot = line_slot(B.lay, m, it, iy, id, kind);
-    if (threadIdx.x == 0) B.lens[slot] = n;
+    if (t == 0) B.lens[slot] = n;
     if (!B.lines) return;
     double2* dst = B.lines + slot * (size_t)B.lay.cap;
     const int nn = n < B.lay.cap ? n : B.lay.cap;
-    for (int k = threadIdx.x; k < nn; k += kThreads) dst[k] = make_double2(x[k], y[k]);
+    for (int k = t; k < nn; k += nt) dst[k] = make_double2(x[k], y[k]);
 }
 
 // Top = largest step of the fixed-trip knot search (lines hold fewer than 2*Top points; chosen at launch from cap)
@@ -75,16 +87,19 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBat
     const int tid = threadIdx.x;
     __shared__ DevModel s_p;
     __shared__ int s_status;
-    __shared__ int s_n[2];
+    __shared__ int s_n[kGroups][2];
+    __shared__ int s_sum[6];
+    const int grp = tid / kGroupThreads, gt = tid % kGroupThreads;  // thread group of phases B and C, index inside it
     if (tid == 0) {
         s_p = B.models[m];
         s_status = 0;
     }
+    if (tid < 6) s_sum[tid] = 0;
     __syncthreads();
     const DevModel& p = s_p;
     const int na = p.na, ny = p.ny, nT = p.nT;
     const GPlan P(B.lay.cap, B.lay.isec_cap, na, ny);
-    const EnvScratch S = P.env;
+    const EnvScratch S = P.scratch(grp);  // this thread group's envelope scratch
     const double* __restrict__ avec = B.grids + (size_t)p.grid * na;
     const double* __restrict__ wgt = B.wgt + (size_t)m * ny * ny;               // [iy][jy]
     const double* __restrict__ offm = B.off + (size_t)m * (nT - 1) * 2 * ny;    // [t][iid][jy]
@@ -98,6 +113,7 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBat
     {
         const int t = nT - 1;
         const int nv = p.nu > 0 ? na : 2;
+        const EnvScratch S0 = P.scratch(0);  // staging of the retiree's bequest line (whole CTA)
         for (int iy = 0; iy < ny; iy++) {
             if (tid == 0) {
                 double* wcx = P.line(iy, 0); double* wcy = P.line(iy, 1);
@@ -118,8 +134,8 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBat
                     const double b = p.nu * u_plain(avec[k] + p.bbar, p);
                     P.line(iy, 2)[k] = avec[k];
                     P.line(iy, 3)[k] = (b - p.alpha) - 0.0;
-                    S.Dx()[k] = avec[k];
-                    S.Dv()[k] = (b - 0.0) - 10.0;
+                    S0.Dx()[k] = avec[k];
+                    S0.Dv()[k] = (b - 0.0) - 10.0;
                 }
             }
             __syncthreads();
@@ -127,7 +143,7 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBat
             store_line_g(B, m, t, iy, 1, DCEGM_KIND_C, P.line(iy, 4), P.line(iy, 5), 2);
             store_line_g(B, m, t, iy, 0, DCEGM_KIND_V, P.line(iy, 2), P.line(iy, 3), nv);
             if (p.nu > 0)
-                store_line_g(B, m, t, iy, 1, DCEGM_KIND_V, S.Dx(), S.Dv(), na);
+                store_line_g(B, m, t, iy, 1, DCEGM_KIND_V, S0.Dx(), S0.Dv(), na);
             else
                 store_line_g(B, m, t, iy, 1, DCEGM_KIND_V, P.line(iy, 4), P.line(iy, 6), 2);
             if (tid == 0) {
@@ -191,70 +207,67 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBat
         }
         __syncthreads();
 
-        // ---- B. current choice: ccp / logsum on integrated values, Euler inversion (dc_algo.jl:159-182)
-        for (int item = tid; item < ny * 2 * na; item += kThreads) {
-            const int ia = item % na;
-            const int id = (item / na) & 1;
-            const int iy = item / (2 * na);
-            const double v1 = P.mat(iy, 0)[ia], v2 = P.mat(iy, 1)[ia];
-            const double cm1 = P.mat(iy, 2)[ia], cm2 = P.mat(iy, 3)[ia];
-            double pw = 0.0, ev = v2;
-            if (id == 0) {
-                const bool w_hi = v1 > v2;
-                const double mx = w_hi ? v1 : v2;
-                const double d = ((w_hi ? v2 : v1) - mx) / p.lambda;
-                const double e = dc_exp(d);
-                const double e1 = w_hi ? 1.0 : e, e2 = w_hi ? e : 1.0;
-                const double s = e1 + e2;
-                pw = e1 / s;
-                ev = mx + p.lambda * dc_log(s);
+        // ---- B + C, one income state per thread group -------------------------------------------------
+        for (int iy0 = 0; iy0 < ny; iy0 += kGroups) {
+            const int iy = iy0 + grp;
+            if (iy >= ny) continue;  // uniform over the group: its named barrier is not used in this round
+            // ---- B. current choice: ccp / logsum on integrated values, Euler inversion (dc_algo.jl:159-182)
+            for (int item = gt; item < 2 * na; item += kGroupThreads) {
+                const int ia = item % na;
+                const int id = item / na;
+                const double v1 = P.mat(iy, 0)[ia], v2 = P.mat(iy, 1)[ia];
+                const double cm1 = P.mat(iy, 2)[ia], cm2 = P.mat(iy, 3)[ia];
+                double pw = 0.0, ev = v2;
+                if (id == 0) {
+                    const bool w_hi = v1 > v2;
+                    const double mx = w_hi ? v1 : v2;
+                    const double d = ((w_hi ? v2 : v1) - mx) / p.lambda;
+                    const double e = dc_exp(d);
+                    const double e1 = w_hi ? 1.0 : e, e2 = w_hi ? e : 1.0;
+                    const double s = e1 + e2;
+                    pw = e1 / s;
+                    ev = mx + p.lambda * dc_log(s);
+                }
+                const double mu1 = pw * cm1 + (1.0 - pw) * cm2;  // dc_algo.jl:165
+                const double rhs = scale * mu1;
+                const double c0 = iup(rhs, p);
+                const double x = avec[ia] + c0;
+                const double vy = u_work(c0, id == 0, p) + p.beta * ev;
+                if (id == 0) {  // the dirty worker line, where worker_envelope expects it
+                    S.Dx()[koff + ia] = x;
+                    S.Dv()[koff + ia] = vy;
+                    S.Dc()[koff + ia] = c0;
+                    if (ia == 0) P.vb(iy)[2] = ev;
+                } else {
+                    // the t+1 lines are dead after phase A: the retiree lines of t are built in place
+                    P.line(iy, 4)[1 + ia] = x;
+                    P.line(iy, 5)[1 + ia] = c0;
+                    P.line(iy, 6)[1 + ia] = vy;
+                    if (ia == 0) P.vb(iy)[3] = ev;
+                }
             }
-            const double mu1 = pw * cm1 + (1.0 - pw) * cm2;  // dc_algo.jl:165
-            const double rhs = scale * mu1;
-            const double c0 = iup(rhs, p);
-            const double x = avec[ia] + c0;
-            const double vy = u_work(c0, id == 0, p) + p.beta * ev;
-            if (id == 0) {
-                P.dirty(iy, 0)[koff + ia] = x;
-                P.dirty(iy, 1)[koff + ia] = vy;
-                P.dirty(iy, 2)[koff + ia] = c0;
-                if (ia == 0) P.vb(iy)[2] = ev;
-            } else {
-                // the t+1 lines are dead after phase A: the retiree lines of t are built in place
-                P.line(iy, 4)[1 + ia] = x;
-                P.line(iy, 5)[1 + ia] = c0;
-                P.line(iy, 6)[1 + ia] = vy;
-                if (ia == 0) P.vb(iy)[3] = ev;
-            }
-        }
-        __syncthreads();
+            dc_gsync<kGroupThreads>();
 
-        // ---- C. per state: envelope, credit-constraint point, checks, store ---------------------------
-        for (int iy = 0; iy < ny; iy++) {
+            // ---- C. envelope, credit-constraint point, checks, store ------------------------------------
             const size_t ss = state_slot(B.lay, m, t, iy);
             const bool first_period = t == 0;  // see solve_f_kernel
             const double ev0w = P.vb(iy)[2], ev0r = P.vb(iy)[3];
             if (B.dirty) {
                 double2* d = B.dirty + line_slot(B.lay, m, t, iy, 0, 0) * (size_t)na;
-                for (int k = tid; k < na; k += kThreads) {
-                    d[k] = make_double2(P.dirty(iy, 0)[koff + k], P.dirty(iy, 2)[koff + k]);
-                    d[(size_t)na + k] = make_double2(P.dirty(iy, 0)[koff + k], P.dirty(iy, 1)[koff + k]);
+                for (int k = gt; k < na; k += kGroupThreads) {
+                    d[k] = make_double2(S.Dx()[koff + k], S.Dc()[koff + k]);
+                    d[(size_t)na + k] = make_double2(S.Dx()[koff + k], S.Dv()[koff + k]);
                     d[(size_t)2 * na + k] = make_double2(P.line(iy, 4)[1 + k], P.line(iy, 5)[1 + k]);
                     d[(size_t)3 * na + k] = make_double2(P.line(iy, 4)[1 + k], P.line(iy, 6)[1 + k]);
                 }
+                dc_gsync<kGroupThreads>();  // read before the envelope prepends bend-back points in front
             }
-            // stage this state's dirty worker line into the envelope scratch
-            for (int k = tid; k < na; k += kThreads) {
-                S.Dx()[koff + k] = P.dirty(iy, 0)[koff + k];
-                S.Dv()[koff + k] = P.dirty(iy, 1)[koff + k];
-                S.Dc()[koff + k] = P.dirty(iy, 2)[koff + k];
-            }
-            __syncthreads();
-            worker_envelope(S, koff, na, a0, ev0w, p, P.line(iy, 2), P.line(iy, 3), &s_n[0], P.line(iy, 0),
-                            P.line(iy, 1), &s_n[1], B.meta + ss, B.isects + ss * (size_t)B.lay.isec_cap,
-                            B.removed + ss * (size_t)B.lay.rem_words, B.lay.rem_words, first_period);
-            const int n_wv = s_n[0], n_wc = s_n[1], n_r = na + 1;
-            if (tid == 0) {
+            worker_envelope<EnvScratch, kGroupThreads>(S, koff, na, a0, ev0w, p, P.line(iy, 2), P.line(iy, 3), &s_n[grp][0],
+                                                       P.line(iy, 0), P.line(iy, 1), &s_n[grp][1], B.meta + ss,
+                                                       B.isects + ss * (size_t)B.lay.isec_cap,
+                                                       B.removed + ss * (size_t)B.lay.rem_words, B.lay.rem_words, first_period);
+            const int n_wv = s_n[grp][0], n_wc = s_n[grp][1], n_r = na + 1;
+            if (gt == 0) {
                 P.line(iy, 4)[0] = a0;
                 P.line(iy, 5)[0] = 0.0;
                 P.line(iy, 6)[0] = ev0r;
@@ -264,22 +277,22 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBat
                 P.vb(iy)[0] = ev0w;
                 P.vb(iy)[1] = ev0r;
             }
-            __syncthreads();
+            dc_gsync<kGroupThreads>();
             int flag = 0;
             {
                 const double* rx = P.line(iy, 4);
-                for (int k = tid; k < n_r; k += kThreads) {
+                for (int k = gt; k < n_r; k += kGroupThreads) {
                     if (k + 1 < n_r) flag |= knot_pair_flag(rx[k], rx[k + 1], first_period);
                     if (!isfinite(rx[k]) || !isfinite(P.line(iy, 5)[k]) || !isfinite(P.line(iy, 6)[k])) flag |= DCEGM_ST_NONFINITE;
                 }
             }
             if (flag) atomicOr(&s_status, flag);
-            if (tid == 0 && S.cnt()[2]) atomicOr(&s_status, S.cnt()[2]);
-            store_line_g(B, m, t, iy, 0, DCEGM_KIND_C, P.line(iy, 0), P.line(iy, 1), n_wc);
-            store_line_g(B, m, t, iy, 0, DCEGM_KIND_V, P.line(iy, 2), P.line(iy, 3), n_wv);
-            store_line_g(B, m, t, iy, 1, DCEGM_KIND_C, P.line(iy, 4), P.line(iy, 5), n_r);
-            store_line_g(B, m, t, iy, 1, DCEGM_KIND_V, P.line(iy, 4), P.line(iy, 6), n_r);
-            if (tid == 0) {
+            if (gt == 0 && S.cnt()[2]) atomicOr(&s_status, S.cnt()[2]);
+            store_line_g(B, m, t, iy, 0, DCEGM_KIND_C, P.line(iy, 0), P.line(iy, 1), n_wc, gt, kGroupThreads);
+            store_line_g(B, m, t, iy, 0, DCEGM_KIND_V, P.line(iy, 2), P.line(iy, 3), n_wv, gt, kGroupThreads);
+            store_line_g(B, m, t, iy, 1, DCEGM_KIND_C, P.line(iy, 4), P.line(iy, 5), n_r, gt, kGroupThreads);
+            store_line_g(B, m, t, iy, 1, DCEGM_KIND_V, P.line(iy, 4), P.line(iy, 6), n_r, gt, kGroupThreads);
+            if (gt == 0) {
                 B.vbound[ss * 2 + 0] = ev0w;
                 B.vbound[ss * 2 + 1] = ev0r;
                 const dcegm_env_meta mt = B.meta[ss];
@@ -292,8 +305,28 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBat
                 sum_maxlen = sum_maxlen > ml ? sum_maxlen : ml;
                 sum_pts += n_wc + n_wv + 2 * n_r;
             }
-            __syncthreads();
+            dc_gsync<kGroupThreads>();
         }
+        __syncthreads();  // every state's lines of period t are in place before phase A of t - 1 reads them
+    }
+
+    // the group leaders' partial sums -> thread 0
+    if (gt == 0 && grp > 0) {
+        atomicAdd(&s_sum[0], sum_envp);
+        atomicAdd(&s_sum[1], sum_seg);
+        atomicAdd(&s_sum[2], sum_is);
+        atomicAdd(&s_sum[3], sum_rm);
+        atomicMax(&s_sum[4], sum_maxlen);
+        atomicAdd(&s_sum[5], (int)sum_pts);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        sum_envp += s_sum[0];
+        sum_seg += s_sum[1];
+        sum_is += s_sum[2];
+        sum_rm += s_sum[3];
+        sum_maxlen = sum_maxlen > s_sum[4] ? sum_maxlen : s_sum[4];
+        sum_pts += s_sum[5];
     }
 
     // ---- per-model summary ----------------------------------------------------------------------------
