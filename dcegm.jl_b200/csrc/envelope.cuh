@@ -43,14 +43,14 @@ template <class Mem>
 struct EnvScratchT : Mem {
     int off;  // byte offset of the region inside the scratch memory (dc_smem, or the model's global region)
     int cap, isec_cap;
-    // region layout: 5 double[cap] | 12 double[isec_cap] | redd[kWarps] | scan int[cap] | segb int[kSegCap+1]
+    // region layout: 5 double[cap] | 8 double[isec_cap] | redd[kWarps] | scan int[cap] | segb int[kSegCap+1]
     //                | 2 int[isec_cap] | red int[kWarps+1] | cnt int[8] | 5 u16[cap] | 4 u8[cap] | segrise u8[kSegCap]
     //                | 2 u8[isec_cap]
     __host__ __device__ static int align16(int b) { return (b + 15) / 16 * 16; }
     __host__ __device__ int segcap() const { return Mem::kSegCapFixed > 0 ? Mem::kSegCapFixed : cap; }
     __host__ __device__ int o_d(int j) const { return off + j * align16(cap * 8); }
     __host__ __device__ int o_i(int j) const { return o_d(5) + j * align16(isec_cap * 8); }
-    __host__ __device__ int o_redd() const { return o_i(12); }
+    __host__ __device__ int o_redd() const { return o_i(8); }
     __host__ __device__ int o_scan() const { return o_redd() + align16(Mem::kMaxWarps * 8); }
     __host__ __device__ int o_segb() const { return o_scan() + align16(cap * 4); }
     __host__ __device__ int o_key(int j) const { return o_segb() + align16(((Mem::kSegCapFixed > 0 ? Mem::kSegCapFixed : cap) + 1) * 4) + j * align16(isec_cap * 4); }

@@ -10,10 +10,12 @@
 //   B. thread per (current choice id, ia) of one state: ccp / logsum on the integrated values, Euler
 //      inversion, value (dc_algo.jl:159-182)
 //   C. worker envelope + policy repair (envelope.cuh), credit-constraint point, store.
-// B and C run per income state on THREAD GROUPS (kGroups groups of kGroupThreads threads, each with its own envelope
+// B and C run per income state on THREAD GROUPS (G = 2 or 4 groups of 256 / G threads, each with its own envelope
 // scratch and named barrier): the envelopes of a period — short lines, many barriers, stretches where one warp works —
 // proceed side by side instead of one after the other on the whole CTA.
 #include <math_constants.h>
+
+#include <cstdlib>
 
 #define DC_SEG_INTERP_ATTR static __device__ __noinline__  // envelope.cuh
 #define DC_GROUPED 1  // block_* and worker_envelope run on groups of NT threads (device_common.cuh)
@@ -22,31 +24,28 @@
 
 namespace dcegm {
 
-#ifndef DCEGM_G_GROUPS
-#define DCEGM_G_GROUPS 2
-#endif
-constexpr int kGroups = DCEGM_G_GROUPS;            // income states in flight through phases B and C
-constexpr int kGroupThreads = kThreads / kGroups;  // 128
-static_assert(kGroupThreads % 32 == 0 && kGroups * kGroupThreads == kThreads && kGroups <= 8, "thread groups");
-
-// shared-memory map: ny x 7 double[cap] line arrays | vmat,cmat double[ny][2][na] each | per-state words |
-// kGroups envelope scratch regions (the dirty worker line of a state is written straight into its group's region)
+// shared-memory map: ny x 4 double[cap] worker line arrays | ny x 3 double[na + 1] retiree line arrays |
+// vmat,cmat double[ny][2][na] each | per-state words | `groups` envelope scratch regions (the dirty worker line of a
+// state is written straight into its group's region)
 struct GPlan {
-    int cap8, na8, ny;
-    int o_mat, o_meta, env_stride;
+    int cap8, na8, r8, ny, groups;
+    int o_ret, o_mat, o_meta, env_stride;
     EnvScratch env;  // region of group 0
-    __host__ __device__ GPlan(int cap, int isec_cap, int na, int ny_) {
+    __host__ __device__ GPlan(int cap, int isec_cap, int na, int ny_, int groups_) {
         ny = ny_;
+        groups = groups_;
         cap8 = EnvScratch::align16(cap * 8);
         na8 = EnvScratch::align16(na * 8);
-        o_mat = ny * 7 * cap8;
+        r8 = EnvScratch::align16((na + 1) * 8);  // the retiree's lines have exactly na + 1 points
+        o_ret = ny * 4 * cap8;
+        o_mat = o_ret + ny * 3 * r8;
         o_meta = o_mat + ny * 4 * na8;
         env.off = o_meta + EnvScratch::align16(ny * 5 * 8) + EnvScratch::align16(ny * 3 * 4);
         env.cap = cap;
         env.isec_cap = isec_cap;
         env_stride = EnvScratch::align16(env.bytes());
     }
-    __host__ __device__ size_t bytes() const { return (size_t)env.off + (size_t)kGroups * env_stride; }
+    __host__ __device__ size_t bytes() const { return (size_t)env.off + (size_t)groups * env_stride; }
     __device__ __forceinline__ EnvScratch scratch(int g) const {
         EnvScratch S = env;
         S.off += g * env_stride;
@@ -54,7 +53,7 @@ struct GPlan {
     }
     // line arrays of income state iy: 0 wc_x, 1 wc_y, 2 wv_x, 3 wv_y, 4 r_x, 5 rc_y, 6 rv_y
     __device__ __forceinline__ double* line(int iy, int a) const {
-        return reinterpret_cast<double*>(dc_smem + (iy * 7 + a) * cap8);
+        return reinterpret_cast<double*>(dc_smem + (a < 4 ? (iy * 4 + a) * cap8 : o_ret + (iy * 3 + a - 4) * r8));
     }
     // 0 vmat[iid=0], 1 vmat[iid=1], 2 cmat[0], 3 cmat[1]
     __device__ __forceinline__ double* mat(int iy, int a) const {
@@ -67,7 +66,8 @@ struct GPlan {
     }
 };
 
-size_t solver_g_smem_bytes(int cap, int isec_cap, int na, int ny) { return GPlan(cap, isec_cap, na, ny).bytes(); }
+// what the kernel needs at least (two thread groups); launch_solve_g takes four when they fit twice per SM
+size_t solver_g_smem_bytes(int cap, int isec_cap, int na, int ny) { return GPlan(cap, isec_cap, na, ny, 2).bytes(); }
 
 // stored by the nt threads t = 0 .. nt - 1 of the CTA or of one thread group
 __device__ inline void store_line_g(const DeviceBatch& B, int m, int it, int iy, int id, int kind, const double* x,
@@ -81,8 +81,11 @@ __device__ inline void store_line_g(const DeviceBatch& B, int m, int it, int iy,
 }
 
 // Top = largest step of the fixed-trip knot search (lines hold fewer than 2*Top points; chosen at launch from cap)
-template <int Top>
+// G = thread groups (income states in flight through phases B and C), kThreads / G threads each
+template <int Top, int G>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBatch B) {
+    constexpr int kGroups = G, kGroupThreads = kThreads / G;
+    static_assert(kGroupThreads % 32 == 0 && kGroups * kGroupThreads == kThreads && kGroups <= 8, "thread groups");
     const int m = B.order ? B.order[B.first + blockIdx.x] : B.first + blockIdx.x;
     const int tid = threadIdx.x;
     __shared__ DevModel s_p;
@@ -98,7 +101,7 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBat
     __syncthreads();
     const DevModel& p = s_p;
     const int na = p.na, ny = p.ny, nT = p.nT;
-    const GPlan P(B.lay.cap, B.lay.isec_cap, na, ny);
+    const GPlan P(B.lay.cap, B.lay.isec_cap, na, ny, kGroups);
     const EnvScratch S = P.scratch(grp);  // this thread group's envelope scratch
     const double* __restrict__ avec = B.grids + (size_t)p.grid * na;
     const double* __restrict__ wgt = B.wgt + (size_t)m * ny * ny;               // [iy][jy]
@@ -364,19 +367,36 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) solve_g_kernel(DeviceBat
     signal_model_done(B, m);
 }
 
+template <int Top, int G>
+static cudaError_t launch_solve_g_as(const DeviceBatch& B, int count, size_t smem, cudaStream_t stream) {
+    cudaError_t e = cudaFuncSetAttribute(solve_g_kernel<Top, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    solve_g_kernel<Top, G><<<count, kThreads, smem, stream>>>(B);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_solve_g(const DeviceBatch& B0, int first, int count, cudaStream_t stream) {
     DeviceBatch B = B0;
     B.first = first;
-    const size_t smem = GPlan(B.lay.cap, B.lay.isec_cap, B.lay.na, B.lay.ny).bytes();
+    // four thread groups when their scratch regions still leave room for kCtasPerSm CTAs per SM, else two
+    const size_t smem4 = GPlan(B.lay.cap, B.lay.isec_cap, B.lay.na, B.lay.ny, 4).bytes();
+    const size_t smem2 = GPlan(B.lay.cap, B.lay.isec_cap, B.lay.na, B.lay.ny, 2).bytes();
     const bool small = B.lay.cap < 256;  // na <= ~170: eight search steps instead of eleven
-    cudaError_t e = small ? cudaFuncSetAttribute(solve_g_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
-                          : cudaFuncSetAttribute(solve_g_kernel<kSearchTop>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    if (small)
-        solve_g_kernel<128><<<count, kThreads, smem, stream>>>(B);
-    else
-        solve_g_kernel<kSearchTop><<<count, kThreads, smem, stream>>>(B);
-    return cudaGetLastError();
+    bool four = false;
+    if (B.lay.ny > 2) {
+        int nb = 0;
+        cudaError_t e = small ? cudaFuncSetAttribute(solve_g_kernel<128, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4)
+                              : cudaFuncSetAttribute(solve_g_kernel<kSearchTop, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4);
+        if (e == cudaSuccess)
+            e = small ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, solve_g_kernel<128, 4>, kThreads, smem4)
+                      : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, solve_g_kernel<kSearchTop, 4>, kThreads, smem4);
+        if (e != cudaSuccess) cudaGetLastError();  // too large for one CTA even: two groups
+        four = e == cudaSuccess && nb >= kCtasPerSm;
+    }
+    const char* env = getenv("DCEGM_G_GROUPS");  // 2 or 4: overrides the choice (measurements)
+    if (env) four = atoi(env) == 4;
+    if (four) return small ? launch_solve_g_as<128, 4>(B, count, smem4, stream) : launch_solve_g_as<kSearchTop, 4>(B, count, smem4, stream);
+    return small ? launch_solve_g_as<128, 2>(B, count, smem2, stream) : launch_solve_g_as<kSearchTop, 2>(B, count, smem2, stream);
 }
 
 }  // namespace dcegm
