@@ -55,13 +55,31 @@ def test_gmodel_c5_draws(solver, oracle):
         assert_bitwise(g, oracle.solve_g(ps, nthreads=8, portable=True))
 
 
-@pytest.mark.parametrize("na,ny,nT", [(50, 3, 8), (200, 7, 12), (100, 1, 5)])
+# ny against the kernel's thread groups (four income states per round, two when ny <= 2): part of a round, exactly
+# one, one and a part, exactly two, two and one
+@pytest.mark.parametrize("na,ny,nT", [(50, 3, 8), (200, 7, 12), (100, 1, 5), (60, 2, 6), (80, 4, 6), (60, 8, 5), (120, 9, 4)])
 def test_gmodel_sizes(solver, oracle, na, ny, nT):
     from dcegm_jl_b200 import Param, _abi
 
     ps = [Param(par=dict(na=na, ny=ny, nT=nT)), Param(par=dict(na=na, ny=ny, nT=nT, rho=0.0, sigma=0.2))]
     g = solver.solve(_abi.MODEL_G, ps)
     assert_bitwise(g, oracle.solve_g(ps, portable=True))
+
+
+def test_gmodel_two_and_four_thread_groups_agree(solver, oracle):
+    """DCEGM_G_GROUPS forces the number of thread groups of solve_g_kernel (read at launch): both give the oracle's bits"""
+    import os
+
+    from dcegm_jl_b200 import _abi
+
+    ps = g_draws(64)
+    ref = oracle.solve_g(ps, nthreads=8, portable=True)
+    try:
+        for groups in ("2", "4"):
+            os.environ["DCEGM_G_GROUPS"] = groups
+            assert_bitwise(solver.solve(_abi.MODEL_G, ps), ref)
+    finally:
+        os.environ.pop("DCEGM_G_GROUPS", None)
 
 
 def test_minimal_egm(solver, oracle):
