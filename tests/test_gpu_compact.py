@@ -128,3 +128,39 @@ def test_minimal_models_and_small_batches():
         with pytest.raises(Exception):
             s.solve(_abi.MODEL_F, c3_draws(2, na=60), summary_only=True)
             s.fetch_compact()
+
+
+def test_device_records_equal_the_reference_encoder():
+    """the device encoder writes exactly the records the numpy restatement of the format builds (word for word):
+    abscissa runs, control bytes, residual payload, padding"""
+    from dcegm_jl_b200 import Param, _abi
+    from dcegm_jl_b200.compact import encode_reference
+    from dcegm_jl_b200.solver import Solver
+
+    ps = []
+    for lam, sig in ((2e-6, 0.35), (1e-3, 0.1), (0.05, 0.5)):
+        d = dict(na=120, sigma=sig)
+        d["lambda"] = lam
+        ps.append(Param(par=d))
+    os.environ["DCEGM_COMPACT_ALIAS"] = "0"  # every slot with its own record
+    try:
+        with Solver(0) as s:
+            sol = s.solve(_abi.MODEL_F, ps)
+            assert (sol.status.astype(np.int64) & _abi.ST_FATAL_MASK == 0).all()
+            cl = s.fetch_compact()
+            checked = 0
+            for m in range(len(ps)):
+                grid = cl.grid(m)
+                for it in range(sol.lay.nT):
+                    for id_ in range(2):
+                        nc, nv = int(sol.lens[m, it, 0, id_, 0]), int(sol.lens[m, it, 0, id_, 1])
+                        rc, ac, rv, av = encode_reference(sol.lines[m, it, 0, id_, 0, :nc], sol.lines[m, it, 0, id_, 1, :nv], grid)
+                        sc, sv = cl.slot(m, _abi.KIND_C, id_, it), cl.slot(m, _abi.KIND_V, id_, it)
+                        for slot, rec, aux in ((sc, rc, ac), (sv, rv, av)):
+                            w0 = int(cl.woffsets[slot])
+                            assert int(cl.aux[slot]) == aux, (m, it, id_, slot)
+                            assert cl.words[w0:w0 + len(rec)].tobytes() == rec.tobytes(), (m, it, id_, slot)
+                            checked += len(rec)
+            assert checked == int(cl.woffsets[-1])  # the records tile the stream: nothing between or behind them
+    finally:
+        os.environ.pop("DCEGM_COMPACT_ALIAS")
