@@ -48,6 +48,7 @@ struct EnvScratchT : Mem {
     //                | 2 u8[isec_cap]
     __host__ __device__ static int align16(int b) { return (b + 15) / 16 * 16; }
     __host__ __device__ int segcap() const { return Mem::kSegCapFixed > 0 ? Mem::kSegCapFixed : cap; }
+#ifndef DC_ENV_GUARDS
     __host__ __device__ int o_d(int j) const { return off + j * align16(cap * 8); }
     __host__ __device__ int o_i(int j) const { return o_d(5) + j * align16(isec_cap * 8); }
     __host__ __device__ int o_redd() const { return o_i(8); }
@@ -61,6 +62,60 @@ struct EnvScratchT : Mem {
     __host__ __device__ int o_segrise() const { return o_u8(4); }
     __host__ __device__ int o_ok(int j) const { return o_segrise() + align16(Mem::kSegCapFixed > 0 ? Mem::kSegCapFixed : cap) + j * align16(isec_cap); }
     __host__ __device__ int bytes() const { return o_ok(2) - off; }
+#else
+    // Debug build (-DDC_ENV_GUARDS, tools/env_guards_run.sh): 16 guard bytes behind every array.  worker_envelope fills
+    // them (and the alignment padding) on entry and checks them on exit; a written guard shows up as status bit 15 — the
+    // stand-in for compute-sanitizer's memcheck on the envelope's index arithmetic, in shared and in global memory
+    static constexpr int kGuard = 16;
+    __host__ __device__ static int slot(int b) { return align16(b) + kGuard; }
+    __host__ __device__ int o_d(int j) const { return off + j * slot(cap * 8); }
+    __host__ __device__ int o_i(int j) const { return o_d(5) + j * slot(isec_cap * 8); }
+    __host__ __device__ int o_redd() const { return o_i(8); }
+    __host__ __device__ int o_scan() const { return o_redd() + slot(Mem::kMaxWarps * 8); }
+    __host__ __device__ int o_segb() const { return o_scan() + slot(cap * 4); }
+    __host__ __device__ int o_key(int j) const { return o_segb() + slot((segcap() + 1) * 4) + j * slot(isec_cap * 4); }
+    __host__ __device__ int o_red() const { return o_key(2); }
+    __host__ __device__ int o_cnt() const { return o_red() + slot((Mem::kMaxWarps + 1) * 4); }
+    __host__ __device__ int o_u16(int j) const { return o_cnt() + 32 + kGuard + j * slot(cap * 2); }
+    __host__ __device__ int o_u8(int j) const { return o_u16(5) + j * slot(cap); }
+    __host__ __device__ int o_segrise() const { return o_u8(4); }
+    __host__ __device__ int o_ok(int j) const { return o_segrise() + slot(segcap()) + j * slot(isec_cap); }
+    __host__ __device__ int bytes() const { return o_ok(2) - off; }
+#endif
+#ifdef DC_ENV_GUARDS
+    // f(offset of an array, its bytes, bytes of its slot) for every array of the region
+    template <class F>
+    __device__ void each_array(F f) const {
+        for (int j = 0; j < 5; j++) f(o_d(j), cap * 8, slot(cap * 8));
+        for (int j = 0; j < 8; j++) f(o_i(j), isec_cap * 8, slot(isec_cap * 8));
+        f(o_redd(), Mem::kMaxWarps * 8, slot(Mem::kMaxWarps * 8));
+        f(o_scan(), cap * 4, slot(cap * 4));
+        f(o_segb(), (segcap() + 1) * 4, slot((segcap() + 1) * 4));
+        for (int j = 0; j < 2; j++) f(o_key(j), isec_cap * 4, slot(isec_cap * 4));
+        f(o_red(), (Mem::kMaxWarps + 1) * 4, slot((Mem::kMaxWarps + 1) * 4));
+        f(o_cnt(), 32, 32 + kGuard);
+        for (int j = 0; j < 5; j++) f(o_u16(j), cap * 2, slot(cap * 2));
+        for (int j = 0; j < 4; j++) f(o_u8(j), cap, slot(cap));
+        f(o_segrise(), segcap(), slot(segcap()));
+        for (int j = 0; j < 2; j++) f(o_ok(j), isec_cap, slot(isec_cap));
+    }
+    __device__ void guards_fill() const {
+        unsigned char* base = reinterpret_cast<unsigned char*>(this->mem());
+        each_array([&](int o, int b, int sl) {
+            for (int k = b; k < sl; k++) base[o + k] = 0xA5;
+        });
+    }
+    __device__ int guards_bad() const {  // arrays whose guard was written
+        const unsigned char* base = reinterpret_cast<const unsigned char*>(this->mem());
+        int bad = 0;
+        each_array([&](int o, int b, int sl) {
+            int hit = 0;
+            for (int k = b; k < sl; k++) hit |= base[o + k] != 0xA5;
+            bad += hit;
+        });
+        return bad;
+    }
+#endif
 #define DC_ARR(T, name, expr) \
     __device__ __forceinline__ T* name() const { return reinterpret_cast<T*>(this->mem() + (expr)); }
     // extended dirty worker line (EGM order): x, value, policy.  The EGM step writes the na points at
@@ -234,6 +289,12 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
                                        int rem_words, bool first_period = false) {
     const int tid = dc_gtid<NT>();  // index inside the thread group (the CTA unless DC_GROUPED)
     unsigned status = 0;
+#ifdef DC_ENV_GUARDS
+    if (tid == 0) S.guards_fill();  // ordered before every write of this call by the barrier below
+#ifdef DC_ENV_GUARD_SELFTEST  // positive control: one int written one element behind an array must be reported
+    if (tid == 1) S.scan()[S.cap] = 1;
+#endif
+#endif
 
     // ---- bend-back guard (dc_algo.jl:394-418) ------------------------------------------------
     double mn = CUDART_INF;
@@ -884,6 +945,9 @@ __device__ inline void worker_envelope(const ES& S, int koff, int na, double a0,
     if (flag || status) atomicOr(&S.cnt()[2], flag | (int)status);
     dc_gsync<NT>();
     if (tid == 0) {
+#ifdef DC_ENV_GUARDS
+        if (S.guards_bad()) atomicOr(&S.cnt()[2], 1 << 15);  // an index left its array: shows up as status bit 15
+#endif
         *nV = lenV;
         *nC = lenC;
         meta_out->n_segments = nseg;
